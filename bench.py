@@ -1,0 +1,315 @@
+"""Headline benchmark: training throughput (samples/s) of the reference's own workload.
+
+Config ("reference default"): the VGG conv-BN-ReLU net of /root/reference/multigpu.py:36-71
+on CIFAR-shaped synthetic data, per-GPU batch 512 (multigpu.py:259), fp32 parameters/activations with TF32
+tensor-core convolutions (what torch's cuDNN default does for the reference), SGD(lr .4, momentum .9, wd 5e-4) +
+the triangular LambdaLR stepped per batch (multigpu.py:129-143), data-parallel over N GPUs (weak scaling).
+
+    python bench.py --gpus 1 --steps 20 --warmup 5                  # this framework
+    python bench.py --impl reference --gpus 1 --steps 20 --warmup 5 # unmodified reference (baseline/_ref)
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 --master-port P \
+        bench.py --gpus N ...
+
+One JSON line on stdout (rank 0). `value` is device-timed (CUDA events, max over ranks) with device-resident
+synthetic batches; `e2e` re-measures through the public Trainer API with the batch copied from pinned host memory
+every step and the loss read back to the host.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+from pathlib import Path
+
+REPO = Path(__file__).resolve().parent
+sys.path.insert(0, str(REPO))
+
+BATCH_PER_GPU = 512
+NUM_CLASSES = 10
+
+
+# ------------------------------------------------------------------------------------------------
+# clocks sampler (B200_PROFILING.md "clocks DURING the timed region")
+# ------------------------------------------------------------------------------------------------
+class ClockSampler:
+    FIELDS = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+              "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+              "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index: int = 0):
+        self.gpu_index = gpu_index
+        self.proc = None
+        self.lines: list[str] = []
+        self.thread = None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--id={self.gpu_index}", f"--query-gpu={self.FIELDS}", "--format=csv,noheader,nounits",
+                 "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+        except Exception:
+            self.proc = None
+            return
+        def pump():
+            for line in self.proc.stdout:
+                self.lines.append(line.strip())
+        self.thread = threading.Thread(target=pump, daemon=True)
+        self.thread.start()
+
+    def stop(self) -> dict:
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, smax, reasons, power = [], [], set(), []
+        for ln in self.lines:
+            parts = [x.strip() for x in ln.split(",")]
+            if len(parts) < 9:
+                continue
+            try:
+                sm.append(float(parts[1])); smax.append(float(parts[2])); power.append(float(parts[3]))
+            except ValueError:
+                continue
+            for name, val in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), parts[5:9]):
+                if val.lower().startswith("active"):
+                    reasons.add(name)
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no samples"]}
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": max(smax), "power_w_max": max(power), "samples": len(sm),
+                "reasons": sorted(reasons)}
+
+
+# ------------------------------------------------------------------------------------------------
+# shared helpers
+# ------------------------------------------------------------------------------------------------
+def dist_env():
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    return rank, local_rank, world
+
+
+def make_host_batches(n: int, batch: int, seed: int):
+    """`n` distinct CIFAR-shaped batches in pinned host memory (synthetic: uniform pixels, random labels)."""
+    import torch
+    g = torch.Generator().manual_seed(seed)
+    xs, ys = [], []
+    for _ in range(n):
+        x = torch.rand(batch, 3, 32, 32, generator=g)
+        y = torch.randint(0, NUM_CLASSES, (batch,), generator=g)
+        if torch.cuda.is_available():
+            x = x.pin_memory(); y = y.pin_memory()
+        xs.append(x); ys.append(y)
+    return xs, ys
+
+
+def max_over_ranks(ms: float, world: int) -> float:
+    import torch
+    if world == 1:
+        return ms
+    import torch.distributed as dist
+    t = torch.tensor([ms], device="cuda", dtype=torch.float64)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return float(t.item())
+
+
+def barrier(world: int):
+    import torch
+    if world > 1:
+        import torch.distributed as dist
+        dist.barrier()
+    torch.cuda.synchronize()
+
+
+def timed_loop(step_fn, steps: int, world: int) -> float:
+    """barrier+sync, CUDA-event time `steps` calls of step_fn(i), barrier+sync; returns ms (max over ranks)."""
+    import torch
+    barrier(world)
+    e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(steps):
+        step_fn(i)
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1)
+    barrier(world)
+    return max_over_ranks(ms, world)
+
+
+def emit(args, world, impl, total_ms, e2e_ms, h2d, d2h, launches, clocks, extra_cfg):
+    global_batch = BATCH_PER_GPU * world
+    value = global_batch * args.steps / (total_ms / 1e3)
+    e2e_value = global_batch * args.steps / (e2e_ms / 1e3) if e2e_ms else None
+    baseline = None  # BASELINE.md publishes no number for the reference
+    out = {
+        "metric": "training throughput, samples/s (VGG/CIFAR-shaped, batch 512 per GPU, SGD+LambdaLR)",
+        "value": round(value, 1), "unit": "samples/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": round(total_ms / args.steps, 4), "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": baseline, "dtype": "fp32 storage, TF32 tensor-core conv math (reference default: cudnn.allow_tf32)",
+        "data": "synthetic (uniform CIFAR-shaped images, random labels; random-init weights)",
+        "impl": impl,
+        "config": {"model": "VGG (reference multigpu.py:36-71, 9.23M params)", "global_batch": global_batch,
+                   "batch_per_gpu": BATCH_PER_GPU, "seq_len": None, "image": "3x32x32",
+                   "parallelism": f"dp{world}", "optimizer": "SGD lr0.4 m0.9 wd5e-4 + LambdaLR per step",
+                   "l2": "per-step working set (~2.5 GB of activations) exceeds the 126 MB L2; 4 distinct input batches rotate",
+                   **extra_cfg},
+        "clocks": clocks,
+        "e2e": {"value": round(e2e_value, 1) if e2e_value else None, "unit": "samples/s",
+                "ms_per_step": round(e2e_ms / args.steps, 4) if e2e_ms else None,
+                "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
+        "gpu_launches": launches,
+    }
+    print(json.dumps(out), flush=True)
+
+
+# ------------------------------------------------------------------------------------------------
+# reference arm: unmodified /root/reference scripts from baseline/_ref, through their own classes
+# ------------------------------------------------------------------------------------------------
+def run_reference(args):
+    ref_dir = REPO / "baseline" / "_ref"
+    if not (ref_dir / "multigpu.py").exists():
+        print(json.dumps({"impl": "reference", "unavailable": "baseline/_ref is missing (run baseline/install_ref.sh)"}))
+        return
+    sys.path.insert(0, str(ref_dir))
+    import numpy as np
+    import torch
+    rank, local_rank, world = dist_env()
+    try:
+        if world > 1:
+            import multigpu as ref   # noqa: the reference's multi-GPU script (DDP + NCCL)
+        else:
+            import singlegpu as ref  # noqa: the reference's single-GPU script
+    except Exception as e:  # pragma: no cover
+        print(json.dumps({"impl": "reference", "unavailable": f"import failed: {type(e).__name__}: {e}"}))
+        return
+    if not torch.cuda.is_available():
+        print(json.dumps({"impl": "reference", "unavailable": "no CUDA device"}))
+        return
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        # ddp_setup (multigpu.py:24-33) rewrites MASTER_ADDR/PORT to localhost:12355 for every rank and calls
+        # init_process_group("nccl") - the reference's own bootstrap.
+        ref.ddp_setup(rank, world)
+    torch.manual_seed(1234 + rank)
+    # load_train_objs() (multigpu.py:122-144) minus the CIFAR-10 download (no network): same literals.
+    model = ref.VGG().cuda()
+    optimizer = torch.optim.SGD(model.parameters(), lr=0.4, momentum=0.9, weight_decay=5e-4)
+    num_epochs, steps_per_epoch = 20, (49 if world > 1 else 98)
+    lr_lambda = lambda step: np.interp([step / steps_per_epoch], [0, num_epochs * 0.3, num_epochs], [0, 1, 0])[0]
+    scheduler = torch.optim.lr_scheduler.LambdaLR(optimizer, lr_lambda)
+    trainer = ref.Trainer(model, [], optimizer, local_rank, 1, scheduler=scheduler)
+
+    xs, ys = make_host_batches(4, BATCH_PER_GPU, seed=100 + rank)
+    dxs = [x.cuda() for x in xs]; dys = [y.cuda() for y in ys]
+
+    def dev_step(i):
+        trainer._run_batch(dxs[i % 4], dys[i % 4])
+
+    probe = trainer.model.module.classifier.bias if world > 1 else trainer.model.classifier.bias
+
+    def e2e_step(i):
+        # what Trainer._run_epoch does per batch (multigpu.py:104-107): blocking .to(gpu) then _run_batch;
+        # the reference never reads the loss, so the device->host read is one updated parameter element.
+        source = xs[i % 4].to(local_rank); targets = ys[i % 4].to(local_rank)
+        trainer._run_batch(source, targets)
+        probe[0].item()
+
+    for i in range(args.warmup):
+        dev_step(i)
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    total_ms = timed_loop(dev_step, args.steps, world)
+    clocks = sampler.stop() if rank == 0 else {}
+    for i in range(2):
+        e2e_step(i)
+    e2e_ms = timed_loop(e2e_step, args.steps, world)
+    if rank == 0:
+        h2d = xs[0].numel() * 4 + ys[0].numel() * 8
+        emit(args, world, "reference", total_ms, e2e_ms, h2d, 4, 0, clocks,
+             {"stack": "torch DDP + NCCL + cuDNN/cuBLAS" if world > 1 else "torch eager + cuDNN/cuBLAS"})
+    if world > 1:
+        ref.destroy_process_group()
+
+
+# ------------------------------------------------------------------------------------------------
+# this framework
+# ------------------------------------------------------------------------------------------------
+def run_ours(args):
+    import torch
+    import distributed_data_parallel_experiment_b200 as ddpx
+    from distributed_data_parallel_experiment_b200 import _lib
+    rank, local_rank, world = dist_env()
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device (CPU runs are covered by tests/)")
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        ddpx.launch.setup_from_env()
+    torch.manual_seed(1234 + rank)
+    train_objs = ddpx.recipes.vgg_train_objs(world_size=world, synthetic=True)
+    model, optimizer, scheduler = train_objs.model, train_objs.optimizer, train_objs.scheduler
+    trainer = ddpx.Trainer(model, [], optimizer, local_rank, 1, scheduler=scheduler)
+
+    xs, ys = make_host_batches(4, BATCH_PER_GPU, seed=100 + rank)
+    dxs = [x.cuda() for x in xs]; dys = [y.cuda() for y in ys]
+
+    def dev_step(i):
+        trainer._run_batch(dxs[i % 4], dys[i % 4])
+
+    def e2e_step(i):
+        loss = trainer.train_step(xs[i % 4], ys[i % 4])   # public API: pinned host batch in, host float out
+        return loss
+
+    for i in range(args.warmup):
+        dev_step(i)
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    l0 = _lib.launches()
+    total_ms = timed_loop(dev_step, args.steps, world)
+    launches = _lib.launches() - l0
+    clocks = sampler.stop() if rank == 0 else {}
+    for i in range(2):
+        e2e_step(i)
+    e2e_ms = timed_loop(e2e_step, args.steps, world)
+    if rank == 0:
+        h2d = xs[0].numel() * 4 + ys[0].numel() * 8
+        emit(args, world, "ddpx_b200", total_ms, e2e_ms, h2d, 4, launches, clocks,
+             {"stack": "hand-written sm_100a kernels (tcgen05/TMEM/TMA conv+GEMM, fused BN/ReLU/pool/CE/SGD)"
+                       + (", P2P fused all-reduce+SGD over NVLink" if world > 1 else "")})
+    if world > 1:
+        ddpx.launch.teardown()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=30)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    args = ap.parse_args()
+    if args.warmup < 3:
+        args.warmup = 3
+    _, _, world = dist_env()
+    if args.gpus > 1 and world == 1:
+        # convenience: re-launch under torchrun when invoked directly with --gpus N
+        cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={args.gpus}",
+               "--master-addr", "127.0.0.1", "--master-port", os.environ.get("MASTER_PORT", "29511"), __file__,
+               "--gpus", str(args.gpus), "--steps", str(args.steps), "--warmup", str(args.warmup), "--impl", args.impl]
+        raise SystemExit(subprocess.call(cmd))
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,391 @@
+// Convolution helpers that do not need tensor cores, sm_100a:
+//   * weight re-packing torch [Cout][Cin][3][3] -> [tap][Cout][Cin] (fprop) and tap-flipped [tap][Cin][Cout] (dgrad)
+//   * direct 3x3 convolution for tiny Cin (the RGB stem, K = 27): forward (+bias, +BN statistics) and weight gradient
+//   * NCHW <-> NHWC layout transposes, stand-alone ReLU / 2x2 max-pool forward+backward, spatial mean
+// Reference parity: conv0 at /root/reference/multigpu.py:53, pools :59, mean :68, DeepNN S:21-31.
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include "../../include/ddpx_kernels.h"
+
+namespace {
+
+inline int nblocks(long long total, int block, int cap = 148 * 16) {
+  long long b = (total + block - 1) / block;
+  if (b > cap) b = cap;
+  if (b < 1) b = 1;
+  return static_cast<int>(b);
+}
+
+// ------------------------------------------------------------------------------------------------
+// weight packing
+// ------------------------------------------------------------------------------------------------
+__global__ void pack_conv_w_kernel(const float* __restrict__ w, float* __restrict__ wf, float* __restrict__ wd, int Cout,
+                                   int Cin) {
+  const long long total = static_cast<long long>(Cout) * Cin * 9;
+  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    // i indexes the fprop layout [tap][co][ci] so that writes are coalesced
+    const int ci = static_cast<int>(i % Cin);
+    const long long t = i / Cin;
+    const int co = static_cast<int>(t % Cout);
+    const int tap = static_cast<int>(t / Cout);
+    const float v = w[(static_cast<long long>(co) * Cin + ci) * 9 + tap];
+    if (wf != nullptr) wf[i] = v;
+    if (wd != nullptr) wd[(static_cast<long long>(8 - tap) * Cin + ci) * Cout + co] = v;  // flipped tap, transposed
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// direct conv for Cin == 3 (input NCHW, output NHWC).  One thread = one output pixel, all Cout channels.
+// ------------------------------------------------------------------------------------------------
+constexpr int kStemPix = 128;  // pixels per block
+
+__global__ void __launch_bounds__(kStemPix)
+conv_stem_fprop_kernel(const float* __restrict__ x, const float* __restrict__ w, const float* __restrict__ bias,
+                       float* __restrict__ y, int Nimg, int H, int W, int Cout, int act, float* __restrict__ stat_sum,
+                       float* __restrict__ stat_sq) {
+  extern __shared__ float sm[];
+  float* sw = sm;                        // [27][Cout]  (tap-major so the per-cout read is a broadcast-free row)
+  float* tile = sm + 27 * Cout;          // [kStemPix][Cout + 1]
+  for (int i = threadIdx.x; i < 27 * Cout; i += blockDim.x) {
+    const int co = i % Cout, k = i / Cout;   // k = ci*9 + tap
+    sw[i] = w[co * 27 + k];
+  }
+  __syncthreads();
+  const long long P = static_cast<long long>(Nimg) * H * W;
+  const int ld = Cout + 1;
+  for (long long p0 = static_cast<long long>(blockIdx.x) * kStemPix; p0 < P; p0 += static_cast<long long>(gridDim.x) * kStemPix) {
+    const long long p = p0 + threadIdx.x;
+    float in[27];
+    if (p < P) {
+      const int wq = static_cast<int>(p % W);
+      const long long t = p / W;
+      const int hq = static_cast<int>(t % H);
+      const long long n = t / H;
+#pragma unroll
+      for (int ci = 0; ci < 3; ++ci)
+#pragma unroll
+        for (int r = 0; r < 3; ++r)
+#pragma unroll
+          for (int s = 0; s < 3; ++s) {
+            const int hh = hq + r - 1, ww = wq + s - 1;
+            in[ci * 9 + r * 3 + s] = (hh >= 0 && hh < H && ww >= 0 && ww < W)
+                                         ? __ldg(x + ((n * 3 + ci) * H + hh) * W + ww) : 0.f;
+          }
+    }
+    for (int co = 0; co < Cout; ++co) {
+      float acc = bias != nullptr ? __ldg(bias + co) : 0.f;
+#pragma unroll
+      for (int k = 0; k < 27; ++k) acc = fmaf(in[k], sw[k * Cout + co], acc);
+      tile[threadIdx.x * ld + co] = (p < P) ? acc : 0.f;
+    }
+    __syncthreads();
+    // coalesced store + per-channel statistics from the tile
+    const long long valid = (P - p0 < kStemPix) ? (P - p0) : kStemPix;
+    for (int i = threadIdx.x; i < kStemPix * Cout; i += blockDim.x) {
+      const int px = i / Cout, co = i % Cout;
+      if (px < valid) {
+        float v = tile[px * ld + co];
+        if (act == 1) v = fmaxf(v, 0.f);
+        y[(p0 + px) * Cout + co] = v;
+      }
+    }
+    if (stat_sum != nullptr) {
+      for (int co = threadIdx.x; co < Cout; co += blockDim.x) {
+        float s = 0.f, q = 0.f;
+        for (int px = 0; px < valid; ++px) { const float v = tile[px * ld + co]; s += v; q += v * v; }
+        atomicAdd(stat_sum + co, s);
+        atomicAdd(stat_sq + co, q);
+      }
+    }
+    __syncthreads();
+  }
+}
+
+// weight gradient for Cin == 3: dw[co][ci][r][s] += sum_pixels dy[p][co] * x[n][ci][h+r-1][w+s-1]
+// block = one image at a time (padded image staged in shared memory); thread = (co, tap-group)
+__global__ void __launch_bounds__(256)
+conv_stem_wgrad_kernel(const float* __restrict__ dy, const float* __restrict__ x, float* __restrict__ dw, int Nimg, int H,
+                       int W, int Cout) {
+  extern __shared__ float sm[];
+  const int PH = H + 2, PW = W + 2;
+  float* img = sm;  // [3][PH][PW]
+  const int groups = blockDim.x / Cout;          // how many tap groups fit
+  const int co = threadIdx.x % Cout;
+  const int grp = threadIdx.x / Cout;
+  const int per = (27 + groups - 1) / groups;    // taps per group
+  const int k0 = grp * per;
+  float acc[27];
+#pragma unroll
+  for (int k = 0; k < 27; ++k) acc[k] = 0.f;
+  for (int n = blockIdx.x; n < Nimg; n += gridDim.x) {
+    __syncthreads();
+    for (int i = threadIdx.x; i < 3 * PH * PW; i += blockDim.x) {
+      const int ww = i % PW - 1, hh = (i / PW) % PH - 1, ci = i / (PW * PH);
+      img[i] = (hh >= 0 && hh < H && ww >= 0 && ww < W) ? __ldg(x + ((static_cast<long long>(n) * 3 + ci) * H + hh) * W + ww) : 0.f;
+    }
+    __syncthreads();
+    if (grp < groups) {
+      for (int h = 0; h < H; ++h)
+        for (int wq = 0; wq < W; ++wq) {
+          const float g = __ldg(dy + ((static_cast<long long>(n) * H + h) * W + wq) * Cout + co);
+#pragma unroll
+          for (int j = 0; j < 27; ++j) {
+            if (j < per) {
+              const int k = k0 + j;
+              if (k < 27) {
+                const int ci = k / 9, r = (k % 9) / 3, s = k % 3;
+                acc[j] = fmaf(g, img[(ci * PH + h + r) * PW + wq + s], acc[j]);
+              }
+            }
+          }
+        }
+    }
+  }
+  if (grp < groups) {
+#pragma unroll
+    for (int j = 0; j < 27; ++j)
+      if (j < per && k0 + j < 27) atomicAdd(dw + co * 27 + k0 + j, acc[j]);
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// layout transposes (per image: [C][HW] <-> [HW][C]) through a padded shared-memory tile
+// ------------------------------------------------------------------------------------------------
+__global__ void transpose_batched_kernel(const float* __restrict__ in, float* __restrict__ out, int rows, int cols) {
+  // in: [batch][rows][cols] -> out: [batch][cols][rows]
+  __shared__ float t[32][33];
+  const long long b = blockIdx.z;
+  const float* src = in + b * rows * cols;
+  float* dst = out + b * rows * cols;
+  const int c0 = blockIdx.x * 32, r0 = blockIdx.y * 32;
+  for (int j = threadIdx.y; j < 32; j += blockDim.y) {
+    const int r = r0 + j, c = c0 + threadIdx.x;
+    if (r < rows && c < cols) t[j][threadIdx.x] = src[static_cast<long long>(r) * cols + c];
+  }
+  __syncthreads();
+  for (int j = threadIdx.y; j < 32; j += blockDim.y) {
+    const int c = c0 + j, r = r0 + threadIdx.x;
+    if (r < rows && c < cols) dst[static_cast<long long>(c) * rows + r] = t[threadIdx.x][j];
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// stand-alone ReLU / max-pool (NHWC) and spatial mean
+// ------------------------------------------------------------------------------------------------
+__global__ void relu_fwd_kernel(const float* __restrict__ x, float* __restrict__ y, long long n) {
+  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < n; i += static_cast<long long>(gridDim.x) * blockDim.x)
+    y[i] = fmaxf(x[i], 0.f);
+}
+__global__ void relu_bwd_kernel(const float* __restrict__ y, const float* __restrict__ dy, float* __restrict__ dx, long long n) {
+  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < n; i += static_cast<long long>(gridDim.x) * blockDim.x)
+    dx[i] = y[i] > 0.f ? dy[i] : 0.f;
+}
+__global__ void maxpool_fwd_kernel(const float* __restrict__ x, float* __restrict__ y, int Nimg, int H, int W, int C) {
+  const int Ho = H / 2, Wo = W / 2;
+  const long long total = static_cast<long long>(Nimg) * Ho * Wo * C;
+  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total; i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int c = static_cast<int>(i % C);
+    long long t = i / C;
+    const int wo = static_cast<int>(t % Wo); t /= Wo;
+    const int ho = static_cast<int>(t % Ho);
+    const long long n = t / Ho;
+    const float* b = x + ((n * H + 2 * ho) * W + 2 * wo) * C + c;
+    y[i] = fmaxf(fmaxf(b[0], b[C]), fmaxf(b[static_cast<long long>(W) * C], b[static_cast<long long>(W) * C + C]));
+  }
+}
+__global__ void maxpool_bwd_kernel(const float* __restrict__ x, const float* __restrict__ dy, float* __restrict__ dx, int Nimg,
+                                   int H, int W, int C) {
+  const int Ho = H / 2, Wo = W / 2;
+  const long long total = static_cast<long long>(Nimg) * Ho * Wo * C;
+  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total; i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int c = static_cast<int>(i % C);
+    long long t = i / C;
+    const int wo = static_cast<int>(t % Wo); t /= Wo;
+    const int ho = static_cast<int>(t % Ho);
+    const long long n = t / Ho;
+    const long long o = ((n * H + 2 * ho) * W + 2 * wo) * C + c;
+    const long long offs[4] = {o, o + C, o + static_cast<long long>(W) * C, o + static_cast<long long>(W) * C + C};
+    int arg = 0; float m = x[offs[0]];
+#pragma unroll
+    for (int q = 1; q < 4; ++q) { const float v = x[offs[q]]; if (v > m) { m = v; arg = q; } }
+    const float g = dy[i];
+#pragma unroll
+    for (int q = 0; q < 4; ++q) dx[offs[q]] = (q == arg) ? g : 0.f;
+  }
+}
+// y[n][c] = mean over hw of x[n][hw][c]; backward broadcasts dy/HW
+__global__ void spatial_mean_fwd_kernel(const float* __restrict__ x, float* __restrict__ y, int Nimg, int HW, int C) {
+  const long long total = static_cast<long long>(Nimg) * C;
+  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total; i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int c = static_cast<int>(i % C);
+    const long long n = i / C;
+    float s = 0.f;
+    for (int p = 0; p < HW; ++p) s += x[(n * HW + p) * C + c];
+    y[i] = s / HW;
+  }
+}
+__global__ void spatial_mean_bwd_kernel(const float* __restrict__ dy, float* __restrict__ dx, int Nimg, int HW, int C) {
+  const long long total = static_cast<long long>(Nimg) * HW * C;
+  const float inv = 1.f / HW;
+  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total; i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int c = static_cast<int>(i % C);
+    const long long n = i / (static_cast<long long>(HW) * C);
+    dx[i] = dy[n * C + c] * inv;
+  }
+}
+// column sums: out[c] (+)= sum_r x[r][c]   (bias gradients)
+__global__ void colsum_kernel(const float* __restrict__ x, float* __restrict__ out, long long rows, int cols, int accumulate) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= cols) return;
+  float s = 0.f;
+  for (long long r = blockIdx.y; r < rows; r += gridDim.y) s += x[r * cols + c];
+  if (gridDim.y == 1 && !accumulate) out[c] = s; else atomicAdd(out + c, s);
+}
+__global__ void scale_copy_kernel(const float* __restrict__ src, float* __restrict__ dst, long long n, float scale, int accumulate) {
+  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < n; i += static_cast<long long>(gridDim.x) * blockDim.x)
+    dst[i] = accumulate ? dst[i] + src[i] * scale : src[i] * scale;
+}
+
+}  // namespace
+
+#define LAUNCH_OK() (cudaGetLastError() == cudaSuccess ? DDPX_OK : DDPX_ERR_LAUNCH)
+
+extern "C" int ddpx_pack_conv_weights(const float* w, float* w_fprop, float* w_dgrad, int Cout, int Cin, void* stream) {
+  const long long total = static_cast<long long>(Cout) * Cin * 9;
+  pack_conv_w_kernel<<<nblocks(total, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(w, w_fprop, w_dgrad, Cout, Cin);
+  return LAUNCH_OK();
+}
+
+extern "C" int ddpx_conv_stem_fprop(const float* x_nchw, const float* w, const float* bias, float* y_nhwc, int Nimg, int H,
+                                    int W, int Cout, int act, float* stat_sum, float* stat_sq, void* stream) {
+  if (Cout > 128) return DDPX_ERR_SHAPE;
+  const size_t smem = (27 * Cout + kStemPix * (Cout + 1)) * sizeof(float);
+  static bool attr = false;
+  if (!attr) {
+    cudaFuncSetAttribute(conv_stem_fprop_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024);
+    attr = true;
+  }
+  const long long P = static_cast<long long>(Nimg) * H * W;
+  conv_stem_fprop_kernel<<<nblocks(P, kStemPix, 148 * 4), kStemPix, smem, static_cast<cudaStream_t>(stream)>>>(
+      x_nchw, w, bias, y_nhwc, Nimg, H, W, Cout, act, stat_sum, stat_sq);
+  return LAUNCH_OK();
+}
+
+extern "C" int ddpx_conv_stem_wgrad(const float* dy_nhwc, const float* x_nchw, float* dw, int Nimg, int H, int W, int Cout,
+                                    void* stream) {
+  if (Cout > 256 || 256 % Cout) return DDPX_ERR_SHAPE;
+  const size_t smem = static_cast<size_t>(3) * (H + 2) * (W + 2) * sizeof(float);
+  if (smem > 48 * 1024) return DDPX_ERR_SHAPE;
+  int grid = Nimg < 148 * 2 ? Nimg : 148 * 2;
+  conv_stem_wgrad_kernel<<<grid, 256, smem, static_cast<cudaStream_t>(stream)>>>(dy_nhwc, x_nchw, dw, Nimg, H, W, Cout);
+  return LAUNCH_OK();
+}
+
+// [batch][rows][cols] -> [batch][cols][rows];  NCHW->NHWC: rows = C, cols = H*W;  NHWC->NCHW: rows = H*W, cols = C
+extern "C" int ddpx_transpose_batched(const float* in, float* out, int batch, int rows, int cols, void* stream) {
+  dim3 grid((cols + 31) / 32, (rows + 31) / 32, batch), block(32, 8);
+  if (grid.y > 65535 || grid.z > 65535) return DDPX_ERR_SHAPE;
+  transpose_batched_kernel<<<grid, block, 0, static_cast<cudaStream_t>(stream)>>>(in, out, rows, cols);
+  return LAUNCH_OK();
+}
+
+extern "C" int ddpx_relu_fwd(const float* x, float* y, long long n, void* stream) {
+  relu_fwd_kernel<<<nblocks(n, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(x, y, n);
+  return LAUNCH_OK();
+}
+extern "C" int ddpx_relu_bwd(const float* y, const float* dy, float* dx, long long n, void* stream) {
+  relu_bwd_kernel<<<nblocks(n, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(y, dy, dx, n);
+  return LAUNCH_OK();
+}
+extern "C" int ddpx_maxpool2x2_fwd(const float* x, float* y, int Nimg, int H, int W, int C, void* stream) {
+  if ((H | W) & 1) return DDPX_ERR_SHAPE;
+  const long long total = static_cast<long long>(Nimg) * (H / 2) * (W / 2) * C;
+  maxpool_fwd_kernel<<<nblocks(total, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(x, y, Nimg, H, W, C);
+  return LAUNCH_OK();
+}
+extern "C" int ddpx_maxpool2x2_bwd(const float* x, const float* dy, float* dx, int Nimg, int H, int W, int C, void* stream) {
+  if ((H | W) & 1) return DDPX_ERR_SHAPE;
+  const long long total = static_cast<long long>(Nimg) * (H / 2) * (W / 2) * C;
+  maxpool_bwd_kernel<<<nblocks(total, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(x, dy, dx, Nimg, H, W, C);
+  return LAUNCH_OK();
+}
+extern "C" int ddpx_spatial_mean_fwd(const float* x, float* y, int Nimg, int HW, int C, void* stream) {
+  spatial_mean_fwd_kernel<<<nblocks(static_cast<long long>(Nimg) * C, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(x, y, Nimg, HW, C);
+  return LAUNCH_OK();
+}
+extern "C" int ddpx_spatial_mean_bwd(const float* dy, float* dx, int Nimg, int HW, int C, void* stream) {
+  spatial_mean_bwd_kernel<<<nblocks(static_cast<long long>(Nimg) * HW * C, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(dy, dx, Nimg, HW, C);
+  return LAUNCH_OK();
+}
+extern "C" int ddpx_colsum(const float* x, float* out, long long rows, int cols, int accumulate, void* stream) {
+  int gy = static_cast<int>(rows / 64);
+  if (gy < 1) gy = 1;
+  if (gy > 256) gy = 256;
+  if (gy > 1 && !accumulate) cudaMemsetAsync(out, 0, sizeof(float) * cols, static_cast<cudaStream_t>(stream));
+  dim3 grid((cols + 127) / 128, gy);
+  colsum_kernel<<<grid, 128, 0, static_cast<cudaStream_t>(stream)>>>(x, out, rows, cols, accumulate);
+  return LAUNCH_OK();
+}
+extern "C" int ddpx_scale_copy(const float* src, float* dst, long long n, float scale, int accumulate, void* stream) {
+  scale_copy_kernel<<<nblocks(n, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(src, dst, n, scale, accumulate);
+  return LAUNCH_OK();
+}
+extern "C" int ddpx_zero(void* p, long long bytes, void* stream) {
+  return cudaMemsetAsync(p, 0, static_cast<size_t>(bytes), static_cast<cudaStream_t>(stream)) == cudaSuccess ? DDPX_OK : DDPX_ERR_LAUNCH;
+}
+
+// ------------------------------------------------------------------------------------------------
+// small / odd-shaped fp32 GEMM on CUDA cores (classifier N = 10, toy Linear(20,1): shapes whose row pitch is not a
+// multiple of 16 bytes cannot be described to TMA).  C[m][n] = act(sum_k A(m,k) * B(n,k) + bias[n]) (+ C if accumulate),
+// A(m,k) = A[m*sam + k*sak], B(n,k) = B[n*sbn + k*sbk].
+// ------------------------------------------------------------------------------------------------
+namespace {
+__global__ void gemm_small_kernel(const float* __restrict__ A, const float* __restrict__ B, float* __restrict__ C, int M, int N,
+                                  int K, long long sam, long long sak, long long sbn, long long sbk, long long ldc,
+                                  const float* __restrict__ bias, int act, int accumulate) {
+  __shared__ float As[32][33];
+  __shared__ float Bs[32][33];
+  const int tx = threadIdx.x, ty = threadIdx.y;           // 32 x 8
+  const int m0 = blockIdx.y * 32, n0 = blockIdx.x * 32;
+  float acc[4] = {0.f, 0.f, 0.f, 0.f};
+  for (int k0 = 0; k0 < K; k0 += 32) {
+    for (int j = ty; j < 32; j += 8) {
+      const int m = m0 + j, n = n0 + j, k = k0 + tx;
+      As[j][tx] = (m < M && k < K) ? A[m * sam + k * sak] : 0.f;
+      Bs[j][tx] = (n < N && k < K) ? B[n * sbn + k * sbk] : 0.f;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int kk = 0; kk < 32; ++kk) {
+      const float b = Bs[tx][kk];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) acc[i] = fmaf(As[ty + 8 * i][kk], b, acc[i]);
+    }
+    __syncthreads();
+  }
+  const int n = n0 + tx;
+  if (n < N) {
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int m = m0 + ty + 8 * i;
+      if (m < M) {
+        float v = acc[i] + (bias != nullptr ? bias[n] : 0.f);
+        if (act == 1) v = fmaxf(v, 0.f);
+        float* c = C + m * ldc + n;
+        *c = accumulate ? *c + v : v;
+      }
+    }
+  }
+}
+}  // namespace
+
+extern "C" int ddpx_gemm_small(const float* A, const float* B, float* C, int M, int N, int K, long long sam, long long sak,
+                               long long sbn, long long sbk, long long ldc, const float* bias, int act, int accumulate,
+                               void* stream) {
+  dim3 grid((N + 31) / 32, (M + 31) / 32), block(32, 8);
+  if (grid.y > 65535) return DDPX_ERR_SHAPE;
+  gemm_small_kernel<<<grid, block, 0, static_cast<cudaStream_t>(stream)>>>(A, B, C, M, N, K, sam, sak, sbn, sbk, ldc, bias, act,
+                                                                          accumulate);
+  return LAUNCH_OK();
+}

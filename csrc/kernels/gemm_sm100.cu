@@ -1,0 +1,579 @@
+// tcgen05 / TMEM / TMA tensor-core core for sm_100a.
+//
+// One persistent, warp-specialised kernel template serves three problem shapes:
+//   MODE_GEMM   D[M,N] = op(A) * op(B)                  (Linear fwd / dgrad / wgrad; K- or MN-major operands)
+//   MODE_FPROP  3x3 stride-1 pad-1 convolution as an implicit GEMM over NHWC activations
+//               (also used for the data-gradient with tap-flipped, transposed weights)
+//   MODE_WGRAD  3x3 convolution weight-gradient: K = pixels, both operands MN-major
+//
+// Reference parity: these replace the cuDNN / cuBLAS calls behind nn.Conv2d / nn.Linear in
+// /root/reference/multigpu.py:53,62 (W13-W15, W20).
+//
+// Roles (256 threads): warp 0 = TMA producer, warp 1 = MMA issuer (one lane), warp 2 = TMEM allocator,
+// warps 4-7 = epilogue (TMEM -> registers -> global). Accumulators are double-buffered in TMEM so the
+// epilogue of tile i overlaps the MMAs of tile i+1. Operand tiles are 128-byte-swizzled in shared memory
+// exactly as TMA writes them; padding of the convolution comes from TMA out-of-bounds zero fill with
+// signed start coordinates (no im2col buffer is ever materialised).
+#include "sm100_ptx.cuh"
+#include "../../include/ddpx_kernels.h"
+
+#include <cudaTypedefs.h>
+#include <stdio.h>
+#include <mutex>
+
+namespace ddpx {
+
+enum { MODE_GEMM = 0, MODE_FPROP = 1, MODE_WGRAD = 2 };
+
+constexpr int kBlockM = 128;          // TMEM lanes / UMMA M
+constexpr int kStageABytes = 16384;   // 128 rows x 128 B
+constexpr int kNumThreads = 256;
+constexpr int kMaxStages = 8;
+
+struct TcParams {
+  int M, N;                 // logical extent of the output (rows <-> TMEM lanes, cols <-> TMEM columns)
+  int m_blocks, n_blocks;
+  int block_n;              // 32..256, multiple of 32
+  int k_steps_total;        // GEMM: ceil(K/BK); FPROP: 9*cin_blocks; WGRAD: pixels/32
+  int k_steps_per_split;
+  int num_splits;
+  int num_stages;
+  int a_mn, b_mn;           // operand majors (1 = MN-major / "transposed")
+  // convolution geometry
+  int H, W, cin_blocks;
+  int box_w, box_h, box_n;
+  int cin_total;
+  // epilogue
+  void* out;
+  long long ldo;
+  int out_bf16;
+  int atomic;               // 1 = accumulate with red.global.add.f32 (split-K / wgrad)
+  int act;                  // 0 none, 1 relu, 2 gelu(tanh)
+  const float* bias;        // GEMM: per output column; FPROP: per output channel (row)
+  float* stat_sum;          // FPROP: per-channel sum / sum-of-squares of the raw conv output
+  float* stat_sq;
+};
+
+__device__ __forceinline__ float gelu_tanh(float x) {
+  const float k0 = 0.7978845608028654f, k1 = 0.044715f;
+  float u = k0 * (x + k1 * x * x * x);
+  return 0.5f * x * (1.f + tanhf(u));
+}
+
+template <int kMode, bool kBF16>
+__global__ void __launch_bounds__(kNumThreads, 1)
+tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const TcParams p) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  // carve shared memory: [stages x (A | B)] | barriers | tmem ptr
+  const uint32_t stage_b_bytes = static_cast<uint32_t>(p.block_n) * 128u;
+  const uint32_t stage_bytes = kStageABytes + stage_b_bytes;
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + static_cast<size_t>(p.num_stages) * stage_bytes);
+  uint64_t* empty_bar = full_bar + kMaxStages;
+  uint64_t* tfull_bar = empty_bar + kMaxStages;   // [2]
+  uint64_t* tempty_bar = tfull_bar + 2;           // [2]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + 2);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+
+  constexpr int kElt = kBF16 ? 2 : 4;
+  constexpr int kBK = 128 / kElt;          // K elements per stage for K-major operands (= K rows for MN-major)
+  constexpr int kUmmaK = 32 / kElt;        // K per MMA instruction
+  constexpr int kChunk = 128 / kElt;       // MN elements per 128-byte swizzle row
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmA);
+    tma_prefetch_desc(&tmB);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int s = 0; s < p.num_stages; ++s) {
+      mbar_init(&full_bar[s], 1);
+      mbar_init(&empty_bar[s], 1);
+    }
+    for (int s = 0; s < 2; ++s) {
+      mbar_init(&tfull_bar[s], 1);
+      mbar_init(&tempty_bar[s], 4);
+    }
+    fence_barrier_init();
+  }
+  if (warp == 2) {
+    tmem_alloc(tmem_slot, 512);
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  const int tiles_mn = p.m_blocks * p.n_blocks;
+  const int taps = (kMode == MODE_WGRAD) ? 9 : 1;
+  const int num_items = tiles_mn * taps * p.num_splits;
+
+  auto decode = [&](int item, int& m_blk, int& n_blk, int& tap, int& split) {
+    m_blk = item % p.m_blocks;
+    int t = item / p.m_blocks;
+    n_blk = t % p.n_blocks;
+    t /= p.n_blocks;
+    tap = t % taps;
+    split = t / taps;
+  };
+  auto ksteps_of = [&](int split) {
+    int k0 = split * p.k_steps_per_split;
+    int k1 = min(k0 + p.k_steps_per_split, p.k_steps_total);
+    return max(k1 - k0, 0);
+  };
+
+  if (warp == 0) {
+    // ======================================= TMA producer =======================================
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int item = blockIdx.x; item < num_items; item += gridDim.x) {
+        int m_blk, n_blk, tap, split;
+        decode(item, m_blk, n_blk, tap, split);
+        const int m0 = m_blk * kBlockM;
+        const int n0 = n_blk * p.block_n;
+        const int kbeg = split * p.k_steps_per_split;
+        const int nk = ksteps_of(split);
+        for (int i = 0; i < nk; ++i) {
+          const int kk = kbeg + i;
+          mbar_wait(&empty_bar[stage], phase ^ 1u, 0x100u + stage);
+          uint8_t* sa = smem + static_cast<size_t>(stage) * stage_bytes;
+          uint8_t* sb = sa + kStageABytes;
+          mbar_arrive_expect_tx(&full_bar[stage], stage_bytes);
+          if constexpr (kMode == MODE_GEMM) {
+            const int k0 = kk * kBK;
+            if (!p.a_mn) {
+              tma_load_2d(sa, &tmA, &full_bar[stage], k0, m0);
+            } else {
+              for (int j = 0; j < kBlockM / kChunk; ++j)
+                tma_load_2d(sa + j * (kBK * 128), &tmA, &full_bar[stage], m0 + j * kChunk, k0);
+            }
+            if (!p.b_mn) {
+              tma_load_2d(sb, &tmB, &full_bar[stage], k0, n0);
+            } else {
+              for (int j = 0; j < p.block_n / kChunk; ++j)
+                tma_load_2d(sb + j * (kBK * 128), &tmB, &full_bar[stage], n0 + j * kChunk, k0);
+            }
+          } else if constexpr (kMode == MODE_FPROP) {
+            // K order: tap-major, then input-channel block.  A = packed weights [tap][Cout][Cin].
+            const int t9 = kk / p.cin_blocks;
+            const int cb = kk - t9 * p.cin_blocks;
+            const int r = t9 / 3, s = t9 - r * 3;
+            tma_load_3d(sa, &tmA, &full_bar[stage], cb * kBK, m0, t9);
+            // B = NHWC activations; tile of block_n consecutive pixels = box (box_w, box_h, box_n)
+            const int hw = p.H * p.W;
+            const int img = n0 / hw;
+            const int h0 = (n0 - img * hw) / p.W;
+            tma_load_4d(sb, &tmB, &full_bar[stage], cb * kBK, s - 1, h0 + r - 1, img);
+          } else {
+            // WGRAD: K step = 32 consecutive pixels.  A = dY [pixels][Cout] (MN-major), B = shifted X.
+            const int r = tap / 3, s = tap - r * 3;
+            const int p0 = kk * 32;
+            const int hw = p.H * p.W;
+            const int img = p0 / hw;
+            const int h0 = (p0 - img * hw) / p.W;
+            for (int j = 0; j < kBlockM / kChunk; ++j)
+              tma_load_2d(sa + j * (kBK * 128), &tmA, &full_bar[stage], m0 + j * kChunk, p0);
+            for (int j = 0; j < p.block_n / kChunk; ++j)
+              tma_load_4d(sb + j * (kBK * 128), &tmB, &full_bar[stage], n0 + j * kChunk, s - 1, h0 + r - 1, img);
+          }
+          if (++stage == p.num_stages) { stage = 0; phase ^= 1u; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ======================================= MMA issuer =========================================
+    if (lane == 0) {
+      const bool a_mn = (kMode == MODE_WGRAD) ? true : (kMode == MODE_FPROP ? false : (p.a_mn != 0));
+      const bool b_mn = (kMode == MODE_WGRAD) ? true : (kMode == MODE_FPROP ? false : (p.b_mn != 0));
+      const uint32_t idesc = make_idesc(kBF16, a_mn, b_mn, kBlockM, static_cast<uint32_t>(p.block_n));
+      // descriptor strides: K-major -> 8-row groups 1024 B apart; MN-major -> 128-B-wide chunks kBK*128 apart
+      const uint32_t a_lbo = a_mn ? kBK * 128u : 16u, b_lbo = b_mn ? kBK * 128u : 16u;
+      const uint32_t a_kadv = a_mn ? kUmmaK * 128u : 32u, b_kadv = b_mn ? kUmmaK * 128u : 32u;
+      // MN-major tf32 must use the 32-byte-atom flavour of the 128B swizzle (4-row groups, 512 B apart)
+      const uint32_t a_lay = (a_mn && !kBF16) ? 1u : 2u, b_lay = (b_mn && !kBF16) ? 1u : 2u;
+      const uint32_t a_sbo = (a_mn && !kBF16) ? 512u : 1024u, b_sbo = (b_mn && !kBF16) ? 512u : 1024u;
+      int stage = 0;
+      uint32_t phase = 0;
+      int acc = 0;
+      uint32_t acc_phase = 0;
+      for (int item = blockIdx.x; item < num_items; item += gridDim.x) {
+        int m_blk, n_blk, tap, split;
+        decode(item, m_blk, n_blk, tap, split);
+        const int nk = ksteps_of(split);
+        mbar_wait(&tempty_bar[acc], acc_phase ^ 1u, 0x200u + acc);
+        tc_fence_after();
+        const uint32_t tmem_d = tmem_base + static_cast<uint32_t>(acc * p.block_n);
+        for (int i = 0; i < nk; ++i) {
+          mbar_wait(&full_bar[stage], phase, 0x300u + stage);
+          tc_fence_after();
+          const uint32_t sa = smem_u32(smem + static_cast<size_t>(stage) * stage_bytes);
+          const uint32_t sb = sa + kStageABytes;
+#pragma unroll
+          for (int k = 0; k < kBK / kUmmaK; ++k) {
+            const uint64_t adesc = make_smem_desc_sw128(sa + k * a_kadv, a_lbo, a_sbo, a_lay);
+            const uint64_t bdesc = make_smem_desc_sw128(sb + k * b_kadv, b_lbo, b_sbo, b_lay);
+            tc_mma<kBF16>(tmem_d, adesc, bdesc, idesc, (i > 0 || k > 0) ? 1u : 0u);
+          }
+          tc_commit(&empty_bar[stage]);   // smem slot is free once these MMAs retire
+          if (++stage == p.num_stages) { stage = 0; phase ^= 1u; }
+        }
+        tc_commit(&tfull_bar[acc]);       // accumulator complete -> epilogue
+        if (++acc == 2) { acc = 0; acc_phase ^= 1u; }
+      }
+    }
+  } else if (warp >= 4) {
+    // ======================================= epilogue ===========================================
+    const int ew = warp - 4;                 // == warp % 4 -> TMEM lanes [32*ew, 32*ew+32)
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    for (int item = blockIdx.x; item < num_items; item += gridDim.x) {
+      int m_blk, n_blk, tap, split;
+      decode(item, m_blk, n_blk, tap, split);
+      const int nk = ksteps_of(split);
+      const int row = m_blk * kBlockM + ew * 32 + lane;     // output row owned by this thread
+      const int n0 = n_blk * p.block_n;
+      mbar_wait(&tfull_bar[acc], acc_phase, 0x400u + acc);
+      tc_fence_after();
+      const uint32_t taddr = tmem_base + (static_cast<uint32_t>(ew * 32) << 16) + static_cast<uint32_t>(acc * p.block_n);
+      float ssum = 0.f, ssq = 0.f;
+      for (int c0 = 0; c0 < p.block_n; c0 += 32) {
+        uint32_t v[32];
+        tmem_ld_32x32(taddr + c0, v);
+        tmem_ld_wait();
+        if (nk == 0) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) v[j] = 0u;
+        }
+        if constexpr (kMode == MODE_GEMM) {
+          if (row < p.M) {
+            if (p.atomic) {
+              float* o = reinterpret_cast<float*>(p.out) + static_cast<long long>(row) * p.ldo + n0 + c0;
+#pragma unroll
+              for (int j = 0; j < 32; ++j)
+                if (n0 + c0 + j < p.N) atomicAdd(o + j, __uint_as_float(v[j]));
+            } else {
+              float f[32];
+#pragma unroll
+              for (int j = 0; j < 32; ++j) {
+                float x = __uint_as_float(v[j]);
+                const int col = n0 + c0 + j;
+                if (p.bias != nullptr && col < p.N) x += __ldg(p.bias + col);
+                if (p.act == 1) x = fmaxf(x, 0.f);
+                else if (p.act == 2) x = gelu_tanh(x);
+                f[j] = x;
+              }
+              const bool full = (n0 + c0 + 32 <= p.N);
+              if (p.out_bf16) {
+                __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(p.out) + static_cast<long long>(row) * p.ldo + n0 + c0;
+                if (full && ((reinterpret_cast<uintptr_t>(o) & 15) == 0)) {
+#pragma unroll
+                  for (int j = 0; j < 32; j += 8) {
+                    __nv_bfloat162 h0 = __floats2bfloat162_rn(f[j], f[j + 1]);
+                    __nv_bfloat162 h1 = __floats2bfloat162_rn(f[j + 2], f[j + 3]);
+                    __nv_bfloat162 h2 = __floats2bfloat162_rn(f[j + 4], f[j + 5]);
+                    __nv_bfloat162 h3 = __floats2bfloat162_rn(f[j + 6], f[j + 7]);
+                    uint4 u;
+                    u.x = *reinterpret_cast<uint32_t*>(&h0);
+                    u.y = *reinterpret_cast<uint32_t*>(&h1);
+                    u.z = *reinterpret_cast<uint32_t*>(&h2);
+                    u.w = *reinterpret_cast<uint32_t*>(&h3);
+                    *reinterpret_cast<uint4*>(o + j) = u;
+                  }
+                } else {
+#pragma unroll
+                  for (int j = 0; j < 32; ++j)
+                    if (n0 + c0 + j < p.N) o[j] = __float2bfloat16(f[j]);
+                }
+              } else {
+                float* o = reinterpret_cast<float*>(p.out) + static_cast<long long>(row) * p.ldo + n0 + c0;
+                if (full && ((reinterpret_cast<uintptr_t>(o) & 15) == 0)) {
+#pragma unroll
+                  for (int j = 0; j < 32; j += 4)
+                    *reinterpret_cast<float4*>(o + j) = make_float4(f[j], f[j + 1], f[j + 2], f[j + 3]);
+                } else {
+#pragma unroll
+                  for (int j = 0; j < 32; ++j)
+                    if (n0 + c0 + j < p.N) o[j] = f[j];
+                }
+              }
+            }
+          }
+        } else if constexpr (kMode == MODE_FPROP) {
+          // row = output channel, column = pixel; NHWC store is coalesced across the warp's 32 channels
+          if (row < p.M) {
+            float* o = reinterpret_cast<float*>(p.out) + static_cast<long long>(n0 + c0) * p.ldo + row;
+            const float b = (p.bias != nullptr) ? __ldg(p.bias + row) : 0.f;
+#pragma unroll
+            for (int j = 0; j < 32; ++j) {
+              if (n0 + c0 + j < p.N) {
+                float x = __uint_as_float(v[j]) + b;
+                ssum += x;
+                ssq += x * x;
+                if (p.act == 1) x = fmaxf(x, 0.f);
+                o[static_cast<long long>(j) * p.ldo] = x;
+              }
+            }
+          }
+        } else {
+          // WGRAD: row = Cout, column = Cin; scatter-accumulate into the torch-layout gradient [Cout][Cin][3][3]
+          if (row < p.M) {
+            float* o = reinterpret_cast<float*>(p.out) + (static_cast<long long>(row) * p.cin_total + n0 + c0) * 9 + tap;
+#pragma unroll
+            for (int j = 0; j < 32; ++j)
+              if (n0 + c0 + j < p.N) atomicAdd(o + j * 9, __uint_as_float(v[j]));
+          }
+        }
+      }
+      if constexpr (kMode == MODE_FPROP) {
+        if (p.stat_sum != nullptr && row < p.M) {
+          atomicAdd(p.stat_sum + row, ssum);
+          atomicAdd(p.stat_sq + row, ssq);
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&tempty_bar[acc]);
+      if (++acc == 2) { acc = 0; acc_phase ^= 1u; }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  if (warp == 2) tmem_dealloc(tmem_base, 512);
+}
+
+// =================================================================================================
+// host side
+// =================================================================================================
+static PFN_cuTensorMapEncodeTiled_v12000 get_encode_fn() {
+  static PFN_cuTensorMapEncodeTiled_v12000 fn = nullptr;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void* ptr = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &ptr, cudaEnableDefault, &qres) == cudaSuccess &&
+        qres == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<PFN_cuTensorMapEncodeTiled_v12000>(ptr);
+  });
+  return fn;
+}
+
+// rank-N tiled map with 128B swizzle; dims/strides innermost first; strides in bytes for dims 1..rank-1
+static int make_tmap(CUtensorMap* out, const void* base, bool bf16, int rank, const uint64_t* dims,
+                     const uint64_t* strides_bytes, const uint32_t* box, bool atom32 = false) {
+  auto fn = get_encode_fn();
+  if (!fn) return DDPX_ERR_DRIVER;
+  cuuint64_t gdim[5];
+  cuuint64_t gstr[4];
+  cuuint32_t bx[5], es[5];
+  for (int i = 0; i < rank; ++i) { gdim[i] = dims[i]; bx[i] = box[i]; es[i] = 1; }
+  for (int i = 0; i < rank - 1; ++i) gstr[i] = strides_bytes[i];
+  CUresult r = fn(out, bf16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32, rank,
+                  const_cast<void*>(base), gdim, gstr, bx, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                  atom32 ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B : CU_TENSOR_MAP_SWIZZLE_128B,
+                  CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    fprintf(stderr, "[ddpx] cuTensorMapEncodeTiled failed: %d (rank %d)\n", static_cast<int>(r), rank);
+    return DDPX_ERR_TMAP;
+  }
+  return DDPX_OK;
+}
+
+static int g_num_sms = 0;
+static int num_sms() {
+  if (g_num_sms == 0) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&g_num_sms, cudaDevAttrMultiProcessorCount, dev);
+  }
+  return g_num_sms;
+}
+
+static int pick_stages(int block_n) {
+  const int stage = kStageABytes + block_n * 128;
+  int s = (220 * 1024) / stage;
+  if (s > kMaxStages) s = kMaxStages;
+  if (s < 2) s = 2;
+  return s;
+}
+
+template <int kMode, bool kBF16>
+static int launch_tc(const CUtensorMap& a, const CUtensorMap& b, TcParams& p, cudaStream_t stream) {
+  p.num_stages = pick_stages(p.block_n);
+  const size_t smem = static_cast<size_t>(p.num_stages) * (kStageABytes + p.block_n * 128) + 1024 /*align*/ + 256;
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaError_t e = cudaFuncSetAttribute(tc_kernel<kMode, kBF16>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    if (e != cudaSuccess) return DDPX_ERR_LAUNCH;
+    attr_set = true;
+  }
+  const int taps = (kMode == MODE_WGRAD) ? 9 : 1;
+  const int items = p.m_blocks * p.n_blocks * taps * p.num_splits;
+  int grid = items < num_sms() ? items : num_sms();
+  if (grid < 1) grid = 1;
+  tc_kernel<kMode, kBF16><<<grid, kNumThreads, smem, stream>>>(a, b, p);
+  return cudaGetLastError() == cudaSuccess ? DDPX_OK : DDPX_ERR_LAUNCH;
+}
+
+}  // namespace ddpx
+
+using namespace ddpx;
+
+extern "C" int ddpx_gemm(const void* A, const void* B, void* D, int M, int N, int K, long long lda, long long ldb,
+                         long long ldd, int a_mn, int b_mn, int bf16, int out_bf16, const float* bias, int act,
+                         int split_k, int accumulate, void* stream_) {
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  const int elt = bf16 ? 2 : 4;
+  const int bk = 128 / elt, chunk = 128 / elt;
+  if (M <= 0 || N <= 0 || K <= 0) return DDPX_ERR_ARG;
+  if ((lda * elt) % 16 || (ldb * elt) % 16) return DDPX_ERR_ALIGN;
+  if ((reinterpret_cast<uintptr_t>(A) & 15) || (reinterpret_cast<uintptr_t>(B) & 15)) return DDPX_ERR_ALIGN;
+  TcParams p{};
+  p.M = M; p.N = N;
+  // N tile: the largest of {256,128,64} that still gives every SM a tile; narrow outputs get a narrow tile
+  const int mb = (M + kBlockM - 1) / kBlockM;
+  const int min_bn = (b_mn && chunk > 32) ? chunk : 32;
+  int bn = 256;
+  while (bn > 64 && mb * ((N + bn - 1) / bn) < num_sms()) bn /= 2;
+  while (bn > min_bn && bn / 2 >= N) bn /= 2;
+  if (bn < min_bn) bn = min_bn;
+  p.block_n = bn;
+  p.m_blocks = mb;
+  p.n_blocks = (N + bn - 1) / bn;
+  p.k_steps_total = (K + bk - 1) / bk;
+  int splits = split_k > 0 ? split_k : 1;
+  if (splits > p.k_steps_total) splits = p.k_steps_total;
+  p.k_steps_per_split = (p.k_steps_total + splits - 1) / splits;
+  p.num_splits = (p.k_steps_total + p.k_steps_per_split - 1) / p.k_steps_per_split;
+  p.a_mn = a_mn; p.b_mn = b_mn;
+  p.out = D; p.ldo = ldd; p.out_bf16 = out_bf16;
+  p.atomic = (accumulate || p.num_splits > 1) ? 1 : 0;
+  if (p.atomic && out_bf16) return DDPX_ERR_ARG;
+  p.act = act; p.bias = bias;
+  CUtensorMap ta, tb;
+  int rc;
+  {
+    uint64_t dims[2], str[1]; uint32_t box[2];
+    if (!a_mn) { dims[0] = K; dims[1] = M; box[0] = bk; box[1] = kBlockM; }
+    else       { dims[0] = M; dims[1] = K; box[0] = chunk; box[1] = bk; }
+    str[0] = static_cast<uint64_t>(lda) * elt;
+    if ((rc = make_tmap(&ta, A, bf16, 2, dims, str, box, a_mn && !bf16)) != DDPX_OK) return rc;
+    if (!b_mn) { dims[0] = K; dims[1] = N; box[0] = bk; box[1] = bn; }
+    else       { dims[0] = N; dims[1] = K; box[0] = chunk; box[1] = bk; }
+    str[0] = static_cast<uint64_t>(ldb) * elt;
+    if ((rc = make_tmap(&tb, B, bf16, 2, dims, str, box, b_mn && !bf16)) != DDPX_OK) return rc;
+  }
+  return bf16 ? launch_tc<MODE_GEMM, true>(ta, tb, p, stream) : launch_tc<MODE_GEMM, false>(ta, tb, p, stream);
+}
+
+// pixel-tile geometry shared by fprop / wgrad: `pixels` consecutive NHWC pixels as a (w,h,n) box
+static int conv_box(int pixels, int H, int W, int Nimg, int* bw, int* bh, int* bn) {
+  if (W > pixels || pixels % W) return DDPX_ERR_SHAPE;
+  int rows = pixels / W;
+  if (rows <= H) {
+    if (H % rows) return DDPX_ERR_SHAPE;
+    *bw = W; *bh = rows; *bn = 1;
+  } else {
+    if (rows % H) return DDPX_ERR_SHAPE;
+    *bw = W; *bh = H; *bn = rows / H;
+    if (Nimg % *bn) return DDPX_ERR_SHAPE;
+  }
+  if (*bw > 256 || *bh > 256 || *bn > 256) return DDPX_ERR_SHAPE;
+  return DDPX_OK;
+}
+
+extern "C" int ddpx_conv3x3_fprop(const float* x, const float* wpacked, float* y, int Nimg, int H, int W, int Cin,
+                                  int Cout, const float* bias, int act, float* stat_sum, float* stat_sq,
+                                  void* stream_) {
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  if (Cin % 32 || Cout % 32) return DDPX_ERR_SHAPE;
+  const long long P = static_cast<long long>(Nimg) * H * W;
+  int bn = 256;
+  while (bn > 32 && (P % bn)) bn /= 2;
+  int bw, bh, bnn;
+  while (bn >= 32 && conv_box(bn, H, W, Nimg, &bw, &bh, &bnn) != DDPX_OK) bn /= 2;
+  if (bn < 32 || P % bn) return DDPX_ERR_SHAPE;
+  TcParams p{};
+  p.M = Cout; p.N = static_cast<int>(P);
+  p.block_n = bn;
+  p.m_blocks = (Cout + kBlockM - 1) / kBlockM;
+  p.n_blocks = static_cast<int>(P / bn);
+  p.cin_blocks = Cin / 32;
+  p.k_steps_total = 9 * p.cin_blocks;
+  p.k_steps_per_split = p.k_steps_total;
+  p.num_splits = 1;
+  p.H = H; p.W = W; p.box_w = bw; p.box_h = bh; p.box_n = bnn; p.cin_total = Cin;
+  p.out = y; p.ldo = Cout; p.act = act; p.bias = bias; p.stat_sum = stat_sum; p.stat_sq = stat_sq;
+  CUtensorMap ta, tb;
+  int rc;
+  {
+    uint64_t dims[3] = {static_cast<uint64_t>(Cin), static_cast<uint64_t>(Cout), 9};
+    uint64_t str[2] = {static_cast<uint64_t>(Cin) * 4, static_cast<uint64_t>(Cin) * Cout * 4};
+    uint32_t box[3] = {32, kBlockM, 1};
+    if ((rc = make_tmap(&ta, wpacked, false, 3, dims, str, box)) != DDPX_OK) return rc;
+  }
+  {
+    uint64_t dims[4] = {static_cast<uint64_t>(Cin), static_cast<uint64_t>(W), static_cast<uint64_t>(H),
+                        static_cast<uint64_t>(Nimg)};
+    uint64_t str[3] = {static_cast<uint64_t>(Cin) * 4, static_cast<uint64_t>(Cin) * W * 4,
+                       static_cast<uint64_t>(Cin) * W * H * 4};
+    uint32_t box[4] = {32, static_cast<uint32_t>(bw), static_cast<uint32_t>(bh), static_cast<uint32_t>(bnn)};
+    if ((rc = make_tmap(&tb, x, false, 4, dims, str, box)) != DDPX_OK) return rc;
+  }
+  return launch_tc<MODE_FPROP, false>(ta, tb, p, stream);
+}
+
+extern "C" int ddpx_conv3x3_wgrad(const float* dy, const float* x, float* dw, int Nimg, int H, int W, int Cin,
+                                  int Cout, int split_k, void* stream_) {
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  if (Cin % 32 || Cout % 32) return DDPX_ERR_SHAPE;
+  const long long P = static_cast<long long>(Nimg) * H * W;
+  if (P % 32) return DDPX_ERR_SHAPE;
+  int bw, bh, bnn, rc;
+  if ((rc = conv_box(32, H, W, Nimg, &bw, &bh, &bnn)) != DDPX_OK) return rc;
+  TcParams p{};
+  p.M = Cout; p.N = Cin;
+  int bn = Cin >= 256 ? 256 : Cin;      // Cin is a multiple of 32
+  if (Cin > 256 && Cin % 256) bn = 128;
+  if (bn % 32) return DDPX_ERR_SHAPE;
+  p.block_n = bn;
+  p.m_blocks = (Cout + kBlockM - 1) / kBlockM;
+  p.n_blocks = (Cin + bn - 1) / bn;
+  p.k_steps_total = static_cast<int>(P / 32);
+  const int tiles = p.m_blocks * p.n_blocks * 9;
+  int splits = split_k;
+  if (splits <= 0) {   // fill the machine about twice over
+    splits = (2 * num_sms() + tiles - 1) / tiles;
+    if (splits < 1) splits = 1;
+  }
+  if (splits > p.k_steps_total) splits = p.k_steps_total;
+  p.k_steps_per_split = (p.k_steps_total + splits - 1) / splits;
+  p.num_splits = (p.k_steps_total + p.k_steps_per_split - 1) / p.k_steps_per_split;
+  p.H = H; p.W = W; p.box_w = bw; p.box_h = bh; p.box_n = bnn; p.cin_total = Cin; p.cin_blocks = Cin / 32;
+  p.out = dw; p.atomic = 1;
+  CUtensorMap ta, tb;
+  {
+    uint64_t dims[2] = {static_cast<uint64_t>(Cout), static_cast<uint64_t>(P)};
+    uint64_t str[1] = {static_cast<uint64_t>(Cout) * 4};
+    uint32_t box[2] = {32, 32};
+    if ((rc = make_tmap(&ta, dy, false, 2, dims, str, box, true)) != DDPX_OK) return rc;
+  }
+  {
+    uint64_t dims[4] = {static_cast<uint64_t>(Cin), static_cast<uint64_t>(W), static_cast<uint64_t>(H),
+                        static_cast<uint64_t>(Nimg)};
+    uint64_t str[3] = {static_cast<uint64_t>(Cin) * 4, static_cast<uint64_t>(Cin) * W * 4,
+                       static_cast<uint64_t>(Cin) * W * H * 4};
+    uint32_t box[4] = {32, static_cast<uint32_t>(bw), static_cast<uint32_t>(bh), static_cast<uint32_t>(bnn)};
+    if ((rc = make_tmap(&tb, x, false, 4, dims, str, box, true)) != DDPX_OK) return rc;
+  }
+  return launch_tc<MODE_WGRAD, false>(ta, tb, p, stream);
+}
+
+extern "C" unsigned int ddpx_read_error_word(void) {
+  unsigned int v = 0;
+  cudaMemcpyFromSymbol(&v, g_ddpx_error_word, sizeof(v));
+  return v;
+}

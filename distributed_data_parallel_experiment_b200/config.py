@@ -1,0 +1,63 @@
+"""Environment / flag knobs (reference has none: every value is a literal).
+
+Defaults reproduce the reference; every knob is optional.
+"""
+from __future__ import annotations
+
+import os
+from dataclasses import dataclass
+
+
+def _env_int(name: str, default: int) -> int:
+    v = os.environ.get(name)
+    return int(v) if v not in (None, "") else default
+
+
+def _env_str(name: str, default: str) -> str:
+    v = os.environ.get(name)
+    return v if v not in (None, "") else default
+
+
+@dataclass
+class RuntimeConfig:
+    master_addr: str = "localhost"      # multigpu.py:30
+    master_port: int = 12355            # multigpu.py:31
+    backend: str = "auto"               # auto | p2p | nccl | gloo
+    allreduce_algo: str = "auto"        # auto | oneshot | twoshot | nccl
+    bucket_cap_mb: float = 25.0         # torch DDP default (distributed.py:831-833)
+    first_bucket_mb: float = 1.0
+    comm_ctas: int = 32                 # CTAs a communication kernel may occupy
+    fuse_optimizer: bool = True
+    wait_timeout_s: float = 30.0        # device-side flag waits give up after this long
+    checkpoint_path: str = "checkpoint.pt"   # multigpu.py:111
+    metrics_jsonl: str = ""
+
+    @staticmethod
+    def from_env() -> "RuntimeConfig":
+        c = RuntimeConfig()
+        c.master_addr = _env_str("DDPX_MASTER_ADDR", c.master_addr)
+        c.master_port = _env_int("DDPX_MASTER_PORT", c.master_port)
+        c.backend = _env_str("DDPX_BACKEND", c.backend)
+        c.allreduce_algo = _env_str("DDPX_ALLREDUCE_ALGO", c.allreduce_algo)
+        c.bucket_cap_mb = float(_env_str("DDPX_BUCKET_CAP_MB", str(c.bucket_cap_mb)))
+        c.comm_ctas = _env_int("DDPX_COMM_CTAS", c.comm_ctas)
+        c.fuse_optimizer = _env_int("DDPX_FUSE_OPTIMIZER", 1) == 1
+        c.wait_timeout_s = float(_env_str("DDPX_WAIT_TIMEOUT_S", str(c.wait_timeout_s)))
+        c.checkpoint_path = _env_str("DDPX_CHECKPOINT_PATH", c.checkpoint_path)
+        c.metrics_jsonl = _env_str("DDPX_METRICS_JSONL", c.metrics_jsonl)
+        return c
+
+
+_cfg: RuntimeConfig | None = None
+
+
+def get() -> RuntimeConfig:
+    global _cfg
+    if _cfg is None:
+        _cfg = RuntimeConfig.from_env()
+    return _cfg
+
+
+def reset() -> None:
+    global _cfg
+    _cfg = None

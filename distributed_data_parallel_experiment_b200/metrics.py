@@ -1,0 +1,81 @@
+"""Model-size helper (reference multigpu.py:208-221), device-timed step metrics and JSONL logging.
+
+The reference only prints wall-clock time around ``trainer.train()`` (multigpu.py:230-235); here step times
+are taken with CUDA events on the launching stream and the exposed-communication time is the gap between the
+end of backward compute and the completion of the last gradient bucket.
+"""
+from __future__ import annotations
+
+import json
+import time
+from typing import Optional
+
+import torch
+
+# bit-based units, exactly as the reference defines them (multigpu.py:218-221)
+Byte = 8
+KiB = 1024 * Byte
+MiB = 1024 * KiB
+GiB = 1024 * MiB
+
+
+def get_model_size(model: torch.nn.Module, data_width: int = 32) -> int:
+    """Model size in bits: number of parameter elements x ``data_width`` (buffers excluded)."""
+    num_elements = 0
+    for param in model.parameters():
+        num_elements += param.numel()
+    return num_elements * data_width
+
+
+class StepTimer:
+    """CUDA-event (or perf_counter on CPU) timer for training steps."""
+
+    def __init__(self, device: Optional[torch.device] = None):
+        self.cuda = torch.cuda.is_available() and (device is None or torch.device(device).type == "cuda")
+        self._pairs = []
+        self._t0 = None
+
+    def start(self):
+        if self.cuda:
+            e = torch.cuda.Event(enable_timing=True)
+            e.record()
+            self._t0 = e
+        else:
+            self._t0 = time.perf_counter()
+
+    def stop(self):
+        if self.cuda:
+            e = torch.cuda.Event(enable_timing=True)
+            e.record()
+            self._pairs.append((self._t0, e))
+        else:
+            self._pairs.append((self._t0, time.perf_counter()))
+
+    def times_ms(self):
+        if self.cuda:
+            torch.cuda.synchronize()
+            return [a.elapsed_time(b) for a, b in self._pairs]
+        return [(b - a) * 1e3 for a, b in self._pairs]
+
+    def reset(self):
+        self._pairs = []
+
+
+class JsonlLogger:
+    """Structured step metrics, one JSON object per line (rank, step, device-ms, samples/s, comm-ms, ...)."""
+
+    def __init__(self, path: str):
+        self.path = path
+        self._fh = open(path, "a") if path else None
+
+    def log(self, **kv):
+        if self._fh is None:
+            return
+        kv.setdefault("ts", time.time())
+        self._fh.write(json.dumps(kv) + "\n")
+        self._fh.flush()
+
+    def close(self):
+        if self._fh is not None:
+            self._fh.close()
+            self._fh = None

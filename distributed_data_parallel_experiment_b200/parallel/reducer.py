@@ -1,0 +1,222 @@
+"""Gradient reducer: buckets, autograd hooks, in-order launch, finalisation, one-time rebuild, ``no_sync``.
+
+Counterpart of ``c10d::Reducer`` (c10d/reducer.hpp:45-584) that torch DDP builds for the reference at multigpu.py:89.
+Bookkeeping (ready counting, strict bucket order, ready-order recording) is the C++ core in
+csrc/runtime/reducer_core.cpp; this file owns the tensors:
+
+* every bucket is ONE flat buffer from the communication backend (peer-mapped symmetric memory on the P2P backend),
+  double-buffered by step parity so a fast rank can start filling step t+1 while a slow peer still reads step t;
+* a post-accumulate-grad hook per parameter copies the gradient into its bucket slot pre-divided by the world size
+  (one small kernel) and asks the core which buckets became launchable;
+* launchable buckets are handed to the backend immediately (overlapping the rest of backward); the last one queues a
+  finalisation callback on the autograd engine that waits for the collectives and points ``param.grad`` at the bucket
+  (no copy back), or - on the fused path - lets the all-reduce kernel apply the optimizer update itself.
+"""
+from __future__ import annotations
+
+import ctypes
+from typing import List, Optional, Sequence
+
+import torch
+
+from .. import _lib
+from .buckets import DEFAULT_FIRST_BUCKET_BYTES, compute_bucket_assignment_by_size
+
+
+class Bucket:
+    __slots__ = ("index", "param_ids", "offsets", "numel", "dtype", "buffers", "views", "handle", "size_bytes")
+
+    def __init__(self, index, param_ids, params, comm, device, double_buffer):
+        self.index = index
+        self.param_ids = list(param_ids)
+        self.offsets = []
+        off = 0
+        for pid in self.param_ids:
+            self.offsets.append(off)
+            n = params[pid].numel()
+            off += (n + 3) // 4 * 4          # keep every slot 16-byte aligned for vector loads
+        self.numel = max(off, 4)
+        self.dtype = params[self.param_ids[0]].dtype
+        self.size_bytes = sum(params[p].numel() * params[p].element_size() for p in self.param_ids)
+        nbuf = 2 if double_buffer else 1
+        self.buffers = [comm.alloc(self.numel, self.dtype, device) for _ in range(nbuf)]
+        self.views = [[buf[o:o + params[pid].numel()].view_as(params[pid]) for pid, o in zip(self.param_ids, self.offsets)]
+                      for buf in self.buffers]
+        self.handle = None
+
+
+class Reducer:
+    def __init__(self, params: Sequence[torch.nn.Parameter], comm, bucket_cap_bytes: int,
+                 first_bucket_bytes: int = DEFAULT_FIRST_BUCKET_BYTES, fused=None):
+        self.params = list(params)
+        self.comm = comm
+        self.world_size = comm.world_size
+        self.bucket_cap_bytes = int(bucket_cap_bytes)
+        self.first_bucket_bytes = int(first_bucket_bytes)
+        self.device = self.params[0].device if self.params else torch.device("cpu")
+        self.fused = fused                      # FusedUpdate object (parallel/p2p.py) or None
+        self.double_buffer = getattr(comm, "needs_double_buffer", False)
+        self._lib = _lib.lib()
+        self._core = None
+        self.buckets: List[Bucket] = []
+        self.armed = False                      # prepare_for_backward() called and not yet finalised
+        self.expect_finalize = False
+        self.has_rebuilt = False
+        self.iteration = 0
+        self.step_parity = 0
+        self._pid_of = {id(p): i for i, p in enumerate(self.params)}
+        self._slot = {}                         # param id -> (bucket, slot)
+        self._hooks = []
+        self._callback_queued = False
+        self._scratch = (ctypes.c_int * max(1, len(self.params)))()
+        self.stats = {"rebuilt_bucket_sizes": [], "num_buckets": 0, "launched": 0}
+        # first iteration: one bucket holding everything (distributed.py:1224-1225, find_unused_parameters=False)
+        idx, _ = compute_bucket_assignment_by_size(self.params, [2 ** 62])
+        self._install(list(reversed(idx)))
+        for i, p in enumerate(self.params):
+            self._hooks.append(p.register_post_accumulate_grad_hook(self._make_hook(i)))
+
+    # ------------------------------------------------------------------------------------------ structure
+    def _install(self, bucket_indices: List[List[int]]):
+        if self._core is not None:
+            self._lib.ddpx_reducer_destroy(ctypes.c_void_p(self._core))
+            self._core = None
+        old = self.buckets
+        self.buckets = [Bucket(b, ids, self.params, self.comm, self.device, self.double_buffer)
+                        for b, ids in enumerate(bucket_indices)]
+        del old
+        n = len(self.params)
+        bof = (ctypes.c_int * max(1, n))()
+        self._slot = {}
+        for b in self.buckets:
+            for s, pid in enumerate(b.param_ids):
+                bof[pid] = b.index
+                self._slot[pid] = (b, s)
+        self._lib.ddpx_reducer_create.restype = ctypes.c_void_p
+        self._core = self._lib.ddpx_reducer_create(n, len(self.buckets), bof)
+        if not self._core:
+            raise RuntimeError("ddpx_reducer_create failed")
+        self.stats["num_buckets"] = len(self.buckets)
+        if self.fused is not None:
+            self.fused.on_buckets_installed(self)
+
+    def bucket_sizes(self) -> List[int]:
+        return [b.size_bytes for b in self.buckets]
+
+    def rebuild_buckets(self) -> bool:
+        """One-time rebuild in the gradient-ready order observed during the first backward (reducer.hpp:136,466),
+        rank 0's order wins (sync_bucket_indices, reducer.hpp:301).  Returns True if a rebuild happened."""
+        if self.has_rebuilt or self.iteration == 0:
+            return False
+        n = len(self.params)
+        cnt = self._lib.ddpx_reducer_ready_order(ctypes.c_void_p(self._core), self._scratch, n)
+        order = [self._scratch[i] for i in range(min(cnt, n))]
+        if len(order) != n:
+            return False
+        order = self.comm.broadcast_object(order, src=0)
+        tensors = [self.params[i] for i in order]
+        idx, _ = compute_bucket_assignment_by_size(tensors, [self.first_bucket_bytes, self.bucket_cap_bytes],
+                                                   tensor_indices=order)
+        self._install(idx)
+        self.has_rebuilt = True
+        self.stats["rebuilt_bucket_sizes"] = self.bucket_sizes()
+        return True
+
+    # ------------------------------------------------------------------------------------------ per iteration
+    def prepare_for_backward(self):
+        if self.expect_finalize:
+            missing = self._unmarked()
+            raise RuntimeError(
+                "Expected to have finished reduction in the prior iteration before starting a new one. "
+                f"Parameters that did not receive a gradient: {missing} (find_unused_parameters is not supported)")
+        self._lib.ddpx_reducer_reset(ctypes.c_void_p(self._core))
+        self.armed = True
+        self.expect_finalize = True
+        self._callback_queued = False
+        for b in self.buckets:
+            b.handle = None
+
+    def _unmarked(self):
+        n = len(self.params)
+        cnt = self._lib.ddpx_reducer_unmarked(ctypes.c_void_p(self._core), self._scratch, n)
+        return [self._scratch[i] for i in range(min(cnt, n))]
+
+    def _make_hook(self, pid: int):
+        def hook(param):
+            if not self.armed:
+                return            # no_sync(): gradients just accumulate in param.grad
+            self._on_grad_ready(pid, param)
+        return hook
+
+    def _on_grad_ready(self, pid: int, param):
+        bucket, slot = self._slot[pid]
+        view = bucket.views[self.step_parity if self.double_buffer else 0][slot]
+        g = param.grad
+        if g is None:
+            raise RuntimeError("gradient hook fired without a gradient")
+        scale = 1.0 / self.world_size
+        if g.data_ptr() != view.data_ptr():
+            _scaled_copy(view, g, scale)
+        elif scale != 1.0:
+            _scaled_copy(view, view, scale)
+        out = self._scratch
+        k = self._lib.ddpx_reducer_mark_ready(ctypes.c_void_p(self._core), pid, out, len(self.params))
+        if k == -1:
+            raise RuntimeError(f"parameter {pid} was marked ready twice in one iteration (reducer.hpp:559-568)")
+        if k < 0:
+            raise RuntimeError("reducer: bad parameter index")
+        for j in range(k):
+            self._launch(self.buckets[out[j]])
+        if k > 0 and self._lib.ddpx_reducer_all_launched(ctypes.c_void_p(self._core)) and not self._callback_queued:
+            self._callback_queued = True
+            torch.autograd.Variable._execution_engine.queue_callback(self.finalize_backward)
+
+    def _launch(self, bucket: Bucket):
+        buf = bucket.buffers[self.step_parity if self.double_buffer else 0]
+        self.stats["launched"] += 1
+        if self.fused is not None:
+            bucket.handle = self.fused.reduce_and_update(bucket, buf, self.step_parity)
+        else:
+            bucket.handle = self.comm.all_reduce_sum_(buf, async_op=True)
+
+    def finalize_backward(self):
+        parity = self.step_parity if self.double_buffer else 0
+        for b in self.buckets:
+            if b.handle is not None:
+                b.handle.wait()
+                b.handle = None
+            if self.fused is None:
+                for pid, v in zip(b.param_ids, b.views[parity]):
+                    self.params[pid].grad = v          # averaged gradient lives in the bucket (no copy back)
+        if self.fused is not None:
+            self.fused.after_backward(self)
+        self.armed = False
+        self.expect_finalize = False
+        self.iteration += 1
+        if self.double_buffer:
+            self.step_parity ^= 1
+
+    def close(self):
+        for h in self._hooks:
+            h.remove()
+        self._hooks = []
+        if self._core is not None:
+            self._lib.ddpx_reducer_destroy(ctypes.c_void_p(self._core))
+            self._core = None
+
+
+def _scaled_copy(dst: torch.Tensor, src: torch.Tensor, scale: float):
+    """dst = src * scale with the framework's own kernel on CUDA fp32; torch math elsewhere."""
+    if dst.is_cuda and dst.dtype == torch.float32 and src.dtype == torch.float32 and src.is_contiguous():
+        from ..ops import native
+        native.scale_copy(src, dst, dst.numel(), scale, 0)
+    elif dst.is_cuda and src.is_contiguous() and dst.dtype == src.dtype and dst.dtype == torch.bfloat16:
+        from ..ops import native
+        native.scale_copy_bf16(src, dst, dst.numel(), scale)
+    else:
+        if dst.data_ptr() == src.data_ptr():
+            dst.mul_(scale)
+        else:
+            dst.copy_(src)
+            if scale != 1.0:
+                dst.mul_(scale)

@@ -1,0 +1,151 @@
+"""``Trainer`` - the framework's public training loop, same surface as the reference's (multigpu.py:74-119,
+singlegpu.py:85-128):
+
+    Trainer(model, train_data, optimizer, gpu_id, save_every[, scheduler]).train(max_epochs)
+
+Differences, all supersets: ``scheduler`` is optional (the upstream tutorial's 5-argument form works), the loss is
+pluggable (cross-entropy default, MSE for the toy regressor), the data-parallel wrapper is chosen from the process
+group (none when single process), and ``train_step`` is the end-to-end public call (pinned host batch in, host loss
+out).  Print lines, save cadence (``epoch % save_every == 0``, rank 0 only, ``checkpoint.pt``) and the per-batch
+``scheduler.step()`` are the reference's.
+"""
+from __future__ import annotations
+
+from typing import Callable, Optional, Union
+
+import torch
+import torch.distributed as dist
+
+from . import checkpoint, config, ops, optim as _optim
+from .parallel import DataParallel
+
+
+def _resolve_loss(loss_fn: Union[str, Callable, None]) -> Callable:
+    if loss_fn is None or loss_fn == "cross_entropy":
+        return ops.cross_entropy
+    if loss_fn == "mse":
+        return ops.mse_loss
+    if callable(loss_fn):
+        return loss_fn
+    raise ValueError(f"unknown loss {loss_fn!r}")
+
+
+class Trainer:
+    def __init__(
+        self,
+        model: torch.nn.Module,
+        train_data,
+        optimizer: torch.optim.Optimizer,
+        gpu_id: int,
+        save_every: int,
+        scheduler=None,
+        loss_fn: Union[str, Callable, None] = None,
+        distributed: Optional[bool] = None,
+        accum_steps: int = 1,
+        checkpoint_path: Optional[str] = None,
+    ) -> None:
+        self.gpu_id = gpu_id
+        self.device = torch.device("cuda", gpu_id) if torch.cuda.is_available() and gpu_id is not None and gpu_id >= 0 \
+            and _model_wants_cuda(model) else torch.device("cpu")
+        self.model = model.to(self.device)
+        self.train_data = train_data
+        self.optimizer = optimizer
+        self.save_every = save_every
+        self.scheduler = scheduler
+        self.loss_fn = _resolve_loss(loss_fn)
+        self.accum_steps = max(1, int(accum_steps))
+        self.checkpoint_path = checkpoint_path or config.get().checkpoint_path
+        self._micro = 0
+        self.last_loss = None
+        if distributed is None:
+            distributed = dist.is_available() and dist.is_initialized()
+        self.distributed = distributed
+        if self.device.type == "cuda":
+            _optim.fuse(self.optimizer)            # optimizer.step() -> one native multi-tensor kernel
+        if distributed:
+            # multigpu.py:89 - wrap; the optimizer was built on the raw module's parameters and keeps working
+            self.model = DataParallel(self.model, device_ids=[gpu_id] if self.device.type == "cuda" else None,
+                                      optimizer=self.optimizer)
+
+    # ------------------------------------------------------------------------------------------ one step
+    def _run_batch(self, source, targets):
+        """zero_grad -> forward -> loss -> backward -> optimizer.step -> scheduler.step (multigpu.py:92-98), with
+        optional gradient accumulation over ``accum_steps`` micro-batches under ``no_sync``."""
+        last = (self._micro + 1) % self.accum_steps == 0
+        if self._micro % self.accum_steps == 0:
+            self.optimizer.zero_grad()
+        if self.distributed and not last:
+            with self.model.no_sync():
+                loss = self._forward_backward(source, targets)
+        else:
+            loss = self._forward_backward(source, targets)
+        self._micro += 1
+        if last:
+            self.optimizer.step()
+            if self.scheduler is not None:
+                self.scheduler.step()
+        self.last_loss = loss
+        return loss
+
+    def _forward_backward(self, source, targets):
+        output = self.model(source)
+        loss = self.loss_fn(output, targets)
+        if self.accum_steps > 1:
+            (loss / self.accum_steps).backward()
+        else:
+            loss.backward()
+        return loss.detach()
+
+    def train_step(self, source: torch.Tensor, targets: torch.Tensor) -> float:
+        """End-to-end step: copy the (pinned) host batch to the device, run the step, read the loss back."""
+        source = source.to(self.device, non_blocking=True)
+        targets = targets.to(self.device, non_blocking=True)
+        loss = self._run_batch(source, targets)
+        return float(loss.item())
+
+    # ------------------------------------------------------------------------------------------ epochs
+    def _run_epoch(self, epoch):
+        b_sz = _batch_size_of(self.train_data)
+        print(f"[GPU{self.gpu_id}] Epoch {epoch} | Batchsize: {b_sz} | Steps: {len(self.train_data)}")
+        sampler = getattr(self.train_data, "sampler", None)
+        if self.distributed and hasattr(sampler, "set_epoch"):
+            sampler.set_epoch(epoch)                     # multigpu.py:103
+        for source, targets in self.train_data:
+            source = source.to(self.device, non_blocking=True)
+            targets = targets.to(self.device, non_blocking=True)
+            self._run_batch(source, targets)
+
+    def _save_checkpoint(self, epoch):
+        PATH = self.checkpoint_path
+        checkpoint.save_checkpoint(self.model, PATH)     # unwrapped module's state_dict, torch.save (multigpu.py:110-112)
+        print(f"Epoch {epoch} | Training checkpoint saved at {PATH}")
+
+    def train(self, max_epochs: int):
+        for epoch in range(max_epochs):
+            self._run_epoch(epoch)
+            # multigpu.py:118 gates on gpu_id == 0 (rank 0); singlegpu.py:127 saves unconditionally
+            if (not self.distributed or self.gpu_id == 0) and epoch % self.save_every == 0:
+                self._save_checkpoint(epoch)
+
+
+def _model_wants_cuda(model) -> bool:
+    """CPU/gloo runs (BASELINE.json config #1) pass a rank as ``gpu_id`` on a host that may also have GPUs; keep the model
+    where the process group lives."""
+    if dist.is_available() and dist.is_initialized():
+        from . import launch
+        be = launch.backend()
+        if be == "gloo":
+            return False
+    return True
+
+
+def _batch_size_of(loader):
+    """The reference prints ``len(next(iter(train_data))[0])`` - which loads and discards a whole batch
+    (multigpu.py:101); read the configured size instead and only fall back to a probe when it is unknown."""
+    bs = getattr(loader, "batch_size", None)
+    if bs is not None:
+        return bs
+    try:
+        return len(next(iter(loader))[0])
+    except Exception:
+        return 0

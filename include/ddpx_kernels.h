@@ -1,0 +1,125 @@
+/* C ABI of libddpx_kernels.so — hand-written sm_100a kernels (no cuBLAS / cuDNN / NCCL inside).
+ *
+ * Every entry point takes raw device pointers plus a CUDA stream (as void*) and returns a DDPX_* code;
+ * nothing here allocates unless the comment says so. Python reaches these through ctypes
+ * (distributed_data_parallel_experiment_b200/_lib.py).
+ *
+ * Reference parity citations are to /root/reference/multigpu.py (M:) and singlegpu.py (S:).
+ */
+#ifndef DDPX_KERNELS_H_
+#define DDPX_KERNELS_H_
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+enum {
+  DDPX_OK = 0,
+  DDPX_ERR_ARG = 1,     /* invalid argument combination */
+  DDPX_ERR_ALIGN = 2,   /* pointer / leading dimension not 16-byte aligned */
+  DDPX_ERR_SHAPE = 3,   /* shape outside what the kernel tiles */
+  DDPX_ERR_DRIVER = 4,  /* driver entry point unavailable */
+  DDPX_ERR_TMAP = 5,    /* cuTensorMapEncodeTiled rejected the descriptor */
+  DDPX_ERR_LAUNCH = 6,  /* kernel launch failed */
+  DDPX_ERR_LIMIT = 7    /* size beyond a stated maximum */
+};
+
+/* ---- tcgen05 / TMEM / TMA GEMM --------------------------------------------------------------
+ * D[M,N] (=|+=) op(A) * op(B), fp32 accumulation in TMEM.
+ *   a_mn = 0: A stored [M][K] (K contiguous, ld = lda)   a_mn = 1: A stored [K][M] (M contiguous)
+ *   b_mn = 0: B stored [N][K] (K contiguous, ld = ldb)   b_mn = 1: B stored [K][N] (N contiguous)
+ *   bf16 = 0: operands fp32 in memory, multiplied as TF32 (what cuDNN/cuBLAS-TF32 do for fp32 tensors)
+ *   bf16 = 1: operands bf16.   out_bf16 selects the output type.  bias is per output column (fp32).
+ *   act: 0 none, 1 ReLU, 2 GELU(tanh).  split_k > 1 or accumulate != 0 -> fp32 atomics into D.
+ * Replaces cuBLAS behind nn.Linear (M:62, S:36-41) and the MLP / GPT-2 GEMMs of BASELINE.json. */
+int ddpx_gemm(const void* A, const void* B, void* D, int M, int N, int K, long long lda, long long ldb,
+              long long ldd, int a_mn, int b_mn, int bf16, int out_bf16, const float* bias, int act,
+              int split_k, int accumulate, void* stream);
+
+/* ---- 3x3 / stride 1 / pad 1 convolution, NHWC fp32, TF32 tensor cores (M:53) ----------------
+ * fprop: y[N,H,W,Cout] = conv(x[N,H,W,Cin], wpacked[9][Cout][Cin]) (+bias[Cout]) (+ReLU);
+ *        optionally accumulates per-channel sum / sum-of-squares of the pre-activation output into
+ *        stat_sum / stat_sq (BatchNorm batch statistics fused into the conv epilogue; pre-zeroed).
+ *        The data gradient is the same call with tap-flipped, transposed weights (see ddpx_pack_conv_weights).
+ * wgrad: dw[Cout][Cin][3][3] += sum_pixels dy (x) shifted x   (torch layout, fp32 atomics; pre-zeroed or
+ *        already holding a gradient to accumulate into). */
+int ddpx_conv3x3_fprop(const float* x, const float* wpacked, float* y, int Nimg, int H, int W, int Cin, int Cout,
+                       const float* bias, int act, float* stat_sum, float* stat_sq, void* stream);
+int ddpx_conv3x3_wgrad(const float* dy, const float* x, float* dw, int Nimg, int H, int W, int Cin, int Cout,
+                       int split_k, void* stream);
+
+
+/* ---- convolution helpers (csrc/kernels/conv_aux.cu) ---------------------------------------- */
+/* torch-layout weights [Cout][Cin][3][3] -> w_fprop [tap][Cout][Cin] and/or w_dgrad [8-tap][Cin][Cout] (either may be NULL) */
+int ddpx_pack_conv_weights(const float* w, float* w_fprop, float* w_dgrad, int Cout, int Cin, void* stream);
+/* RGB stem (Cin == 3, K = 27): direct conv, NCHW input -> NHWC output, optional bias / ReLU / BN statistics (M:53 conv0) */
+int ddpx_conv_stem_fprop(const float* x_nchw, const float* w, const float* bias, float* y_nhwc, int Nimg, int H, int W,
+                         int Cout, int act, float* stat_sum, float* stat_sq, void* stream);
+int ddpx_conv_stem_wgrad(const float* dy_nhwc, const float* x_nchw, float* dw, int Nimg, int H, int W, int Cout, void* stream);
+/* [batch][rows][cols] -> [batch][cols][rows] (NCHW <-> NHWC) */
+int ddpx_transpose_batched(const float* in, float* out, int batch, int rows, int cols, void* stream);
+int ddpx_relu_fwd(const float* x, float* y, long long n, void* stream);
+int ddpx_relu_bwd(const float* y, const float* dy, float* dx, long long n, void* stream);
+int ddpx_maxpool2x2_fwd(const float* x, float* y, int Nimg, int H, int W, int C, void* stream);           /* NHWC, M:59 */
+int ddpx_maxpool2x2_bwd(const float* x, const float* dy, float* dx, int Nimg, int H, int W, int C, void* stream);
+int ddpx_spatial_mean_fwd(const float* x, float* y, int Nimg, int HW, int C, void* stream);               /* M:68 */
+int ddpx_spatial_mean_bwd(const float* dy, float* dx, int Nimg, int HW, int C, void* stream);
+int ddpx_colsum(const float* x, float* out, long long rows, int cols, int accumulate, void* stream);      /* bias grads */
+int ddpx_scale_copy(const float* src, float* dst, long long n, float scale, int accumulate, void* stream);
+int ddpx_zero(void* p, long long bytes, void* stream);
+/* CUDA-core fp32 GEMM for shapes TMA cannot describe (row pitch not a multiple of 16 B): classifier Linear(512,10) at
+ * M:62, toy Linear(20,1).  C[m][n] = act(sum_k A[m*sam+k*sak] * B[n*sbn+k*sbk] + bias[n]) (+C). */
+int ddpx_gemm_small(const float* A, const float* B, float* C, int M, int N, int K, long long sam, long long sak,
+                    long long sbn, long long sbk, long long ldc, const float* bias, int act, int accumulate, void* stream);
+
+/* ---- BatchNorm2d (+ReLU, +2x2 max-pool) on NHWC fp32 (csrc/kernels/batchnorm.cu; M:54-59) -- */
+int ddpx_bn_finalize(const float* sum, const float* sq, float count, float* mean, float* rstd, float* running_mean,
+                     float* running_var, long long* num_batches_tracked, float momentum, float eps, int C, void* stream);
+int ddpx_bn_eval_stats(const float* running_mean, const float* running_var, float eps, float* mean, float* rstd, int C,
+                       void* stream);
+int ddpx_bn_stats(const float* x, long long P, int C, float* sum, float* sq, void* stream);
+int ddpx_bn_apply(const float* x, float* y, const float* mean, const float* rstd, const float* gamma, const float* beta,
+                  int Nimg, int H, int W, int C, int relu, int pool, void* stream);
+int ddpx_bn_bwd_reduce(const float* x, const float* dout, const float* mean, const float* rstd, const float* gamma,
+                       const float* beta, int Nimg, int H, int W, int C, int relu, int pool, float* sum_dz, float* sum_dzx,
+                       void* stream);
+int ddpx_bn_bwd_apply(const float* x, const float* dout, const float* mean, const float* rstd, const float* gamma,
+                      const float* beta, const float* sum_dz, const float* sum_dzx, int Nimg, int H, int W, int C, int relu,
+                      int pool, int use_batch_stats, float* dx, void* stream);
+
+/* ---- losses and optimizers (csrc/kernels/loss_optim.cu) ------------------------------------ */
+/* softmax cross-entropy fwd+bwd fused (M:95): loss_sum[0] = mean NLL, dlogits = (softmax - onehot) * grad_scale / rows */
+int ddpx_softmax_ce(const void* logits, const long long* targets, void* dlogits, float* loss_sum, long long rows, int cols,
+                    long long ld, int bf16, long long ignore_index, float grad_scale, void* stream);
+int ddpx_scale_by_device_scalar(void* p, long long n, const float* g, int bf16, void* stream);
+int ddpx_mse(const float* pred, const float* target, float* dpred, float* loss_sum, long long n, void* stream);
+/* one launch for all tensors; torch SGD / AdamW semantics (M:97, torch/optim/sgd.py:346-380) */
+int ddpx_sgd_multi(int n, void* const* params, void* const* grads, void* const* momentum_bufs, const long long* numel,
+                   float lr, float momentum, float dampening, float weight_decay, int nesterov, int first_step,
+                   float grad_scale, void* stream);
+int ddpx_adamw_multi(int n, void* const* params, void* const* grads, void* const* exp_avg, void* const* exp_avg_sq,
+                     const long long* numel, float lr, float beta1, float beta2, float eps, float weight_decay,
+                     long long step, float grad_scale, void* stream);
+
+/* ---- reducer core (csrc/runtime/reducer_core.cpp): host-side bucket assignment + ready/launch state machine ----
+ * Counterpart of c10d::compute_bucket_assignment_by_size and the bookkeeping of c10d::Reducer that torch DDP builds
+ * for the reference at M:89. */
+int ddpx_bucket_assign(int n, const long long* nbytes, const int* keys, int nlimits, const long long* limits,
+                       int sort_by_min_position, int* out_bucket_of_position, long long* out_bucket_limit,
+                       int* out_num_buckets);
+void* ddpx_reducer_create(int n_params, int n_buckets, const int* bucket_of_param);
+void ddpx_reducer_destroy(void* h);
+void ddpx_reducer_reset(void* h);
+int ddpx_reducer_mark_ready(void* h, int param, int* out_buckets, int max_out);
+int ddpx_reducer_all_launched(void* h);
+int ddpx_reducer_num_marked(void* h);
+int ddpx_reducer_ready_order(void* h, int* out, int max_out);
+int ddpx_reducer_unmarked(void* h, int* out, int max_out);
+
+/* Last device-side error code written by a bounded wait that expired (0 = none). Synchronises. */
+unsigned int ddpx_read_error_word(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DDPX_KERNELS_H_ */

@@ -1,0 +1,136 @@
+"""T0: LR schedule values, model size, unit constants, CLI parsing, Trainer save cadence / argument forms."""
+import os
+import subprocess
+import sys
+from pathlib import Path
+
+import numpy as np
+import pytest
+import torch
+
+import distributed_data_parallel_experiment_b200 as ddpx
+from distributed_data_parallel_experiment_b200 import recipes
+from distributed_data_parallel_experiment_b200.models import VGG, DeepNN, ToyLinear
+
+REPO = Path(__file__).resolve().parent.parent
+
+
+def test_lr_schedule_values():
+    o = recipes.vgg_train_objs(world_size=2, synthetic=True, device=torch.device("cpu"), synthetic_size=0)
+    lr0 = o.optimizer.param_groups[0]["lr"]
+    assert float(lr0) == 0.0                      # LambdaLR ctor performs the initial step: first batch has lr 0
+    lam = recipes.triangular_lr_lambda(49, 20)
+    assert lam(0) == 0.0
+    assert abs(lam(6 * 49) - 1.0) < 1e-12         # peak 0.4 at epoch 6
+    assert lam(20 * 49) == 0.0 and lam(25 * 49) == 0.0
+    assert abs(0.4 * lam(3 * 49) - 0.2) < 1e-12
+    o1 = recipes.vgg_train_objs(world_size=1, synthetic=True, device=torch.device("cpu"), synthetic_size=0)
+    for _ in range(98 * 6):
+        o1.optimizer.step(); o1.scheduler.step()
+    assert abs(o1.optimizer.param_groups[0]["lr"] - 0.4) < 1e-9
+
+
+def test_model_size_and_units():
+    m = VGG()
+    assert sum(p.numel() for p in m.parameters()) == 9228362
+    assert ddpx.get_model_size(m) == 9228362 * 32
+    assert f"{ddpx.get_model_size(m) / ddpx.MiB:.2f}" == "35.20"
+    assert ddpx.Byte == 8 and ddpx.KiB == 8192 and ddpx.GiB == 1024 * ddpx.MiB
+    assert sum(p.numel() for p in DeepNN().parameters()) == 1186986
+    assert len(list(m.buffers())) == 24
+
+
+def test_vgg_shapes_cpu():
+    m = VGG()
+    y = m(torch.randn(2, 3, 32, 32))
+    assert y.shape == (2, 10)
+    assert DeepNN()(torch.randn(2, 3, 32, 32)).shape == (2, 10)
+
+
+class _Loader(list):
+    batch_size = 4
+
+
+def _toy_loader(n=3):
+    g = torch.Generator().manual_seed(0)
+    return _Loader([(torch.rand(4, 20, generator=g), torch.rand(4, 1, generator=g)) for _ in range(n)])
+
+
+def test_trainer_five_arg_form_and_save_cadence(tmp_path, monkeypatch, capsys):
+    monkeypatch.chdir(tmp_path)
+    model = ToyLinear()
+    opt = torch.optim.SGD(model.parameters(), lr=1e-2)
+    t = ddpx.Trainer(model, _toy_loader(), opt, 0, 2, loss_fn="mse", distributed=False)   # scheduler omitted
+    saved = []
+    orig = t._save_checkpoint
+    t._save_checkpoint = lambda e: (saved.append(e), orig(e))
+    t.train(5)
+    assert saved == [0, 2, 4]                       # epoch % save_every == 0, including epoch 0
+    assert (tmp_path / "checkpoint.pt").exists()
+    out = capsys.readouterr().out
+    assert "[GPU0] Epoch 0 | Batchsize: 4 | Steps: 3" in out
+    assert "Epoch 4 | Training checkpoint saved at checkpoint.pt" in out
+
+
+def test_trainer_save_every_zero_raises(tmp_path, monkeypatch):
+    monkeypatch.chdir(tmp_path)
+    model = ToyLinear()
+    t = ddpx.Trainer(model, _toy_loader(), torch.optim.SGD(model.parameters(), lr=1e-2), 0, 0, loss_fn="mse", distributed=False)
+    with pytest.raises(ZeroDivisionError):
+        t.train(1)
+
+
+def test_trainer_scheduler_stepped_per_batch():
+    model = ToyLinear()
+    opt = torch.optim.SGD(model.parameters(), lr=1.0)
+    sched = torch.optim.lr_scheduler.LambdaLR(opt, lambda s: 1.0 / (1 + s))
+    t = ddpx.Trainer(model, _toy_loader(3), opt, 0, 1, scheduler=sched, loss_fn="mse", distributed=False)
+    t._run_epoch(0)
+    assert sched.last_epoch == 3
+
+
+def test_trainer_loss_decreases_toy():
+    torch.manual_seed(0)
+    model = ToyLinear()
+    opt = torch.optim.SGD(model.parameters(), lr=0.05)
+    t = ddpx.Trainer(model, _toy_loader(8), opt, 0, 100, loss_fn="mse", distributed=False)
+    t._run_epoch(0)
+    first = float(t.last_loss)
+    for e in range(30):
+        for x, y in t.train_data:
+            t._run_batch(x, y)
+    assert float(t.last_loss) < first
+
+
+def test_gradient_accumulation_matches_big_batch():
+    torch.manual_seed(0)
+    a, b = ToyLinear(), ToyLinear()
+    b.load_state_dict(a.state_dict())
+    xs = torch.rand(8, 20); ys = torch.rand(8, 1)
+    ta = ddpx.Trainer(a, [], torch.optim.SGD(a.parameters(), lr=0.1), 0, 1, loss_fn="mse", distributed=False)
+    tb = ddpx.Trainer(b, [], torch.optim.SGD(b.parameters(), lr=0.1), 0, 1, loss_fn="mse", distributed=False, accum_steps=2)
+    ta._run_batch(xs, ys)
+    tb._run_batch(xs[:4], ys[:4]); tb._run_batch(xs[4:], ys[4:])
+    for p, q in zip(a.parameters(), b.parameters()):
+        assert torch.allclose(p, q, atol=1e-6)
+
+
+@pytest.mark.parametrize("script", ["multigpu.py", "singlegpu.py"])
+def test_cli_help_matches_reference_surface(script):
+    r = subprocess.run([sys.executable, str(REPO / script), "--help"], capture_output=True, text=True, timeout=120)
+    assert r.returncode == 0
+    assert "total_epochs" in r.stdout and "save_every" in r.stdout and "--batch_size" in r.stdout
+    assert "simple distributed training job" in r.stdout
+
+
+def test_cli_requires_positionals():
+    r = subprocess.run([sys.executable, str(REPO / "singlegpu.py")], capture_output=True, text=True, timeout=120)
+    assert r.returncode != 0 and "total_epochs" in r.stderr
+
+
+def test_datautils_toy_dataset():
+    sys.path.insert(0, str(REPO))
+    from datautils import MyTrainDataset
+    ds = MyTrainDataset(2048)
+    x, y = ds[5]
+    assert len(ds) == 2048 and x.shape == (20,) and y.shape == (1,)
