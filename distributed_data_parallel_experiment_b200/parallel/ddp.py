@@ -40,6 +40,8 @@ class DataParallel(nn.Module):
         cfg = config.get()
         cap_mb = cfg.bucket_cap_mb if bucket_cap_mb is None else bucket_cap_mb
         self.bucket_bytes_cap = int(cap_mb * 1024 * 1024)
+        # torch: the 1 MiB first-bucket cap applies only with the default bucket_cap_mb (distributed.py:1255-1280)
+        self._first_bucket_bytes = int(cfg.first_bucket_mb * 1024 * 1024) if bucket_cap_mb is None else self.bucket_bytes_cap
         if comm is None:
             from .. import launch
             comm = launch.get_comm()
@@ -64,7 +66,7 @@ class DataParallel(nn.Module):
         if init_sync:
             self._sync_module_states()
         self.reducer = Reducer(self._params, comm, self.bucket_bytes_cap,
-                               first_bucket_bytes=int(cfg.first_bucket_mb * 1024 * 1024), fused=self.fused)
+                               first_bucket_bytes=self._first_bucket_bytes, fused=self.fused)
 
     # ------------------------------------------------------------------------------------------ construction
     def _verify_params(self):
