@@ -39,6 +39,11 @@ struct TcParams {
   int num_splits;
   int num_stages;
   int a_mn, b_mn;           // operand majors (1 = MN-major / "transposed")
+  // batching (MODE_GEMM): problem index b = b1 + batch1 * b2; operands addressed through 4-D tensor maps
+  int batch1, batch2;
+  long long out_bs1, out_bs2;   // output strides (elements) of the two batch dimensions
+  int causal;               // 1: skip output tiles entirely above the diagonal (S = Q K^T)
+                            // 2: stop the K loop at the diagonal (O = P V with P lower-triangular)
   // convolution geometry
   int H, W, cin_blocks;
   int box_w, box_h, box_n;
@@ -48,6 +53,7 @@ struct TcParams {
   long long ldo;
   int out_bf16;
   int atomic;               // 1 = accumulate with red.global.add.f32 (split-K / wgrad)
+  float alpha;              // GEMM: D = act(alpha * A*B + bias)
   int act;                  // 0 none, 1 relu, 2 gelu(tanh)
   const float* bias;        // GEMM: per output column; FPROP: per output channel (row)
   float* stat_sum;          // FPROP: per-channel sum / sum-of-squares of the raw conv output
@@ -106,7 +112,8 @@ tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
   const uint32_t tmem_base = *tmem_slot;
 
   const int tiles_mn = p.m_blocks * p.n_blocks;
-  const int taps = (kMode == MODE_WGRAD) ? 9 : 1;
+  // "tap" doubles as the batch index in MODE_GEMM
+  const int taps = (kMode == MODE_WGRAD) ? 9 : (kMode == MODE_GEMM ? p.batch1 * p.batch2 : 1);
   const int num_items = tiles_mn * taps * p.num_splits;
 
   auto decode = [&](int item, int& m_blk, int& n_blk, int& tap, int& split) {
@@ -117,10 +124,14 @@ tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
     tap = t % taps;
     split = t / taps;
   };
-  auto ksteps_of = [&](int split) {
+  auto ksteps_of = [&](int split, int m_blk) {
     int k0 = split * p.k_steps_per_split;
     int k1 = min(k0 + p.k_steps_per_split, p.k_steps_total);
+    if (kMode == MODE_GEMM && p.causal == 2) k1 = min(k1, ((m_blk + 1) * kBlockM + kBK - 1) / kBK);
     return max(k1 - k0, 0);
+  };
+  auto skipped = [&](int m_blk, int n_blk) {
+    return kMode == MODE_GEMM && p.causal == 1 && n_blk * p.block_n >= (m_blk + 1) * kBlockM;
   };
 
   if (warp == 0) {
@@ -134,7 +145,9 @@ tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
         const int m0 = m_blk * kBlockM;
         const int n0 = n_blk * p.block_n;
         const int kbeg = split * p.k_steps_per_split;
-        const int nk = ksteps_of(split);
+        const int nk = ksteps_of(split, m_blk);
+        if (skipped(m_blk, n_blk)) continue;
+        const int b1 = (kMode == MODE_GEMM) ? tap % p.batch1 : 0, b2 = (kMode == MODE_GEMM) ? tap / p.batch1 : 0;
         for (int i = 0; i < nk; ++i) {
           const int kk = kbeg + i;
           mbar_wait(&empty_bar[stage], phase ^ 1u, 0x100u + stage);
@@ -144,16 +157,16 @@ tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
           if constexpr (kMode == MODE_GEMM) {
             const int k0 = kk * kBK;
             if (!p.a_mn) {
-              tma_load_2d(sa, &tmA, &full_bar[stage], k0, m0);
+              tma_load_4d(sa, &tmA, &full_bar[stage], k0, m0, b1, b2);
             } else {
               for (int j = 0; j < kBlockM / kChunk; ++j)
-                tma_load_2d(sa + j * (kBK * 128), &tmA, &full_bar[stage], m0 + j * kChunk, k0);
+                tma_load_4d(sa + j * (kBK * 128), &tmA, &full_bar[stage], m0 + j * kChunk, k0, b1, b2);
             }
             if (!p.b_mn) {
-              tma_load_2d(sb, &tmB, &full_bar[stage], k0, n0);
+              tma_load_4d(sb, &tmB, &full_bar[stage], k0, n0, b1, b2);
             } else {
               for (int j = 0; j < p.block_n / kChunk; ++j)
-                tma_load_2d(sb + j * (kBK * 128), &tmB, &full_bar[stage], n0 + j * kChunk, k0);
+                tma_load_4d(sb + j * (kBK * 128), &tmB, &full_bar[stage], n0 + j * kChunk, k0, b1, b2);
             }
           } else if constexpr (kMode == MODE_FPROP) {
             // K order: tap-major, then input-channel block.  A = packed weights [tap][Cout][Cin].
@@ -201,7 +214,8 @@ tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
       for (int item = blockIdx.x; item < num_items; item += gridDim.x) {
         int m_blk, n_blk, tap, split;
         decode(item, m_blk, n_blk, tap, split);
-        const int nk = ksteps_of(split);
+        const int nk = ksteps_of(split, m_blk);
+        if (skipped(m_blk, n_blk)) continue;
         mbar_wait(&tempty_bar[acc], acc_phase ^ 1u, 0x200u + acc);
         tc_fence_after();
         const uint32_t tmem_d = tmem_base + static_cast<uint32_t>(acc * p.block_n);
@@ -231,7 +245,11 @@ tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
     for (int item = blockIdx.x; item < num_items; item += gridDim.x) {
       int m_blk, n_blk, tap, split;
       decode(item, m_blk, n_blk, tap, split);
-      const int nk = ksteps_of(split);
+      const int nk = ksteps_of(split, m_blk);
+      if (skipped(m_blk, n_blk)) continue;
+      const long long boff = (kMode == MODE_GEMM)
+                                 ? static_cast<long long>(tap % p.batch1) * p.out_bs1 + static_cast<long long>(tap / p.batch1) * p.out_bs2
+                                 : 0;
       const int row = m_blk * kBlockM + ew * 32 + lane;     // output row owned by this thread
       const int n0 = n_blk * p.block_n;
       mbar_wait(&tfull_bar[acc], acc_phase, 0x400u + acc);
@@ -249,15 +267,15 @@ tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
         if constexpr (kMode == MODE_GEMM) {
           if (row < p.M) {
             if (p.atomic) {
-              float* o = reinterpret_cast<float*>(p.out) + static_cast<long long>(row) * p.ldo + n0 + c0;
+              float* o = reinterpret_cast<float*>(p.out) + boff + static_cast<long long>(row) * p.ldo + n0 + c0;
 #pragma unroll
               for (int j = 0; j < 32; ++j)
-                if (n0 + c0 + j < p.N) atomicAdd(o + j, __uint_as_float(v[j]));
+                if (n0 + c0 + j < p.N) atomicAdd(o + j, __uint_as_float(v[j]) * p.alpha);
             } else {
               float f[32];
 #pragma unroll
               for (int j = 0; j < 32; ++j) {
-                float x = __uint_as_float(v[j]);
+                float x = __uint_as_float(v[j]) * p.alpha;
                 const int col = n0 + c0 + j;
                 if (p.bias != nullptr && col < p.N) x += __ldg(p.bias + col);
                 if (p.act == 1) x = fmaxf(x, 0.f);
@@ -266,7 +284,7 @@ tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
               }
               const bool full = (n0 + c0 + 32 <= p.N);
               if (p.out_bf16) {
-                __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(p.out) + static_cast<long long>(row) * p.ldo + n0 + c0;
+                __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(p.out) + boff + static_cast<long long>(row) * p.ldo + n0 + c0;
                 if (full && ((reinterpret_cast<uintptr_t>(o) & 15) == 0)) {
 #pragma unroll
                   for (int j = 0; j < 32; j += 8) {
@@ -287,7 +305,7 @@ tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
                     if (n0 + c0 + j < p.N) o[j] = __float2bfloat16(f[j]);
                 }
               } else {
-                float* o = reinterpret_cast<float*>(p.out) + static_cast<long long>(row) * p.ldo + n0 + c0;
+                float* o = reinterpret_cast<float*>(p.out) + boff + static_cast<long long>(row) * p.ldo + n0 + c0;
                 if (full && ((reinterpret_cast<uintptr_t>(o) & 15) == 0)) {
 #pragma unroll
                   for (int j = 0; j < 32; j += 4)
@@ -410,7 +428,7 @@ static int launch_tc(const CUtensorMap& a, const CUtensorMap& b, TcParams& p, cu
     if (e != cudaSuccess) return DDPX_ERR_LAUNCH;
     attr_set = true;
   }
-  const int taps = (kMode == MODE_WGRAD) ? 9 : 1;
+  const int taps = (kMode == MODE_WGRAD) ? 9 : (kMode == MODE_GEMM ? p.batch1 * p.batch2 : 1);
   const int items = p.m_blocks * p.n_blocks * taps * p.num_splits;
   int grid = items < num_sms() ? items : num_sms();
   if (grid < 1) grid = 1;
@@ -422,23 +440,30 @@ static int launch_tc(const CUtensorMap& a, const CUtensorMap& b, TcParams& p, cu
 
 using namespace ddpx;
 
-extern "C" int ddpx_gemm(const void* A, const void* B, void* D, int M, int N, int K, long long lda, long long ldb,
-                         long long ldd, int a_mn, int b_mn, int bf16, int out_bf16, const float* bias, int act,
-                         int split_k, int accumulate, void* stream_) {
+// Batched GEMM: problem (b1, b2) reads A + b1*a_bs1 + b2*a_bs2 (elements) etc.  All strides in elements.
+extern "C" int ddpx_gemm_batched(const void* A, const void* B, void* D, int M, int N, int K, long long lda, long long ldb,
+                                 long long ldd, int a_mn, int b_mn, int bf16, int out_bf16, const float* bias, int act,
+                                 float alpha, int split_k, int accumulate, int batch1, int batch2, long long a_bs1,
+                                 long long a_bs2, long long b_bs1, long long b_bs2, long long d_bs1, long long d_bs2,
+                                 int causal, void* stream_) {
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
   const int elt = bf16 ? 2 : 4;
   const int bk = 128 / elt, chunk = 128 / elt;
-  if (M <= 0 || N <= 0 || K <= 0) return DDPX_ERR_ARG;
+  if (M <= 0 || N <= 0 || K <= 0 || batch1 < 1 || batch2 < 1) return DDPX_ERR_ARG;
   if ((lda * elt) % 16 || (ldb * elt) % 16) return DDPX_ERR_ALIGN;
+  if ((a_bs1 * elt) % 16 || (a_bs2 * elt) % 16 || (b_bs1 * elt) % 16 || (b_bs2 * elt) % 16) return DDPX_ERR_ALIGN;
   if ((reinterpret_cast<uintptr_t>(A) & 15) || (reinterpret_cast<uintptr_t>(B) & 15)) return DDPX_ERR_ALIGN;
   TcParams p{};
   p.M = M; p.N = N;
+  p.batch1 = batch1; p.batch2 = batch2; p.out_bs1 = d_bs1; p.out_bs2 = d_bs2; p.causal = causal; p.alpha = alpha;
   // N tile: the largest of {256,128,64} that still gives every SM a tile; narrow outputs get a narrow tile
   const int mb = (M + kBlockM - 1) / kBlockM;
+  const int nb_total = batch1 * batch2;
   const int min_bn = (b_mn && chunk > 32) ? chunk : 32;
   int bn = 256;
-  while (bn > 64 && mb * ((N + bn - 1) / bn) < num_sms()) bn /= 2;
+  while (bn > 64 && static_cast<long long>(mb) * ((N + bn - 1) / bn) * nb_total < num_sms()) bn /= 2;
   while (bn > min_bn && bn / 2 >= N) bn /= 2;
+  if (causal == 1 && bn > kBlockM) bn = kBlockM;      // square tiles so whole tiles fall above the diagonal
   if (bn < min_bn) bn = min_bn;
   p.block_n = bn;
   p.m_blocks = mb;
@@ -456,17 +481,29 @@ extern "C" int ddpx_gemm(const void* A, const void* B, void* D, int M, int N, in
   CUtensorMap ta, tb;
   int rc;
   {
-    uint64_t dims[2], str[1]; uint32_t box[2];
+    uint64_t dims[4], str[3]; uint32_t box[4];
+    dims[2] = batch1; dims[3] = batch2; box[2] = 1; box[3] = 1;
     if (!a_mn) { dims[0] = K; dims[1] = M; box[0] = bk; box[1] = kBlockM; }
     else       { dims[0] = M; dims[1] = K; box[0] = chunk; box[1] = bk; }
     str[0] = static_cast<uint64_t>(lda) * elt;
-    if ((rc = make_tmap(&ta, A, bf16, 2, dims, str, box, a_mn && !bf16)) != DDPX_OK) return rc;
+    str[1] = batch1 > 1 ? static_cast<uint64_t>(a_bs1) * elt : str[0] * dims[1];
+    str[2] = batch2 > 1 ? static_cast<uint64_t>(a_bs2) * elt : str[1] * dims[2];
+    if ((rc = make_tmap(&ta, A, bf16, 4, dims, str, box, a_mn && !bf16)) != DDPX_OK) return rc;
     if (!b_mn) { dims[0] = K; dims[1] = N; box[0] = bk; box[1] = bn; }
     else       { dims[0] = N; dims[1] = K; box[0] = chunk; box[1] = bk; }
     str[0] = static_cast<uint64_t>(ldb) * elt;
-    if ((rc = make_tmap(&tb, B, bf16, 2, dims, str, box, b_mn && !bf16)) != DDPX_OK) return rc;
+    str[1] = batch1 > 1 ? static_cast<uint64_t>(b_bs1) * elt : str[0] * dims[1];
+    str[2] = batch2 > 1 ? static_cast<uint64_t>(b_bs2) * elt : str[1] * dims[2];
+    if ((rc = make_tmap(&tb, B, bf16, 4, dims, str, box, b_mn && !bf16)) != DDPX_OK) return rc;
   }
   return bf16 ? launch_tc<MODE_GEMM, true>(ta, tb, p, stream) : launch_tc<MODE_GEMM, false>(ta, tb, p, stream);
+}
+
+extern "C" int ddpx_gemm(const void* A, const void* B, void* D, int M, int N, int K, long long lda, long long ldb,
+                         long long ldd, int a_mn, int b_mn, int bf16, int out_bf16, const float* bias, int act,
+                         int split_k, int accumulate, void* stream_) {
+  return ddpx_gemm_batched(A, B, D, M, N, K, lda, ldb, ldd, a_mn, b_mn, bf16, out_bf16, bias, act, 1.0f, split_k,
+                           accumulate, 1, 1, 0, 0, 0, 0, 0, 0, 0, stream_);
 }
 
 // pixel-tile geometry shared by fprop / wgrad: `pixels` consecutive NHWC pixels as a (w,h,n) box

@@ -181,3 +181,11 @@ def read_error_word() -> int:
 def gemm_small(A, B, C, M, N, K, sam, sak, sbn, sbk, ldc, bias=None, act=0, accumulate=0):
     _call("ddpx_gemm_small", _P(A), _P(B), _P(C), c_int(M), c_int(N), c_int(K), c_longlong(sam), c_longlong(sak),
           c_longlong(sbn), c_longlong(sbk), c_longlong(ldc), _P(bias), c_int(act), c_int(accumulate), _st())
+
+
+def relu_bwd_any(y, dy, dx):
+    """ReLU backward for fp32 or bf16 activations."""
+    if y.dtype == torch.float32:
+        relu_bwd(y, dy, dx)
+    else:
+        _call("ddpx_relu_bwd_bf16", _P(y), _P(dy), _P(dx), c_longlong(y.numel()), _st())

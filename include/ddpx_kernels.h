@@ -36,6 +36,14 @@ int ddpx_gemm(const void* A, const void* B, void* D, int M, int N, int K, long l
               long long ldd, int a_mn, int b_mn, int bf16, int out_bf16, const float* bias, int act,
               int split_k, int accumulate, void* stream);
 
+/* Batched form: problem (b1,b2), b1 < batch1, b2 < batch2, reads A + b1*a_bs1 + b2*a_bs2 (element strides), same for
+ * B and D; D = act(alpha * A*B + bias).  causal = 1 skips output tiles entirely above the diagonal (attention scores),
+ * causal = 2 stops the K loop at the diagonal (probabilities x values).  Used for the attention GEMMs of GPT-2. */
+int ddpx_gemm_batched(const void* A, const void* B, void* D, int M, int N, int K, long long lda, long long ldb,
+                      long long ldd, int a_mn, int b_mn, int bf16, int out_bf16, const float* bias, int act, float alpha,
+                      int split_k, int accumulate, int batch1, int batch2, long long a_bs1, long long a_bs2,
+                      long long b_bs1, long long b_bs2, long long d_bs1, long long d_bs2, int causal, void* stream);
+
 /* ---- 3x3 / stride 1 / pad 1 convolution, NHWC fp32, TF32 tensor cores (M:53) ----------------
  * fprop: y[N,H,W,Cout] = conv(x[N,H,W,Cin], wpacked[9][Cout][Cin]) (+bias[Cout]) (+ReLU);
  *        optionally accumulates per-channel sum / sum-of-squares of the pre-activation output into
