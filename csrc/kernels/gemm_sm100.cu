@@ -48,6 +48,7 @@ struct TcParams {
   int H, W, cin_blocks;
   int box_w, box_h, box_n;
   int cin_total;
+  int conv_taps;            // FPROP: 9 (3x3) or 1 (1x1 over pre-gathered patches)
   // epilogue
   void* out;
   long long ldo;
@@ -172,7 +173,8 @@ tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
             // K order: tap-major, then input-channel block.  A = packed weights [tap][Cout][Cin].
             const int t9 = kk / p.cin_blocks;
             const int cb = kk - t9 * p.cin_blocks;
-            const int r = t9 / 3, s = t9 - r * 3;
+            // a single-tap problem (cin_total taps == 1: pre-gathered patches, i.e. a 1x1 conv) reads the centre
+            const int r = (p.conv_taps == 1) ? 1 : t9 / 3, s = (p.conv_taps == 1) ? 1 : t9 - (t9 / 3) * 3;
             tma_load_3d(sa, &tmA, &full_bar[stage], cb * kBK, m0, t9);
             // B = NHWC activations; tile of block_n consecutive pixels = box (box_w, box_h, box_n)
             const int hw = p.H * p.W;
@@ -522,9 +524,8 @@ static int conv_box(int pixels, int H, int W, int Nimg, int* bw, int* bh, int* b
   return DDPX_OK;
 }
 
-extern "C" int ddpx_conv3x3_fprop(const float* x, const float* wpacked, float* y, int Nimg, int H, int W, int Cin,
-                                  int Cout, const float* bias, int act, float* stat_sum, float* stat_sq,
-                                  void* stream_) {
+static int conv_fprop_impl(const float* x, const float* wpacked, float* y, int Nimg, int H, int W, int Cin, int Cout,
+                           const float* bias, int act, float* stat_sum, float* stat_sq, int taps, void* stream_) {
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
   if (Cin % 32 || Cout % 32) return DDPX_ERR_SHAPE;
   const long long P = static_cast<long long>(Nimg) * H * W;
@@ -539,15 +540,16 @@ extern "C" int ddpx_conv3x3_fprop(const float* x, const float* wpacked, float* y
   p.m_blocks = (Cout + kBlockM - 1) / kBlockM;
   p.n_blocks = static_cast<int>(P / bn);
   p.cin_blocks = Cin / 32;
-  p.k_steps_total = 9 * p.cin_blocks;
+  p.k_steps_total = taps * p.cin_blocks;
   p.k_steps_per_split = p.k_steps_total;
   p.num_splits = 1;
+  p.conv_taps = taps;
   p.H = H; p.W = W; p.box_w = bw; p.box_h = bh; p.box_n = bnn; p.cin_total = Cin;
   p.out = y; p.ldo = Cout; p.act = act; p.bias = bias; p.stat_sum = stat_sum; p.stat_sq = stat_sq;
   CUtensorMap ta, tb;
   int rc;
   {
-    uint64_t dims[3] = {static_cast<uint64_t>(Cin), static_cast<uint64_t>(Cout), 9};
+    uint64_t dims[3] = {static_cast<uint64_t>(Cin), static_cast<uint64_t>(Cout), static_cast<uint64_t>(taps)};
     uint64_t str[2] = {static_cast<uint64_t>(Cin) * 4, static_cast<uint64_t>(Cin) * Cout * 4};
     uint32_t box[3] = {32, kBlockM, 1};
     if ((rc = make_tmap(&ta, wpacked, false, 3, dims, str, box)) != DDPX_OK) return rc;
@@ -561,6 +563,20 @@ extern "C" int ddpx_conv3x3_fprop(const float* x, const float* wpacked, float* y
     if ((rc = make_tmap(&tb, x, false, 4, dims, str, box)) != DDPX_OK) return rc;
   }
   return launch_tc<MODE_FPROP, false>(ta, tb, p, stream);
+}
+
+extern "C" int ddpx_conv3x3_fprop(const float* x, const float* wpacked, float* y, int Nimg, int H, int W, int Cin,
+                                  int Cout, const float* bias, int act, float* stat_sum, float* stat_sq,
+                                  void* stream_) {
+  return conv_fprop_impl(x, wpacked, y, Nimg, H, W, Cin, Cout, bias, act, stat_sum, stat_sq, 9, stream_);
+}
+
+// 1x1 convolution == per-pixel GEMM with the fprop epilogue (NHWC store, bias, ReLU, BN statistics).  Used for the RGB
+// stem after ddpx_im2col_stem gathered the 3x3x3 patches into 32-wide rows (wpacked = [Cout][32]).
+extern "C" int ddpx_conv1x1_fprop(const float* x, const float* wpacked, float* y, int Nimg, int H, int W, int Cin,
+                                  int Cout, const float* bias, int act, float* stat_sum, float* stat_sq,
+                                  void* stream_) {
+  return conv_fprop_impl(x, wpacked, y, Nimg, H, W, Cin, Cout, bias, act, stat_sum, stat_sq, 1, stream_);
 }
 
 extern "C" int ddpx_conv3x3_wgrad(const float* dy, const float* x, float* dw, int Nimg, int H, int W, int Cin,

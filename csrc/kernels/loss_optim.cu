@@ -106,10 +106,10 @@ constexpr int kMaxTensors = 96;
 constexpr int kChunk = 4096;  // elements per block-iteration
 
 struct TensorTable {
-  float* p[kMaxTensors];
-  const float* g[kMaxTensors];
-  float* s0[kMaxTensors];      // SGD: momentum buffer; AdamW: exp_avg
-  float* s1[kMaxTensors];      // AdamW: exp_avg_sq
+  void* p[kMaxTensors];
+  const void* g[kMaxTensors];
+  void* s0[kMaxTensors];       // SGD: momentum buffer; AdamW: exp_avg
+  void* s1[kMaxTensors];       // AdamW: exp_avg_sq
   int chunk_start[kMaxTensors + 1];   // prefix sum of chunk counts
   long long numel[kMaxTensors];
   int n;
@@ -126,6 +126,7 @@ __device__ __forceinline__ int find_tensor(const TensorTable& t, int chunk) {
 
 // torch SGD semantics (sgd.py:346-380): g += wd*p; first step buf = g else buf = mu*buf + (1-dampening)*g;
 // nesterov: g = g + mu*buf else g = buf; p -= lr*g.   State is updated even when lr == 0 (LambdaLR's first step).
+template <typename T>
 __global__ void sgd_multi_kernel(const __grid_constant__ TensorTable t, float lr, float momentum, float dampening, float wd,
                                  int nesterov, int first_step, float grad_scale) {
   const int total_chunks = t.chunk_start[t.n];
@@ -133,24 +134,25 @@ __global__ void sgd_multi_kernel(const __grid_constant__ TensorTable t, float lr
     const int ti = find_tensor(t, chunk);
     const long long base = static_cast<long long>(chunk - t.chunk_start[ti]) * kChunk;
     const long long end = min(base + kChunk, t.numel[ti]);
-    float* __restrict__ p = t.p[ti];
-    const float* __restrict__ g = t.g[ti];
-    float* __restrict__ buf = t.s0[ti];
+    T* __restrict__ p = static_cast<T*>(t.p[ti]);
+    const T* __restrict__ g = static_cast<const T*>(t.g[ti]);
+    T* __restrict__ buf = static_cast<T*>(t.s0[ti]);
     for (long long i = base + threadIdx.x; i < end; i += blockDim.x) {
-      float pv = p[i];
-      float gv = g[i] * grad_scale + wd * pv;
+      float pv = to_f(p[i]);
+      float gv = to_f(g[i]) * grad_scale + wd * pv;
       if (momentum != 0.f) {
-        float b = first_step ? gv : momentum * buf[i] + (1.f - dampening) * gv;
-        buf[i] = b;
+        float b = first_step ? gv : momentum * to_f(buf[i]) + (1.f - dampening) * gv;
+        buf[i] = from_f<T>(b);
         gv = nesterov ? gv + momentum * b : b;
       }
-      p[i] = pv - lr * gv;
+      p[i] = from_f<T>(pv - lr * gv);
     }
   }
 }
 
 // torch AdamW semantics: p *= 1 - lr*wd; m = b1*m + (1-b1)*g; v = b2*v + (1-b2)*g^2;
 // p -= lr/bc1 * m / (sqrt(v)/sqrt(bc2) + eps)
+template <typename T>
 __global__ void adamw_multi_kernel(const __grid_constant__ TensorTable t, float lr, float beta1, float beta2, float eps, float wd,
                                    float bc1, float bc2_sqrt, float grad_scale) {
   const int total_chunks = t.chunk_start[t.n];
@@ -158,19 +160,19 @@ __global__ void adamw_multi_kernel(const __grid_constant__ TensorTable t, float 
     const int ti = find_tensor(t, chunk);
     const long long base = static_cast<long long>(chunk - t.chunk_start[ti]) * kChunk;
     const long long end = min(base + kChunk, t.numel[ti]);
-    float* __restrict__ p = t.p[ti];
-    const float* __restrict__ g = t.g[ti];
-    float* __restrict__ m = t.s0[ti];
-    float* __restrict__ v = t.s1[ti];
+    T* __restrict__ p = static_cast<T*>(t.p[ti]);
+    const T* __restrict__ g = static_cast<const T*>(t.g[ti]);
+    T* __restrict__ m = static_cast<T*>(t.s0[ti]);
+    T* __restrict__ v = static_cast<T*>(t.s1[ti]);
     for (long long i = base + threadIdx.x; i < end; i += blockDim.x) {
-      const float gv = g[i] * grad_scale;
-      float pv = p[i] * (1.f - lr * wd);
-      const float mv = beta1 * m[i] + (1.f - beta1) * gv;
-      const float vv = beta2 * v[i] + (1.f - beta2) * gv * gv;
-      m[i] = mv;
-      v[i] = vv;
+      const float gv = to_f(g[i]) * grad_scale;
+      float pv = to_f(p[i]) * (1.f - lr * wd);
+      const float mv = beta1 * to_f(m[i]) + (1.f - beta1) * gv;
+      const float vv = beta2 * to_f(v[i]) + (1.f - beta2) * gv * gv;
+      m[i] = from_f<T>(mv);
+      v[i] = from_f<T>(vv);
       pv -= (lr / bc1) * mv / (sqrtf(vv) / bc2_sqrt + eps);
-      p[i] = pv;
+      p[i] = from_f<T>(pv);
     }
   }
 }
@@ -182,10 +184,10 @@ int fill_table(TensorTable& t, int n, void* const* params, void* const* grads, v
   t.n = n;
   int chunks = 0;
   for (int i = 0; i < n; ++i) {
-    t.p[i] = static_cast<float*>(params[i]);
-    t.g[i] = static_cast<const float*>(grads[i]);
-    t.s0[i] = s0 ? static_cast<float*>(s0[i]) : nullptr;
-    t.s1[i] = s1 ? static_cast<float*>(s1[i]) : nullptr;
+    t.p[i] = params[i];
+    t.g[i] = grads[i];
+    t.s0[i] = s0 ? s0[i] : nullptr;
+    t.s1[i] = s1 ? s1[i] : nullptr;
     t.numel[i] = numel[i];
     t.chunk_start[i] = chunks;
     chunks += static_cast<int>((numel[i] + kChunk - 1) / kChunk);
@@ -236,7 +238,7 @@ extern "C" int ddpx_mse(const float* pred, const float* target, float* dpred, fl
 
 extern "C" int ddpx_sgd_multi(int n, void* const* params, void* const* grads, void* const* momentum_bufs,
                               const long long* numel, float lr, float momentum, float dampening, float weight_decay,
-                              int nesterov, int first_step, float grad_scale, void* stream) {
+                              int nesterov, int first_step, float grad_scale, int is_bf16, void* stream) {
   for (int off = 0; off < n; off += kMaxTensors) {
     const int m = (n - off) < kMaxTensors ? (n - off) : kMaxTensors;
     TensorTable t;
@@ -244,15 +246,19 @@ extern "C" int ddpx_sgd_multi(int n, void* const* params, void* const* grads, vo
     if (rc != DDPX_OK) return rc;
     int grid = t.chunk_start[m] < 148 * 8 ? t.chunk_start[m] : 148 * 8;
     if (grid < 1) continue;
-    sgd_multi_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(t, lr, momentum, dampening, weight_decay, nesterov,
-                                                                         first_step, grad_scale);
+    if (is_bf16)
+      sgd_multi_kernel<__nv_bfloat16><<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(t, lr, momentum, dampening, weight_decay,
+                                                                                         nesterov, first_step, grad_scale);
+    else
+      sgd_multi_kernel<float><<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(t, lr, momentum, dampening, weight_decay,
+                                                                                 nesterov, first_step, grad_scale);
   }
   return LAUNCH_OK();
 }
 
 extern "C" int ddpx_adamw_multi(int n, void* const* params, void* const* grads, void* const* exp_avg, void* const* exp_avg_sq,
                                 const long long* numel, float lr, float beta1, float beta2, float eps, float weight_decay,
-                                long long step, float grad_scale, void* stream) {
+                                long long step, float grad_scale, int is_bf16, void* stream) {
   const float bc1 = 1.f - powf(beta1, static_cast<float>(step));
   const float bc2_sqrt = sqrtf(1.f - powf(beta2, static_cast<float>(step)));
   for (int off = 0; off < n; off += kMaxTensors) {
@@ -262,8 +268,12 @@ extern "C" int ddpx_adamw_multi(int n, void* const* params, void* const* grads, 
     if (rc != DDPX_OK) return rc;
     int grid = t.chunk_start[m] < 148 * 8 ? t.chunk_start[m] : 148 * 8;
     if (grid < 1) continue;
-    adamw_multi_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(t, lr, beta1, beta2, eps, weight_decay, bc1, bc2_sqrt,
-                                                                           grad_scale);
+    if (is_bf16)
+      adamw_multi_kernel<__nv_bfloat16><<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(t, lr, beta1, beta2, eps, weight_decay,
+                                                                                           bc1, bc2_sqrt, grad_scale);
+    else
+      adamw_multi_kernel<float><<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(t, lr, beta1, beta2, eps, weight_decay, bc1,
+                                                                                   bc2_sqrt, grad_scale);
   }
   return LAUNCH_OK();
 }

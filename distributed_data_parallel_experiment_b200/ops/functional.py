@@ -59,24 +59,37 @@ def _check_f32(*ts):
 
 
 # ------------------------------------------------------------------------------------------------ conv (+BN+ReLU+pool)
-def _conv_forward(xin, w, y, N, H, W_, Cin, Cout, stem, bias, act, ssum, ssq, need_dgrad):
-    """Runs the forward convolution; returns the packed dgrad weights (or None)."""
-    wd = None
+_STEM_SPLIT_K = 296   # two K-slices per SM for the pixels-long reduction of the stem weight gradient
+
+
+def _conv_forward(x, w, y, N, H, W_, Cin, Cout, stem, bias, act, ssum, ssq, need_dgrad):
+    """Runs the forward convolution; returns (tensor to save for the weight gradient, packed dgrad weights or None).
+
+    RGB stem: the 3x3x3 patches are gathered once into 32-float rows (kept for the backward) and the convolution is a
+    1x1 tcgen05 conv over them; everything else is the implicit-GEMM 3x3 kernel straight off the NHWC activations."""
     if stem:
-        native.conv_stem_fprop(xin, w, bias, y, N, H, W_, Cout, act, ssum, ssq)
-    else:
-        wp = torch.empty(9 * Cout * Cin, device=w.device, dtype=torch.float32)
-        if need_dgrad:
-            wd = torch.empty(9 * Cout * Cin, device=w.device, dtype=torch.float32)
-        native.pack_conv_weights(w, wp, wd, Cout, Cin)
-        native.conv3x3_fprop(xin, wp, y, N, H, W_, Cin, Cout, bias, act, ssum, ssq)
-    return wd
+        xc = x if x.is_contiguous() else to_nchw_contiguous(x)
+        patches = torch.empty((N, H, W_, 32), device=w.device, dtype=torch.float32)
+        native.im2col_stem(xc, patches, N, H, W_)
+        wp = torch.empty(Cout * 32, device=w.device, dtype=torch.float32)
+        native.pack_stem_weights(w, wp, Cout)
+        native.conv1x1_fprop(patches, wp, y, N, H, W_, 32, Cout, bias, act, ssum, ssq)
+        return patches, None
+    xin = to_nhwc(x)
+    wd = None
+    wp = torch.empty(9 * Cout * Cin, device=w.device, dtype=torch.float32)
+    if need_dgrad:
+        wd = torch.empty(9 * Cout * Cin, device=w.device, dtype=torch.float32)
+    native.pack_conv_weights(w, wp, wd, Cout, Cin)
+    native.conv3x3_fprop(xin, wp, y, N, H, W_, Cin, Cout, bias, act, ssum, ssq)
+    return xin, wd
 
 
 def _conv_backward(ctx_stem, dconv, xin, w, wd, N, H, W_, Cin, Cout, need_dx):
     dw = _zeros(w.shape, w.device)
     if ctx_stem:
-        native.conv_stem_wgrad(dconv, xin, dw, N, H, W_, Cout)
+        # dw[Cout][27] += dconv^T[Cout][P] @ patches[P][0:27]  (both operands MN-major, split-K, fp32 atomics)
+        native.gemm(dconv, xin, dw, Cout, 27, N * H * W_, Cout, 32, 27, 1, 1, None, 0, _STEM_SPLIT_K, 1)
         return None, dw
     native.conv3x3_wgrad(dconv, xin, dw, N, H, W_, Cin, Cout)
     dx = None
@@ -88,7 +101,7 @@ def _conv_backward(ctx_stem, dconv, xin, w, wd, N, H, W_, Cin, Cout, need_dx):
 
 def _conv_supported(Cin, Cout, H, W_):
     if Cin == 3:
-        return Cout <= 128 and 256 % Cout == 0
+        return Cout % 32 == 0
     return Cin % 32 == 0 and Cout % 32 == 0
 
 
@@ -104,12 +117,11 @@ class _ConvBNAct(Function):
             raise NotImplementedError(f"native conv3x3: unsupported channels Cin={Cin} Cout={Cout}")
         stem = Cin == 3
         dev = x.device
-        xin = (x if x.is_contiguous() else to_nchw_contiguous(x)) if stem else to_nhwc(x)
         y = torch.empty((N, H, W_, Cout), device=dev, dtype=torch.float32)
         stats = _zeros((2, Cout), dev) if training else None
         need_dx = ctx.needs_input_grad[0]
-        wd = _conv_forward(xin, w.detach(), y, N, H, W_, Cin, Cout, stem, None, 0,
-                           stats[0] if training else None, stats[1] if training else None, need_dx)
+        xin, wd = _conv_forward(x, w.detach(), y, N, H, W_, Cin, Cout, stem, None, 0,
+                                stats[0] if training else None, stats[1] if training else None, need_dx)
         mr = torch.empty((2, Cout), device=dev, dtype=torch.float32)
         if training:
             native.bn_finalize(stats[0], stats[1], float(N * H * W_), mr[0], mr[1], running_mean, running_var, nbt,
@@ -150,11 +162,10 @@ class _ConvAct(Function):
         if not _conv_supported(Cin, Cout, H, W_):
             raise NotImplementedError(f"native conv3x3: unsupported channels Cin={Cin} Cout={Cout}")
         stem = Cin == 3
-        xin = (x if x.is_contiguous() else to_nchw_contiguous(x)) if stem else to_nhwc(x)
         y = torch.empty((N, H, W_, Cout), device=x.device, dtype=torch.float32)
         need_dx = ctx.needs_input_grad[0]
-        wd = _conv_forward(xin, w.detach(), y, N, H, W_, Cin, Cout, stem, bias.detach() if bias is not None else None,
-                           1 if relu else 0, None, None, need_dx)
+        xin, wd = _conv_forward(x, w.detach(), y, N, H, W_, Cin, Cout, stem, bias.detach() if bias is not None else None,
+                                1 if relu else 0, None, None, need_dx)
         ctx.save_for_backward(xin, y, w, wd)
         ctx.cfg = (N, H, W_, Cin, Cout, stem, bool(relu), need_dx, bias is not None)
         return from_nhwc(y)
@@ -387,7 +398,7 @@ class _Linear(Function):
                 bf = bf.float()
         out = torch.empty((M, N), device=x.device, dtype=x.dtype)
         pre = None
-        if act == 2 and x.requires_grad or (act == 2 and w.requires_grad):
+        if act == 2 and any(ctx.needs_input_grad[:3]):
             # GELU backward needs the pre-activation: keep it (bias fused), apply GELU in a second epilogue-free pass
             pre = torch.empty((M, N), device=x.device, dtype=x.dtype)
             _gemm_nt(x2, wv, pre, bf, 0)

@@ -20,9 +20,37 @@ def _st():
     return c_void_p(torch.cuda.current_stream().cuda_stream)
 
 
-def _call(name, *args, launches: int = 1):
+_PROFILE = None   # None = off; else list of (name, start_event, end_event)
+
+
+def profile_begin():
+    """Start per-entry-point device timing (CUDA events around every native call; diagnostics only)."""
+    global _PROFILE
+    _PROFILE = []
+
+
+def profile_end():
+    """Stop timing; returns {name: (calls, total_ms)} sorted by total time."""
+    global _PROFILE
+    rec, _PROFILE = _PROFILE, None
+    torch.cuda.synchronize()
+    agg = {}
+    for name, e0, e1 in rec or []:
+        c, t = agg.get(name, (0, 0.0))
+        agg[name] = (c + 1, t + e0.elapsed_time(e1))
+    return dict(sorted(agg.items(), key=lambda kv: -kv[1][1]))
+
+
+def _call(name, *args, launches: int = 1, tag: str = ""):
     fn = getattr(_lib.lib(), name)
-    rc = fn(*args)
+    if _PROFILE is not None:
+        e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
+        e0.record()
+        rc = fn(*args)
+        e1.record()
+        _PROFILE.append((name + tag, e0, e1))
+    else:
+        rc = fn(*args)
     _lib.count_launch(launches)
     if rc != 0:
         _lib.check(rc, name)
@@ -40,12 +68,36 @@ def gemm(A, B, D, M, N, K, lda, ldb, ldd, a_mn=0, b_mn=0, bias=None, act=0, spli
 
 def conv3x3_fprop(x_nhwc, w_packed, y_nhwc, N, H, W, Cin, Cout, bias=None, act=0, stat_sum=None, stat_sq=None):
     _call("ddpx_conv3x3_fprop", _P(x_nhwc), _P(w_packed), _P(y_nhwc), c_int(N), c_int(H), c_int(W), c_int(Cin),
-          c_int(Cout), _P(bias), c_int(act), _P(stat_sum), _P(stat_sq), _st())
+          c_int(Cout), _P(bias), c_int(act), _P(stat_sum), _P(stat_sq), _st(), tag=f"[{Cin}->{Cout}@{H}]")
 
 
 def conv3x3_wgrad(dy_nhwc, x_nhwc, dw, N, H, W, Cin, Cout, split_k=0):
     _call("ddpx_conv3x3_wgrad", _P(dy_nhwc), _P(x_nhwc), _P(dw), c_int(N), c_int(H), c_int(W), c_int(Cin), c_int(Cout),
-          c_int(split_k), _st())
+          c_int(split_k), _st(), tag=f"[{Cin}->{Cout}@{H}]")
+
+
+def im2col_stem(x_nchw, patches, N, H, W):
+    _call("ddpx_im2col_stem", _P(x_nchw), _P(patches), c_int(N), c_int(H), c_int(W), _st())
+
+
+def pack_stem_weights(w, wp, Cout):
+    _call("ddpx_pack_stem_weights", _P(w), _P(wp), c_int(Cout), _st())
+
+
+def conv1x1_fprop(x_nhwc, w_packed, y_nhwc, N, H, W, Cin, Cout, bias=None, act=0, stat_sum=None, stat_sq=None):
+    _call("ddpx_conv1x1_fprop", _P(x_nhwc), _P(w_packed), _P(y_nhwc), c_int(N), c_int(H), c_int(W), c_int(Cin),
+          c_int(Cout), _P(bias), c_int(act), _P(stat_sum), _P(stat_sq), _st(), tag=f"[{Cin}->{Cout}@{H}]")
+
+
+def gemm_batched(A, B, D, M, N, K, lda, ldb, ldd, a_mn, b_mn, batch1, batch2, a_bs, b_bs, d_bs, alpha=1.0, causal=0,
+                 bias=None, act=0):
+    """Batched D = act(alpha * op(A) op(B) + bias); *_bs = (stride_b1, stride_b2) in elements."""
+    bf16 = 1 if A.dtype == torch.bfloat16 else 0
+    out_bf16 = 1 if D.dtype == torch.bfloat16 else 0
+    _call("ddpx_gemm_batched", _P(A), _P(B), _P(D), c_int(M), c_int(N), c_int(K), c_longlong(lda), c_longlong(ldb),
+          c_longlong(ldd), c_int(a_mn), c_int(b_mn), c_int(bf16), c_int(out_bf16), _P(bias), c_int(act), c_float(alpha),
+          c_int(1), c_int(0), c_int(batch1), c_int(batch2), c_longlong(a_bs[0]), c_longlong(a_bs[1]), c_longlong(b_bs[0]),
+          c_longlong(b_bs[1]), c_longlong(d_bs[0]), c_longlong(d_bs[1]), c_int(causal), _st())
 
 
 def pack_conv_weights(w, w_fprop, w_dgrad, Cout, Cin):
@@ -119,17 +171,17 @@ def bn_stats(x, P, C, ssum, ssq):
 
 def bn_apply(x, y, mean, rstd, gamma, beta, N, H, W, C, relu, pool):
     _call("ddpx_bn_apply", _P(x), _P(y), _P(mean), _P(rstd), _P(gamma), _P(beta), c_int(N), c_int(H), c_int(W), c_int(C),
-          c_int(relu), c_int(pool), _st())
+          c_int(relu), c_int(pool), _st(), tag=f"[{C}@{H}]")
 
 
 def bn_bwd_reduce(x, dout, mean, rstd, gamma, beta, N, H, W, C, relu, pool, sum_dz, sum_dzx):
     _call("ddpx_bn_bwd_reduce", _P(x), _P(dout), _P(mean), _P(rstd), _P(gamma), _P(beta), c_int(N), c_int(H), c_int(W),
-          c_int(C), c_int(relu), c_int(pool), _P(sum_dz), _P(sum_dzx), _st())
+          c_int(C), c_int(relu), c_int(pool), _P(sum_dz), _P(sum_dzx), _st(), tag=f"[{C}@{H}]")
 
 
 def bn_bwd_apply(x, dout, mean, rstd, gamma, beta, sum_dz, sum_dzx, N, H, W, C, relu, pool, use_batch_stats, dx):
     _call("ddpx_bn_bwd_apply", _P(x), _P(dout), _P(mean), _P(rstd), _P(gamma), _P(beta), _P(sum_dz), _P(sum_dzx), c_int(N),
-          c_int(H), c_int(W), c_int(C), c_int(relu), c_int(pool), c_int(use_batch_stats), _P(dx), _st())
+          c_int(H), c_int(W), c_int(C), c_int(relu), c_int(pool), c_int(use_batch_stats), _P(dx), _st(), tag=f"[{C}@{H}]")
 
 
 # ------------------------------------------------------------------------------------------------ losses
@@ -161,7 +213,8 @@ def sgd_multi(params, grads, bufs, lr, momentum, dampening, weight_decay, nester
     numel = (c_longlong * n)(*[p.numel() for p in params])
     _call("ddpx_sgd_multi", c_int(n), _ptr_array(params), _ptr_array(grads), _ptr_array(bufs) if bufs is not None else None,
           numel, c_float(lr), c_float(momentum), c_float(dampening), c_float(weight_decay), c_int(int(nesterov)),
-          c_int(int(first_step)), c_float(grad_scale), _st(), launches=(n + 95) // 96)
+          c_int(int(first_step)), c_float(grad_scale), c_int(1 if params[0].dtype == torch.bfloat16 else 0), _st(),
+          launches=(n + 95) // 96)
 
 
 def adamw_multi(params, grads, exp_avg, exp_avg_sq, lr, beta1, beta2, eps, weight_decay, step, grad_scale=1.0):
@@ -169,7 +222,7 @@ def adamw_multi(params, grads, exp_avg, exp_avg_sq, lr, beta1, beta2, eps, weigh
     numel = (c_longlong * n)(*[p.numel() for p in params])
     _call("ddpx_adamw_multi", c_int(n), _ptr_array(params), _ptr_array(grads), _ptr_array(exp_avg), _ptr_array(exp_avg_sq),
           numel, c_float(lr), c_float(beta1), c_float(beta2), c_float(eps), c_float(weight_decay), c_longlong(step),
-          c_float(grad_scale), _st(), launches=(n + 95) // 96)
+          c_float(grad_scale), c_int(1 if params[0].dtype == torch.bfloat16 else 0), _st(), launches=(n + 95) // 96)
 
 
 def read_error_word() -> int:
@@ -189,3 +242,80 @@ def relu_bwd_any(y, dy, dx):
         relu_bwd(y, dy, dx)
     else:
         _call("ddpx_relu_bwd_bf16", _P(y), _P(dy), _P(dx), c_longlong(y.numel()), _st())
+
+
+# ------------------------------------------------------------------------------------------------ transformer kernels
+def _bf(t):
+    return 1 if t.dtype == torch.bfloat16 else 0
+
+
+def layernorm_fwd(x, gamma, beta, y, mean, rstd, rows, C, eps):
+    _call("ddpx_layernorm_fwd", _P(x), _P(gamma), _P(beta), _P(y), _P(mean), _P(rstd), c_longlong(rows), c_int(C),
+          c_float(eps), c_int(_bf(x)), _st())
+
+
+def layernorm_bwd(x, dy, gamma, mean, rstd, dx, dgamma, dbeta, rows, C):
+    _call("ddpx_layernorm_bwd", _P(x), _P(dy), _P(gamma), _P(mean), _P(rstd), _P(dx), _P(dgamma), _P(dbeta),
+          c_longlong(rows), c_int(C), c_int(_bf(x)), _st())
+
+
+def gelu_fwd(x, y):
+    _call("ddpx_gelu_fwd", _P(x), _P(y), c_longlong(x.numel()), c_int(_bf(x)), _st())
+
+
+def gelu_bwd(x, dy, dx):
+    _call("ddpx_gelu_bwd", _P(x), _P(dy), _P(dx), c_longlong(x.numel()), c_int(_bf(x)), _st())
+
+
+def add(a, b, out):
+    _call("ddpx_add", _P(a), _P(b), _P(out), c_longlong(a.numel()), c_int(_bf(a)), _st())
+
+
+def cast_scale(src, dst, scale=1.0):
+    """dst = src * scale across fp32/bf16 (f32->bf16, bf16->f32, bf16->bf16)."""
+    if src.dtype == torch.float32 and dst.dtype == torch.bfloat16:
+        kind = 0
+    elif src.dtype == torch.bfloat16 and dst.dtype == torch.float32:
+        kind = 1
+    elif src.dtype == torch.bfloat16 and dst.dtype == torch.bfloat16:
+        kind = 2
+    else:
+        raise TypeError("cast_scale: unsupported dtype pair")
+    _call("ddpx_cast_scale", _P(src), _P(dst), c_longlong(src.numel()), c_float(scale), c_int(kind), _st())
+
+
+def scale_copy_bf16(src, dst, n, scale):
+    _call("ddpx_cast_scale", _P(src), _P(dst), c_longlong(n), c_float(scale), c_int(2), _st())
+
+
+def cast(src, dtype):
+    dst = torch.empty(src.shape, device=src.device, dtype=dtype)
+    cast_scale(src, dst, 1.0)
+    return dst
+
+
+def colsum_any(x, out, rows, cols):
+    if x.dtype == torch.float32:
+        colsum(x, out, rows, cols)
+    else:
+        _call("ddpx_colsum_bf16", _P(x), _P(out), c_longlong(rows), c_int(cols), _st())
+
+
+def dropout(x, y, p, seed):
+    _call("ddpx_dropout", _P(x), _P(y), c_longlong(x.numel()), c_float(p), ctypes.c_ulonglong(seed), c_int(_bf(x)), _st())
+
+
+def embedding_fwd(idx, wte, wpe, out, BT, T, C):
+    _call("ddpx_embedding_fwd", _P(idx), _P(wte), _P(wpe), _P(out), c_longlong(BT), c_int(T), c_int(C), c_int(_bf(wte)), _st())
+
+
+def embedding_bwd(idx, dy, dwte, dwpe, BT, T, C):
+    _call("ddpx_embedding_bwd", _P(idx), _P(dy), _P(dwte), _P(dwpe), c_longlong(BT), c_int(T), c_int(C), c_int(_bf(dy)), _st())
+
+
+def causal_softmax_fwd(s, rows, T):
+    _call("ddpx_causal_softmax_fwd", _P(s), c_longlong(rows), c_int(T), c_int(_bf(s)), _st())
+
+
+def causal_softmax_bwd(p, dp, rows, T, scale):
+    _call("ddpx_causal_softmax_bwd", _P(p), _P(dp), c_longlong(rows), c_int(T), c_float(scale), c_int(_bf(p)), _st())

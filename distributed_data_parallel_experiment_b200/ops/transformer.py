@@ -1,0 +1,200 @@
+"""autograd Functions for the transformer ops on CUDA (LayerNorm, residual add, embedding, causal attention, padded
+cross-entropy, dropout).  All kernels are the framework's own (csrc/kernels/transformer.cu, attention_aux.cu and the
+batched tcgen05 GEMM); activations may be bf16 or fp32.
+"""
+from __future__ import annotations
+
+import math
+
+import torch
+from torch.autograd import Function
+
+from . import native
+
+
+def _zeros(shape, device, dtype=torch.float32):
+    return native.zero_(torch.empty(shape, device=device, dtype=dtype))
+
+
+def _to_dtype(t32, dtype):
+    return t32 if dtype == torch.float32 else native.cast(t32, dtype)
+
+
+class LayerNormFn(Function):
+    @staticmethod
+    def forward(ctx, x, weight, bias, eps):
+        C = x.shape[-1]
+        x2 = x.reshape(-1, C)
+        if not x2.is_contiguous():
+            x2 = x2.contiguous()
+        rows = x2.shape[0]
+        y = torch.empty_like(x2)
+        stats = torch.empty((2, rows), device=x.device, dtype=torch.float32)
+        native.layernorm_fwd(x2, weight.detach(), bias.detach(), y, stats[0], stats[1], rows, C, eps)
+        ctx.save_for_backward(x2, weight, stats)
+        ctx.shape = x.shape
+        return y.view(x.shape)
+
+    @staticmethod
+    def backward(ctx, dy):
+        x2, weight, stats = ctx.saved_tensors
+        rows, C = x2.shape
+        d = dy.reshape(rows, C)
+        if not d.is_contiguous():
+            d = d.contiguous()
+        dx = torch.empty_like(x2)
+        dgb = _zeros((2, C), x2.device)
+        native.layernorm_bwd(x2, d, weight.detach(), stats[0], stats[1], dx, dgb[0], dgb[1], rows, C)
+        return dx.view(ctx.shape), _to_dtype(dgb[0], weight.dtype), _to_dtype(dgb[1], weight.dtype), None
+
+
+class AddFn(Function):
+    @staticmethod
+    def forward(ctx, a, b):
+        ac = a if a.is_contiguous() else a.contiguous()
+        bc = b if b.is_contiguous() else b.contiguous()
+        out = torch.empty_like(ac)
+        native.add(ac, bc, out)
+        return out
+
+    @staticmethod
+    def backward(ctx, g):
+        return g, g
+
+
+class EmbeddingSumFn(Function):
+    @staticmethod
+    def forward(ctx, idx, wte, wpe):
+        B, T = idx.shape
+        C = wte.shape[1]
+        ic = idx.contiguous()
+        out = torch.empty((B, T, C), device=wte.device, dtype=wte.dtype)
+        native.embedding_fwd(ic, wte.detach(), wpe.detach(), out, B * T, T, C)
+        ctx.save_for_backward(ic)
+        ctx.cfg = (B, T, C, wte.shape[0], wpe.shape[0], wte.dtype)
+        return out
+
+    @staticmethod
+    def backward(ctx, dy):
+        (idx,) = ctx.saved_tensors
+        B, T, C, V, NP, dtype = ctx.cfg
+        d = dy if dy.is_contiguous() else dy.contiguous()
+        dwte = _zeros((V, C), d.device)
+        dwpe = _zeros((NP, C), d.device)
+        native.embedding_bwd(idx, d, dwte, dwpe, B * T, T, C)
+        return None, _to_dtype(dwte, dtype), _to_dtype(dwpe, dtype)
+
+
+class CausalAttentionFn(Function):
+    """softmax(causal(Q K^T / sqrt(d))) V from a packed qkv [B,T,3C] tensor.
+
+    Three stages, all on the framework's kernels: batched tcgen05 GEMM for the scores (tiles above the diagonal are
+    never computed), a causal softmax in place, batched tcgen05 GEMM for P V (K loop cut at the diagonal).  The
+    probabilities are kept for the backward, which is four more batched GEMMs around the softmax backward.
+    """
+
+    @staticmethod
+    def forward(ctx, qkv, n_head):
+        B, T, C3 = qkv.shape
+        C = C3 // 3
+        hd = C // n_head
+        q3 = qkv if qkv.is_contiguous() else qkv.contiguous()
+        scale = 1.0 / math.sqrt(hd)
+        BH = B * n_head
+        P = torch.empty((B, n_head, T, T), device=qkv.device, dtype=qkv.dtype)
+        q = q3.view(-1)
+        k = q[C:]
+        v = q[2 * C:]
+        in_bs = (hd, T * C3)                 # batch1 = head (stride hd), batch2 = batch (stride T*3C)
+        # S[b,h] = scale * Q K^T : A = Q [T, hd] (ld 3C), B = K [T, hd] (ld 3C), both K-major
+        native.gemm_batched(q, k, P, T, T, hd, C3, C3, T, 0, 0, n_head, B, in_bs, in_bs, (T * T, n_head * T * T),
+                            alpha=scale, causal=1)
+        native.causal_softmax_fwd(P, BH * T, T)
+        # O[b,t,h,:] = P V : A = P [T, T] K-major, B = V stored [T(k)][hd] -> MN-major; output into [B,T,C]
+        out = torch.empty((B, T, C), device=qkv.device, dtype=qkv.dtype)
+        native.gemm_batched(P, v, out, T, hd, T, T, C3, C, 0, 1, n_head, B, (T * T, n_head * T * T), in_bs, (hd, T * C),
+                            causal=2)
+        ctx.save_for_backward(q3, P)
+        ctx.cfg = (B, T, C, n_head, hd, scale)
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        q3, P = ctx.saved_tensors
+        B, T, C, n_head, hd, scale = ctx.cfg
+        C3 = 3 * C
+        do = dout if dout.is_contiguous() else dout.contiguous()
+        flat = q3.view(-1)
+        q, k, v = flat, flat[C:], flat[2 * C:]
+        dqkv = torch.empty_like(q3)
+        dflat = dqkv.view(-1)
+        dq, dk, dv = dflat, dflat[C:], dflat[2 * C:]
+        in_bs = (hd, T * C3)
+        p_bs = (T * T, n_head * T * T)
+        o_bs = (hd, T * C)
+        # dV[b,k,h,:] = P^T dO : A = P as [K=t_q][M=t_k] (MN-major), B = dO [K=t_q][N=hd] (MN-major)
+        native.gemm_batched(P, do.view(-1), dv, T, hd, T, T, C, C3, 1, 1, n_head, B, p_bs, o_bs, in_bs)
+        # dP = dO V^T : A = dO [T, hd] K-major (ld C), B = V [T, hd] K-major (ld 3C)
+        dP = torch.empty_like(P)
+        native.gemm_batched(do.view(-1), v, dP, T, T, hd, C, C3, T, 0, 0, n_head, B, o_bs, in_bs, p_bs, causal=1)
+        # dS = P * (dP - rowsum(dP * P)) * scale   (in place, zeros above the diagonal)
+        native.causal_softmax_bwd(P, dP, B * n_head * T, T, scale)
+        # dQ = dS K : A = dS [T, T] K-major, B = K stored [T(k)][hd] -> MN-major
+        native.gemm_batched(dP, k, dq, T, hd, T, T, C3, C3, 0, 1, n_head, B, p_bs, in_bs, in_bs, causal=2)
+        # dK = dS^T Q : A = dS as [K=t_q][M=t_k] (MN-major), B = Q [K=t_q][N=hd] (MN-major)
+        native.gemm_batched(dP, q, dk, T, hd, T, T, C3, C3, 1, 1, n_head, B, p_bs, in_bs, in_bs)
+        return dqkv, None
+
+
+class PaddedCrossEntropyFn(Function):
+    """Mean cross-entropy over the first ``vocab`` columns of [.., V_padded] logits; the gradient of the padding columns
+    is zero.  Loss and dlogits come from one fused kernel that reads the logits once."""
+
+    @staticmethod
+    def forward(ctx, logits, targets, vocab):
+        Vp = logits.shape[-1]
+        l2 = logits.reshape(-1, Vp)
+        if not l2.is_contiguous():
+            l2 = l2.contiguous()
+        rows = l2.shape[0]
+        t = targets.reshape(-1).contiguous()
+        loss = torch.empty(1, device=logits.device, dtype=torch.float32)
+        dl = None
+        if ctx.needs_input_grad[0]:
+            dl = torch.empty_like(l2)
+            if Vp != vocab:
+                native.zero_(dl)
+        native.softmax_ce(l2, t, dl, loss, rows, vocab, Vp)
+        ctx.save_for_backward(dl)
+        ctx.shape = logits.shape
+        return loss[0]
+
+    @staticmethod
+    def backward(ctx, g):
+        (dl,) = ctx.saved_tensors
+        if dl is None:
+            return None, None, None
+        native.scale_by_device_scalar(dl, g.float().contiguous() if g.dtype != torch.float32 else g.contiguous())
+        return dl.view(ctx.shape), None, None
+
+
+class DropoutFn(Function):
+    _counter = 0
+
+    @staticmethod
+    def forward(ctx, x, p):
+        xc = x if x.is_contiguous() else x.contiguous()
+        DropoutFn._counter += 1
+        seed = (int(torch.initial_seed()) * 1000003 + DropoutFn._counter) & 0xFFFFFFFFFFFF
+        y = torch.empty_like(xc)
+        native.dropout(xc, y, p, seed)
+        ctx.cfg = (p, seed)
+        return y
+
+    @staticmethod
+    def backward(ctx, g):
+        p, seed = ctx.cfg
+        gc = g if g.is_contiguous() else g.contiguous()
+        dx = torch.empty_like(gc)
+        native.dropout(gc, dx, p, seed)       # same mask (counter-based RNG), same 1/(1-p) scale
+        return dx, None

@@ -87,7 +87,8 @@ def fuse(optimizer: torch.optim.Optimizer) -> torch.optim.Optimizer:
     if getattr(optimizer, "_ddpx_fused", False) or not supported(optimizer):
         return optimizer
     ps = [p for g in optimizer.param_groups for p in g["params"]]
-    if not ps or not all(p.is_cuda and p.dtype == torch.float32 for p in ps):
+    dtypes = {p.dtype for p in ps}
+    if not ps or not all(p.is_cuda for p in ps) or len(dtypes) != 1 or dtypes.pop() not in (torch.float32, torch.bfloat16):
         return optimizer
     inner = _native_step_sgd if type(optimizer) is torch.optim.SGD else _native_step_adamw
     orig_step = optimizer.step

@@ -55,6 +55,13 @@ int ddpx_conv3x3_fprop(const float* x, const float* wpacked, float* y, int Nimg,
                        const float* bias, int act, float* stat_sum, float* stat_sq, void* stream);
 int ddpx_conv3x3_wgrad(const float* dy, const float* x, float* dw, int Nimg, int H, int W, int Cin, int Cout,
                        int split_k, void* stream);
+/* RGB stem on tensor cores (M:53 conv0, K = 27 padded to 32): patches[P][32] = im2col(x_nchw); forward =
+ * ddpx_conv1x1_fprop(patches, wp[Cout][32]) with the same epilogue as the 3x3 kernel; weight gradient =
+ * ddpx_gemm(dy^T, patches) with split-K. */
+int ddpx_im2col_stem(const float* x_nchw, float* patches, int Nimg, int H, int W, void* stream);
+int ddpx_pack_stem_weights(const float* w, float* wp, int Cout, void* stream);
+int ddpx_conv1x1_fprop(const float* x, const float* wpacked, float* y, int Nimg, int H, int W, int Cin, int Cout,
+                       const float* bias, int act, float* stat_sum, float* stat_sq, void* stream);
 
 
 /* ---- convolution helpers (csrc/kernels/conv_aux.cu) ---------------------------------------- */
@@ -104,10 +111,31 @@ int ddpx_mse(const float* pred, const float* target, float* dpred, float* loss_s
 /* one launch for all tensors; torch SGD / AdamW semantics (M:97, torch/optim/sgd.py:346-380) */
 int ddpx_sgd_multi(int n, void* const* params, void* const* grads, void* const* momentum_bufs, const long long* numel,
                    float lr, float momentum, float dampening, float weight_decay, int nesterov, int first_step,
-                   float grad_scale, void* stream);
+                   float grad_scale, int is_bf16, void* stream);
 int ddpx_adamw_multi(int n, void* const* params, void* const* grads, void* const* exp_avg, void* const* exp_avg_sq,
                      const long long* numel, float lr, float beta1, float beta2, float eps, float weight_decay,
-                     long long step, float grad_scale, void* stream);
+                     long long step, float grad_scale, int is_bf16, void* stream);
+
+/* ---- transformer kernels (csrc/kernels/transformer.cu, attention_aux.cu) -----------------------
+ * No counterpart in the reference (a CNN); required by the MLP / GPT-2 configs of BASELINE.json.
+ * is_bf16 selects the storage type of the activations/parameters (math is fp32). */
+int ddpx_layernorm_fwd(const void* x, const void* gamma, const void* beta, void* y, float* mean, float* rstd,
+                       long long rows, int C, float eps, int is_bf16, void* stream);
+int ddpx_layernorm_bwd(const void* x, const void* dy, const void* gamma, const float* mean, const float* rstd, void* dx,
+                       float* dgamma, float* dbeta, long long rows, int C, int is_bf16, void* stream);
+int ddpx_gelu_fwd(const void* x, void* y, long long n, int is_bf16, void* stream);
+int ddpx_gelu_bwd(const void* x, const void* dy, void* dx, long long n, int is_bf16, void* stream);
+int ddpx_relu_bwd_bf16(const void* y, const void* dy, void* dx, long long n, void* stream);
+int ddpx_add(const void* a, const void* b, void* out, long long n, int is_bf16, void* stream);
+int ddpx_cast_scale(const void* src, void* dst, long long n, float scale, int kind, void* stream);
+int ddpx_colsum_bf16(const void* x, float* out, long long rows, int cols, void* stream);
+int ddpx_dropout(const void* x, void* y, long long n, float p, unsigned long long seed, int is_bf16, void* stream);
+int ddpx_embedding_fwd(const long long* idx, const void* wte, const void* wpe, void* out, long long BT, int T, int C,
+                       int is_bf16, void* stream);
+int ddpx_embedding_bwd(const long long* idx, const void* dy, float* dwte, float* dwpe, long long BT, int T, int C,
+                       int is_bf16, void* stream);
+int ddpx_causal_softmax_fwd(void* s, long long rows, int T, int is_bf16, void* stream);
+int ddpx_causal_softmax_bwd(const void* p, void* dp, long long rows, int T, float scale, int is_bf16, void* stream);
 
 /* ---- reducer core (csrc/runtime/reducer_core.cpp): host-side bucket assignment + ready/launch state machine ----
  * Counterpart of c10d::compute_bucket_assignment_by_size and the bookkeeping of c10d::Reducer that torch DDP builds
