@@ -1,0 +1,84 @@
+"""Gradient all-reduce bandwidth sweep 1 KB - 1 GB (BASELINE.json config 5): the P2P two-shot kernel vs NCCL on the
+same buffers, device-timed (CUDA events, max over ranks), reported as algorithm and bus bandwidth against the
+900 GB/s-per-direction NVLink 5 figure (measured peer copy on this pool: 770 GB/s, B200_PROFILING.md).
+
+    python bench/allreduce_sweep.py --gpus 2 [--max-mb 1024] [--dtype fp32|bf16] [--ctas 32,64]
+Writes one JSON line per (size, impl) on rank 0.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import sys
+from pathlib import Path
+
+sys.path.insert(0, str(Path(__file__).resolve().parent.parent))
+
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+
+def _time(fn, iters, world):
+    for _ in range(3):
+        fn()
+    torch.cuda.synchronize(); dist.barrier()
+    e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(iters):
+        fn()
+    e1.record(); torch.cuda.synchronize()
+    t = torch.tensor([e0.elapsed_time(e1) / iters], device="cuda", dtype=torch.float64)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return float(t.item())
+
+
+def worker(rank, world, port, args):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"; os.environ["MASTER_PORT"] = str(port)
+    import distributed_data_parallel_experiment_b200 as ddpx
+    ddpx.ddp_setup(rank, world, backend="p2p")
+    comm = ddpx.launch.get_comm()
+    dtype = torch.float32 if args.dtype == "fp32" else torch.bfloat16
+    es = 4 if dtype == torch.float32 else 2
+    size = 1024
+    results = []
+    while size <= args.max_mb * 1024 * 1024:
+        n = max(8, size // es // 8 * 8)
+        buf = comm.alloc(n, dtype, None)
+        buf.normal_()
+        ref = torch.empty(n, dtype=dtype, device="cuda").normal_()
+        iters = 50 if size <= (1 << 22) else (10 if size <= (1 << 28) else 4)
+        for ctas in args.ctas:
+            comm.ctas = ctas
+            ms = _time(lambda: comm.all_reduce_sum_(buf, async_op=False), iters, world)
+            algbw = size / ms / 1e6
+            results.append({"impl": "p2p_twoshot", "ctas": ctas, "bytes": size, "us": ms * 1e3, "algbw_gbs": algbw,
+                            "busbw_gbs": algbw * 2 * (world - 1) / world})
+        ms = _time(lambda: dist.all_reduce(ref), iters, world)
+        algbw = size / ms / 1e6
+        results.append({"impl": "nccl", "ctas": None, "bytes": size, "us": ms * 1e3, "algbw_gbs": algbw,
+                        "busbw_gbs": algbw * 2 * (world - 1) / world})
+        size *= 4
+    if rank == 0:
+        for r in results:
+            r.update({"world": world, "dtype": args.dtype, "frac_of_900": r["busbw_gbs"] / 900.0})
+            print(json.dumps(r), flush=True)
+    ddpx.teardown()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=2)
+    ap.add_argument("--max-mb", type=int, default=1024)
+    ap.add_argument("--dtype", default="fp32")
+    ap.add_argument("--ctas", default="32")
+    args = ap.parse_args()
+    args.ctas = [int(c) for c in args.ctas.split(",")]
+    import socket
+    s = socket.socket(); s.bind(("127.0.0.1", 0)); port = s.getsockname()[1]; s.close()
+    mp.spawn(worker, args=(args.gpus, port, args), nprocs=args.gpus, join=True)
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,394 @@
+// Peer-to-peer communication backend over NVLink 5 / NVSwitch, sm_100a.
+//
+// Replaces ProcessGroupNCCL (ncclAllReduce / ncclBroadcast) that torch DDP drives for the reference at
+// /root/reference/multigpu.py:32,89 (W6-W9):
+//   * symmetric buffers: every rank cudaMalloc's the same sizes in the same order and maps every peer's allocation
+//     into its own address space through CUDA IPC handles (exchanged over the control-plane store by the Python side);
+//   * a signal pad per rank (monotonic generation counters written with st.release.sys, polled with ld.acquire.sys);
+//   * ONE kernel per gradient bucket that does all-reduce (two-shot: reduce-scatter by peer loads + all-gather by peer
+//     stores; one-shot for small buckets) AND the optimizer update (SGD-momentum or AdamW) of the parameters the bucket
+//     covers - no NCCL call and no separate elementwise kernel on that path;
+//   * a pull-based broadcast (rank 0 packs tensors into its staging buffer, peers copy them out over NVLink) used for
+//     the initial parameter sync and the per-forward BatchNorm-buffer sync.
+// Every spin is bounded: after ~20 s a rank writes an error code into its pad and traps instead of hanging the box.
+#include <cuda_runtime.h>
+#include <cuda_bf16.h>
+#include <stdint.h>
+#include <string.h>
+#include "../../include/ddpx_kernels.h"
+
+namespace {
+
+constexpr int kMaxRanks = 8;
+constexpr int kMaxSlots = 128;
+// signal-pad layout (uint32 words)
+constexpr int PAD_ARRIVE = 0;     // [8]  peer r's bucket is filled for generation g
+constexpr int PAD_DONE = 8;       // [8]  peer r finished reducing + distributing its shard for generation g
+constexpr int PAD_EXIT = 16;      // [8]  peer r finished reading everybody's bucket (one-shot)
+constexpr int PAD_BCAST = 24;     // [1]  source finished packing broadcast generation g
+constexpr int PAD_ACK = 32;       // [8]  peer r consumed broadcast generation g   (lives on the source's pad)
+constexpr int PAD_ERROR = 48;     // [1]  non-zero after a timed-out wait
+constexpr int PAD_COUNTER = 56;   // [4]  local CTA-arrival counters (never touched by peers)
+constexpr unsigned long long kTimeoutNs = 20ull * 1000ull * 1000ull * 1000ull;
+
+__device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
+  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ unsigned long long globaltimer() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+// wait until *flag >= gen (wrap-safe signed compare); bounded
+__device__ __forceinline__ void wait_flag(uint32_t* flag, uint32_t gen, uint32_t* pad, uint32_t code) {
+  if (static_cast<int32_t>(ld_acquire_sys(flag) - gen) >= 0) return;
+  const unsigned long long t0 = globaltimer();
+  while (static_cast<int32_t>(ld_acquire_sys(flag) - gen) < 0) {
+    __nanosleep(64);
+    if (globaltimer() - t0 > kTimeoutNs) {
+      pad[PAD_ERROR] = code;
+      __threadfence_system();
+      asm volatile("trap;");
+    }
+  }
+}
+
+struct Peers {
+  void* buf[kMaxRanks];        // every rank's copy of the symmetric buffer, indexed by rank (buf[rank] is local)
+  uint32_t* pad[kMaxRanks];    // every rank's signal pad
+  int rank, world;
+};
+
+struct Slot {
+  void* param;
+  void* state0;     // SGD momentum buffer / AdamW exp_avg
+  void* state1;     // AdamW exp_avg_sq
+  long long offset; // element offset inside the bucket
+  long long numel;
+};
+struct SlotTable {
+  Slot s[kMaxSlots];
+  int n;
+};
+struct Hyper {
+  int opt;          // 0 none (just all-reduce), 1 SGD, 2 AdamW
+  float lr, momentum, dampening, wd;
+  int nesterov, first_step;
+  float beta1, beta2, eps, bc1, bc2_sqrt;
+};
+
+template <typename T> struct Vec;
+template <> struct Vec<float> { static constexpr int N = 4; };
+template <> struct Vec<__nv_bfloat16> { static constexpr int N = 8; };
+
+template <typename T> __device__ __forceinline__ void unpack(const uint4& u, float* f);
+template <> __device__ __forceinline__ void unpack<float>(const uint4& u, float* f) {
+  f[0] = __uint_as_float(u.x); f[1] = __uint_as_float(u.y); f[2] = __uint_as_float(u.z); f[3] = __uint_as_float(u.w);
+}
+template <> __device__ __forceinline__ void unpack<__nv_bfloat16>(const uint4& u, float* f) {
+  const uint32_t w[4] = {u.x, u.y, u.z, u.w};
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    f[2 * i] = __uint_as_float(w[i] << 16);
+    f[2 * i + 1] = __uint_as_float(w[i] & 0xffff0000u);
+  }
+}
+template <typename T> __device__ __forceinline__ uint4 pack(const float* f);
+template <> __device__ __forceinline__ uint4 pack<float>(const float* f) {
+  return make_uint4(__float_as_uint(f[0]), __float_as_uint(f[1]), __float_as_uint(f[2]), __float_as_uint(f[3]));
+}
+template <> __device__ __forceinline__ uint4 pack<__nv_bfloat16>(const float* f) {
+  uint32_t w[4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    __nv_bfloat162 h = __floats2bfloat162_rn(f[2 * i], f[2 * i + 1]);
+    w[i] = *reinterpret_cast<uint32_t*>(&h);
+  }
+  return make_uint4(w[0], w[1], w[2], w[3]);
+}
+template <typename T> __device__ __forceinline__ float ldT(const T* p);
+template <> __device__ __forceinline__ float ldT<float>(const float* p) { return *p; }
+template <> __device__ __forceinline__ float ldT<__nv_bfloat16>(const __nv_bfloat16* p) { return __bfloat162float(*p); }
+template <typename T> __device__ __forceinline__ void stT(T* p, float v);
+template <> __device__ __forceinline__ void stT<float>(float* p, float v) { *p = v; }
+template <> __device__ __forceinline__ void stT<__nv_bfloat16>(__nv_bfloat16* p, float v) { *p = __float2bfloat16(v); }
+
+// grid-wide "everybody finished the previous phase": the last CTA to arrive runs `then` (one thread)
+template <typename F>
+__device__ __forceinline__ void last_cta_does(uint32_t* counter, F then) {
+  __threadfence_system();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const unsigned int old = atomicAdd(counter, 1u);
+    if (old == gridDim.x - 1) {
+      *counter = 0;
+      __threadfence_system();
+      then();
+    }
+  }
+}
+
+// optimizer update of one element (torch SGD / AdamW semantics, see loss_optim.cu)
+template <typename T>
+__device__ __forceinline__ void apply_update(const Hyper& h, const Slot& s, long long j, float g) {
+  T* p = static_cast<T*>(s.param) + j;
+  float pv = ldT(p);
+  if (h.opt == 1) {
+    float gv = g + h.wd * pv;
+    if (h.momentum != 0.f) {
+      T* b = static_cast<T*>(s.state0) + j;
+      const float bv = h.first_step ? gv : h.momentum * ldT(b) + (1.f - h.dampening) * gv;
+      stT(b, bv);
+      gv = h.nesterov ? gv + h.momentum * bv : bv;
+    }
+    stT(p, pv - h.lr * gv);
+  } else {
+    T* m = static_cast<T*>(s.state0) + j;
+    T* v = static_cast<T*>(s.state1) + j;
+    pv *= (1.f - h.lr * h.wd);
+    const float mv = h.beta1 * ldT(m) + (1.f - h.beta1) * g;
+    const float vv = h.beta2 * ldT(v) + (1.f - h.beta2) * g * g;
+    stT(m, mv);
+    stT(v, vv);
+    stT(p, pv - (h.lr / h.bc1) * mv / (sqrtf(vv) / h.bc2_sqrt + h.eps));
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// fused all-reduce (+ optimizer).  n = bucket elements (multiple of the vector width).
+// mode 0 = two-shot, mode 1 = one-shot (requires opt != 0: the local bucket is not rewritten)
+// ------------------------------------------------------------------------------------------------
+template <typename T>
+__global__ void __launch_bounds__(512)
+allreduce_fused_kernel(const Peers P, const uint32_t gen, const long long n, const int mode, const Hyper h,
+                       const __grid_constant__ SlotTable slots) {
+  constexpr int V = Vec<T>::N;
+  uint32_t* pad = P.pad[P.rank];
+  const long long nvec = n / V;
+  // ---- 1. announce "my bucket holds generation gen", wait for every peer's announcement
+  if (blockIdx.x == 0 && threadIdx.x < P.world) st_release_sys(P.pad[threadIdx.x] + PAD_ARRIVE + P.rank, gen);
+  if (threadIdx.x < P.world) wait_flag(pad + PAD_ARRIVE + threadIdx.x, gen, pad, 0xA1000000u | threadIdx.x);
+  __syncthreads();
+
+  if (mode == 0) {
+    // ---- 2. reduce my shard from every rank's bucket (fixed rank order => identical bits everywhere),
+    //         store it into every rank's bucket
+    const long long per = (nvec + P.world - 1) / P.world;
+    const long long v0 = per * P.rank, v1 = min(v0 + per, nvec);
+    for (long long i = v0 + static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < v1;
+         i += static_cast<long long>(gridDim.x) * blockDim.x) {
+      float acc[V];
+#pragma unroll
+      for (int k = 0; k < V; ++k) acc[k] = 0.f;
+#pragma unroll 1
+      for (int r = 0; r < P.world; ++r) {
+        const uint4 u = reinterpret_cast<const uint4*>(P.buf[r])[i];
+        float f[V];
+        unpack<T>(u, f);
+#pragma unroll
+        for (int k = 0; k < V; ++k) acc[k] += f[k];
+      }
+      const uint4 o = pack<T>(acc);
+#pragma unroll 1
+      for (int r = 0; r < P.world; ++r) reinterpret_cast<uint4*>(P.buf[r])[i] = o;
+    }
+    // ---- 3. when the whole grid is done with the shard, tell every peer
+    last_cta_does(pad + PAD_COUNTER, [&] {
+      for (int r = 0; r < P.world; ++r) st_release_sys(P.pad[r] + PAD_DONE + P.rank, gen);
+    });
+    // ---- 4. wait until every shard of my bucket has been delivered
+    if (threadIdx.x < P.world) wait_flag(pad + PAD_DONE + threadIdx.x, gen, pad, 0xA2000000u | threadIdx.x);
+    __syncthreads();
+    // ---- 5. optimizer update of every parameter slot of the bucket from the (now averaged) local bucket
+    if (h.opt != 0) {
+      const T* g = static_cast<const T*>(P.buf[P.rank]);
+      for (int si = 0; si < slots.n; ++si) {
+        const Slot& s = slots.s[si];
+        for (long long j = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; j < s.numel;
+             j += static_cast<long long>(gridDim.x) * blockDim.x)
+          apply_update<T>(h, s, j, ldT(g + s.offset + j));
+      }
+    }
+  } else {
+    // ---- one-shot: every rank reduces the whole bucket from peer memory and updates its replica directly
+    for (int si = 0; si < slots.n; ++si) {
+      const Slot& s = slots.s[si];
+      for (long long j = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; j < s.numel;
+           j += static_cast<long long>(gridDim.x) * blockDim.x) {
+        float acc = 0.f;
+#pragma unroll 1
+        for (int r = 0; r < P.world; ++r) acc += ldT(static_cast<const T*>(P.buf[r]) + s.offset + j);
+        apply_update<T>(h, s, j, acc);
+      }
+    }
+    // exit barrier: nobody may refill its bucket before every peer finished reading it
+    last_cta_does(pad + PAD_COUNTER, [&] {
+      for (int r = 0; r < P.world; ++r) st_release_sys(P.pad[r] + PAD_EXIT + P.rank, gen);
+    });
+    if (threadIdx.x < P.world) wait_flag(pad + PAD_EXIT + threadIdx.x, gen, pad, 0xA3000000u | threadIdx.x);
+    __syncthreads();
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// broadcast (pull model).  Source: pack tensors into its staging slot, publish.  Others: wait, copy out of the source's
+// staging (peer loads), acknowledge.  Table entries: {tensor ptr, byte offset in staging, bytes} (16-byte granules).
+// ------------------------------------------------------------------------------------------------
+struct CopyEntry { void* ptr; long long offset; long long bytes; };
+struct CopyTable { CopyEntry e[kMaxSlots]; int n; };
+
+__device__ __forceinline__ void copy_bytes(uint8_t* dst, const uint8_t* src, long long bytes) {
+  const long long tid = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  const long long nth = static_cast<long long>(gridDim.x) * blockDim.x;
+  if (((reinterpret_cast<uintptr_t>(dst) | reinterpret_cast<uintptr_t>(src)) & 15) == 0) {
+    const long long nv = bytes / 16;
+    for (long long i = tid; i < nv; i += nth) reinterpret_cast<uint4*>(dst)[i] = reinterpret_cast<const uint4*>(src)[i];
+    for (long long i = nv * 16 + tid; i < bytes; i += nth) dst[i] = src[i];
+  } else {
+    for (long long i = tid; i < bytes; i += nth) dst[i] = src[i];
+  }
+}
+
+__global__ void __launch_bounds__(512)
+bcast_src_kernel(const Peers P, const uint32_t gen, uint8_t* staging, const __grid_constant__ CopyTable tab) {
+  uint32_t* pad = P.pad[P.rank];
+  // the staging slot was last used two generations ago: wait until every peer consumed that one
+  if (gen >= 2 && threadIdx.x < P.world && static_cast<int>(threadIdx.x) != P.rank)
+    wait_flag(pad + PAD_ACK + threadIdx.x, gen - 2, pad, 0xB1000000u | threadIdx.x);
+  __syncthreads();
+  for (int i = 0; i < tab.n; ++i)
+    copy_bytes(staging + tab.e[i].offset, static_cast<const uint8_t*>(tab.e[i].ptr), tab.e[i].bytes);
+  last_cta_does(pad + PAD_COUNTER + 1, [&] {
+    for (int r = 0; r < P.world; ++r)
+      if (r != P.rank) st_release_sys(P.pad[r] + PAD_BCAST, gen);
+  });
+}
+
+__global__ void __launch_bounds__(512)
+bcast_dst_kernel(const Peers P, const int src, const uint32_t gen, const uint8_t* src_staging,
+                 const __grid_constant__ CopyTable tab) {
+  uint32_t* pad = P.pad[P.rank];
+  if (threadIdx.x == 0) wait_flag(pad + PAD_BCAST, gen, pad, 0xB2000000u | src);
+  __syncthreads();
+  for (int i = 0; i < tab.n; ++i)
+    copy_bytes(static_cast<uint8_t*>(tab.e[i].ptr), src_staging + tab.e[i].offset, tab.e[i].bytes);
+  last_cta_does(pad + PAD_COUNTER + 1, [&] { st_release_sys(P.pad[src] + PAD_ACK + P.rank, gen); });
+}
+
+int fill_peers(Peers& P, int rank, int world, void* const* bufs, void* const* pads) {
+  if (world < 1 || world > kMaxRanks || rank < 0 || rank >= world) return DDPX_ERR_ARG;
+  memset(&P, 0, sizeof(P));
+  P.rank = rank; P.world = world;
+  for (int r = 0; r < world; ++r) {
+    P.buf[r] = bufs ? bufs[r] : nullptr;
+    P.pad[r] = static_cast<uint32_t*>(pads[r]);
+  }
+  return DDPX_OK;
+}
+
+}  // namespace
+
+#define CUDA_OK(x) ((x) == cudaSuccess ? DDPX_OK : DDPX_ERR_LAUNCH)
+
+// ---- memory + IPC ---------------------------------------------------------------------------------
+extern "C" int ddpx_p2p_malloc(void** out, long long bytes) {
+  void* p = nullptr;
+  if (cudaMalloc(&p, static_cast<size_t>(bytes)) != cudaSuccess) return DDPX_ERR_LAUNCH;
+  if (cudaMemset(p, 0, static_cast<size_t>(bytes)) != cudaSuccess) return DDPX_ERR_LAUNCH;
+  cudaDeviceSynchronize();
+  *out = p;
+  return DDPX_OK;
+}
+extern "C" int ddpx_p2p_free(void* p) { return CUDA_OK(cudaFree(p)); }
+extern "C" int ddpx_p2p_export(void* p, unsigned char* handle64) {
+  cudaIpcMemHandle_t h;
+  if (cudaIpcGetMemHandle(&h, p) != cudaSuccess) return DDPX_ERR_DRIVER;
+  memcpy(handle64, &h, sizeof(h));
+  return DDPX_OK;
+}
+extern "C" int ddpx_p2p_import(const unsigned char* handle64, void** out) {
+  cudaIpcMemHandle_t h;
+  memcpy(&h, handle64, sizeof(h));
+  void* p = nullptr;
+  cudaError_t e = cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess);
+  if (e != cudaSuccess) return DDPX_ERR_DRIVER;
+  *out = p;
+  return DDPX_OK;
+}
+extern "C" int ddpx_p2p_unimport(void* p) { return CUDA_OK(cudaIpcCloseMemHandle(p)); }
+extern "C" int ddpx_p2p_can_access(int dev, int peer) {
+  int ok = 0;
+  if (cudaDeviceCanAccessPeer(&ok, dev, peer) != cudaSuccess) return 0;
+  return ok;
+}
+extern "C" unsigned int ddpx_p2p_read_error(void* pad) {
+  uint32_t v = 0;
+  cudaMemcpy(&v, static_cast<uint32_t*>(pad) + PAD_ERROR, sizeof(v), cudaMemcpyDeviceToHost);
+  return v;
+}
+
+// ---- collectives -----------------------------------------------------------------------------------
+// slots: arrays of length nslots (param / state0 / state1 pointers, element offsets, element counts); may be 0 slots
+// when opt == 0.  hyper: [lr, momentum, dampening, wd, beta1, beta2, eps, bc1, bc2_sqrt].
+extern "C" int ddpx_p2p_allreduce_fused(int rank, int world, void* const* bufs, void* const* pads, unsigned int gen,
+                                        long long n, int is_bf16, int mode, int opt, const float* hyper, int nesterov,
+                                        int first_step, int nslots, void* const* params, void* const* state0,
+                                        void* const* state1, const long long* offsets, const long long* numels, int ctas,
+                                        void* stream) {
+  Peers P;
+  int rc = fill_peers(P, rank, world, bufs, pads);
+  if (rc != DDPX_OK) return rc;
+  if (nslots > kMaxSlots) return DDPX_ERR_LIMIT;
+  if (mode == 1 && opt == 0) return DDPX_ERR_ARG;
+  const int vec = is_bf16 ? 8 : 4;
+  if (n % vec) return DDPX_ERR_ALIGN;
+  static SlotTable tab;   // filled per call; passed by value
+  memset(&tab, 0, sizeof(tab));
+  tab.n = nslots;
+  for (int i = 0; i < nslots; ++i) {
+    tab.s[i].param = params[i];
+    tab.s[i].state0 = state0 ? state0[i] : nullptr;
+    tab.s[i].state1 = state1 ? state1[i] : nullptr;
+    tab.s[i].offset = offsets[i];
+    tab.s[i].numel = numels[i];
+  }
+  Hyper h;
+  memset(&h, 0, sizeof(h));
+  h.opt = opt;
+  if (opt != 0) {
+    h.lr = hyper[0]; h.momentum = hyper[1]; h.dampening = hyper[2]; h.wd = hyper[3];
+    h.beta1 = hyper[4]; h.beta2 = hyper[5]; h.eps = hyper[6]; h.bc1 = hyper[7]; h.bc2_sqrt = hyper[8];
+    h.nesterov = nesterov; h.first_step = first_step;
+  }
+  if (ctas < 1) ctas = 1;
+  if (ctas > 148) ctas = 148;
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  if (is_bf16) allreduce_fused_kernel<__nv_bfloat16><<<ctas, 512, 0, s>>>(P, gen, n, mode, h, tab);
+  else allreduce_fused_kernel<float><<<ctas, 512, 0, s>>>(P, gen, n, mode, h, tab);
+  return CUDA_OK(cudaGetLastError());
+}
+
+// broadcast one chunk: `ptrs[i]` (bytes[i] long) <-> staging offset offs[i].  is_src selects the role.
+extern "C" int ddpx_p2p_broadcast(int rank, int world, void* const* pads, int src, unsigned int gen, void* staging_of_src,
+                                  int n, void* const* ptrs, const long long* offs, const long long* bytes, int ctas,
+                                  void* stream) {
+  Peers P;
+  int rc = fill_peers(P, rank, world, nullptr, pads);
+  if (rc != DDPX_OK) return rc;
+  if (n > kMaxSlots) return DDPX_ERR_LIMIT;
+  static CopyTable tab;
+  memset(&tab, 0, sizeof(tab));
+  tab.n = n;
+  for (int i = 0; i < n; ++i) { tab.e[i].ptr = ptrs[i]; tab.e[i].offset = offs[i]; tab.e[i].bytes = bytes[i]; }
+  if (ctas < 1) ctas = 1;
+  if (ctas > 148) ctas = 148;
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  if (rank == src) bcast_src_kernel<<<ctas, 512, 0, s>>>(P, gen, static_cast<uint8_t*>(staging_of_src), tab);
+  else bcast_dst_kernel<<<ctas, 512, 0, s>>>(P, src, gen, static_cast<const uint8_t*>(staging_of_src), tab);
+  return CUDA_OK(cudaGetLastError());
+}

@@ -100,6 +100,7 @@ def fuse(optimizer: torch.optim.Optimizer) -> torch.optim.Optimizer:
             with torch.enable_grad():
                 loss = closure()
         if getattr(self, "_ddpx_skip_step", False):     # the fused all-reduce kernel already applied this update
+            self._ddpx_skip_step = False
             return loss
         inner(self)
         return loss

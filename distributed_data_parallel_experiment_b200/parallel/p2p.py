@@ -1,0 +1,358 @@
+"""Peer-to-peer NVLink communication backend (Python side of csrc/runtime/p2p.cu).
+
+One process per GPU.  ``P2PComm`` owns
+* a signal pad and a double-slot staging buffer in *symmetric* memory (same allocation sequence on every rank, every
+  peer's copy mapped locally through CUDA IPC handles exchanged over the torch.distributed control plane);
+* a high-priority communication stream on which the fused all-reduce(+optimizer) kernels run so they overlap backward;
+* two monotonically increasing generation counters (all-reduce, broadcast) that stand in for barriers.
+
+``FusedUpdate`` binds a stock ``torch.optim.SGD`` / ``AdamW`` to the reducer: each bucket's kernel averages the gradients
+over peer memory AND applies the optimizer update to the parameters of that bucket, after which ``optimizer.step()`` is
+a no-op for that iteration.
+"""
+from __future__ import annotations
+
+import ctypes
+import math
+from typing import List, Optional, Sequence
+
+import torch
+import torch.distributed as dist
+
+from .. import _lib, config
+from .comm import CommBase
+
+ONESHOT_MAX_BYTES = 256 * 1024
+_MAX_SLOTS = 128
+
+
+class _RawCuda:
+    """Expose a raw device allocation to torch through __cuda_array_interface__ (no copy, no ownership)."""
+
+    def __init__(self, ptr: int, nbytes: int):
+        self.__cuda_array_interface__ = {"shape": (nbytes,), "typestr": "|u1", "data": (ptr, False), "version": 3,
+                                         "strides": None}
+
+
+class SymBuf:
+    __slots__ = ("local", "ptrs", "nbytes", "tensor")
+
+    def __init__(self, local, ptrs, nbytes, tensor):
+        self.local, self.ptrs, self.nbytes, self.tensor = local, ptrs, nbytes, tensor
+
+
+class _EventHandle:
+    def __init__(self, ev):
+        self.ev = ev
+
+    def wait(self):
+        torch.cuda.current_stream().wait_event(self.ev)
+
+
+def _cvoidp_array(vals: Sequence[int]):
+    arr = (ctypes.c_void_p * max(1, len(vals)))()
+    for i, v in enumerate(vals):
+        arr[i] = v
+    return arr
+
+
+class P2PComm(CommBase):
+    name = "p2p"
+    supports_fused_update = True
+    needs_double_buffer = False
+
+    def __init__(self, staging_mb: int = 64):
+        super().__init__()
+        if not torch.cuda.is_available():
+            raise RuntimeError("P2PComm needs CUDA")
+        self.device = torch.device("cuda", torch.cuda.current_device())
+        self.lib = _lib.lib()
+        self.cfg = config.get()
+        self._bufs: List[SymBuf] = []
+        self._by_ptr = {}
+        if self.world_size > 8:
+            raise RuntimeError("P2PComm supports up to 8 ranks (one NVSwitch domain)")
+        self.pad = self._sym_alloc(4096)
+        self.slot_bytes = staging_mb * 1024 * 1024
+        self.staging = self._sym_alloc(2 * self.slot_bytes)
+        self.ar_gen = 0
+        self.bc_gen = 0
+        self.stream = torch.cuda.Stream(device=self.device, priority=-1)
+        self.ctas = int(self.cfg.comm_ctas)
+        self._pads_arr = _cvoidp_array(self.pad.ptrs)
+        self.barrier()
+
+    # ------------------------------------------------------------------------------------------ symmetric memory
+    def _sym_alloc(self, nbytes: int) -> SymBuf:
+        nbytes = (int(nbytes) + 255) // 256 * 256
+        p = ctypes.c_void_p()
+        _lib.check(self.lib.ddpx_p2p_malloc(ctypes.byref(p), ctypes.c_longlong(nbytes)), "ddpx_p2p_malloc")
+        handle = (ctypes.c_ubyte * 64)()
+        ptrs = [0] * self.world_size
+        ptrs[self.rank] = p.value
+        if self.world_size > 1:
+            _lib.check(self.lib.ddpx_p2p_export(p, handle), "ddpx_p2p_export")
+            handles = self.all_gather_object(bytes(handle))
+            for r, h in enumerate(handles):
+                if r == self.rank:
+                    continue
+                q = ctypes.c_void_p()
+                hb = (ctypes.c_ubyte * 64).from_buffer_copy(h)
+                _lib.check(self.lib.ddpx_p2p_import(hb, ctypes.byref(q)), f"ddpx_p2p_import(rank {r})")
+                ptrs[r] = q.value
+        t = torch.as_tensor(_RawCuda(p.value, nbytes), device=self.device)
+        sb = SymBuf(p.value, ptrs, nbytes, t)
+        self._bufs.append(sb)
+        self._by_ptr[p.value] = sb
+        return sb
+
+    def alloc(self, numel: int, dtype: torch.dtype, device=None) -> torch.Tensor:
+        """Collective: every rank must call with the same sizes in the same order."""
+        es = torch.empty((), dtype=dtype).element_size()
+        sb = self._sym_alloc(numel * es)
+        return sb.tensor[: numel * es].view(dtype)
+
+    def symbuf_of(self, t: torch.Tensor) -> SymBuf:
+        sb = self._by_ptr.get(t.data_ptr())
+        if sb is None:
+            raise RuntimeError("tensor is not the base of a symmetric allocation")
+        return sb
+
+    # ------------------------------------------------------------------------------------------ all-reduce
+    def _next_ar_gen(self) -> int:
+        self.ar_gen = (self.ar_gen + 1) & 0x7FFFFFFF
+        return self.ar_gen
+
+    def launch_allreduce(self, flat: torch.Tensor, mode: int = 0, opt: int = 0, hyper=None, nesterov=False, first_step=False,
+                         slots=None) -> _EventHandle:
+        """Enqueue the fused kernel for one symmetric flat buffer on the communication stream."""
+        sb = self.symbuf_of(flat)
+        is_bf16 = 1 if flat.dtype == torch.bfloat16 else 0
+        n = flat.numel()
+        gen = self._next_ar_gen()
+        cur = torch.cuda.current_stream()
+        ready = torch.cuda.Event()
+        ready.record(cur)
+        self.stream.wait_event(ready)
+        hy = (ctypes.c_float * 9)(*(hyper or [0.0] * 9))
+        if slots:
+            params, s0, s1, offs, nums = slots
+            ns = len(params)
+        else:
+            params = s0 = s1 = offs = nums = None
+            ns = 0
+        rc = self.lib.ddpx_p2p_allreduce_fused(
+            self.rank, self.world_size, _cvoidp_array(sb.ptrs), self._pads_arr, ctypes.c_uint(gen), ctypes.c_longlong(n),
+            is_bf16, mode, opt, hy, int(nesterov), int(first_step), ns,
+            _cvoidp_array(params) if ns else None, _cvoidp_array(s0) if ns and s0 else None,
+            _cvoidp_array(s1) if ns and s1 else None,
+            (ctypes.c_longlong * max(1, ns))(*(offs or [0])), (ctypes.c_longlong * max(1, ns))(*(nums or [0])),
+            self.ctas, ctypes.c_void_p(self.stream.cuda_stream))
+        _lib.count_launch(1)
+        _lib.check(rc, "ddpx_p2p_allreduce_fused")
+        done = torch.cuda.Event()
+        done.record(self.stream)
+        return _EventHandle(done)
+
+    def all_reduce_sum_(self, flat: torch.Tensor, async_op: bool = True):
+        h = self.launch_allreduce(flat, mode=0, opt=0)
+        if not async_op:
+            h.wait()
+        return h
+
+    # ------------------------------------------------------------------------------------------ broadcast
+    def broadcast_tensors_(self, tensors: Sequence[torch.Tensor], src: int = 0):
+        """In-place broadcast of ``src``'s values of ``tensors`` (any dtypes, contiguous) to every rank."""
+        if self.world_size == 1:
+            return
+        pieces = []        # (ptr, nbytes)
+        for t in tensors:
+            if not t.is_contiguous():
+                raise RuntimeError("broadcast_tensors_: tensors must be contiguous")
+            ptr, nb = t.data_ptr(), t.numel() * t.element_size()
+            while nb > 0:               # split anything larger than a staging slot
+                take = min(nb, self.slot_bytes)
+                pieces.append((ptr, take))
+                ptr += take
+                nb -= take
+        chunk, used = [], 0
+        for ptr, nb in pieces:
+            pad = (nb + 15) // 16 * 16
+            if chunk and (used + pad > self.slot_bytes or len(chunk) >= _MAX_SLOTS):
+                self._bcast_chunk(chunk, src)
+                chunk, used = [], 0
+            chunk.append((ptr, used, nb))
+            used += pad
+        if chunk:
+            self._bcast_chunk(chunk, src)
+
+    def _bcast_chunk(self, chunk, src):
+        self.bc_gen = (self.bc_gen + 1) & 0x7FFFFFFF
+        gen = self.bc_gen
+        n = len(chunk)
+        staging = self.staging.ptrs[src] + (gen & 1) * self.slot_bytes
+        ptrs = _cvoidp_array([c[0] for c in chunk])
+        offs = (ctypes.c_longlong * n)(*[c[1] for c in chunk])
+        nbs = (ctypes.c_longlong * n)(*[c[2] for c in chunk])
+        total = sum(c[2] for c in chunk)
+        ctas = max(1, min(self.ctas, (total + (1 << 16) - 1) >> 16))
+        rc = self.lib.ddpx_p2p_broadcast(self.rank, self.world_size, self._pads_arr, src, ctypes.c_uint(gen),
+                                         ctypes.c_void_p(staging), n, ptrs, offs, nbs, ctas,
+                                         ctypes.c_void_p(torch.cuda.current_stream().cuda_stream))
+        _lib.count_launch(1)
+        _lib.check(rc, "ddpx_p2p_broadcast")
+
+    def broadcast_(self, flat: torch.Tensor, src: int = 0):
+        self.broadcast_tensors_([flat], src)
+
+    # ------------------------------------------------------------------------------------------ misc
+    def error_word(self) -> int:
+        fn = self.lib.ddpx_p2p_read_error
+        fn.restype = ctypes.c_uint
+        return int(fn(ctypes.c_void_p(self.pad.local)))
+
+    def close(self):
+        try:
+            torch.cuda.synchronize()
+            self.barrier()
+        except Exception:
+            pass
+        for sb in self._bufs:
+            for r, q in enumerate(sb.ptrs):
+                if r != self.rank and q:
+                    self.lib.ddpx_p2p_unimport(ctypes.c_void_p(q))
+        try:
+            self.barrier()
+        except Exception:
+            pass
+        for sb in self._bufs:
+            sb.tensor = None
+            self.lib.ddpx_p2p_free(ctypes.c_void_p(sb.local))
+        self._bufs = []
+        self._by_ptr = {}
+
+
+class FusedUpdate:
+    """Per-bucket fused all-reduce + optimizer step on the P2P backend."""
+
+    def __init__(self, comm: P2PComm, params, optimizer, kind: str):
+        self.comm = comm
+        self.params = list(params)
+        self.optimizer = optimizer
+        self.kind = kind                      # "sgd" | "adamw"
+        self.group_of = {}
+        for g in optimizer.param_groups:
+            for p in g["params"]:
+                self.group_of[id(p)] = g
+        self.tables = {}
+        self.modes = {}
+        self.first_step_pending = kind == "sgd"
+        self._steps = 0
+
+    @staticmethod
+    def try_create(comm, params, optimizer) -> Optional["FusedUpdate"]:
+        from .. import optim as _optim
+        if not _optim.supported(optimizer):
+            return None
+        params = list(params)
+        owned = {id(p) for g in optimizer.param_groups for p in g["params"]}
+        if not all(id(p) in owned for p in params):
+            return None
+        dts = {p.dtype for p in params}
+        if len(dts) != 1 or next(iter(dts)) not in (torch.float32, torch.bfloat16):
+            return None
+        if not all(p.is_cuda and p.is_contiguous() for p in params):
+            return None
+        _optim.fuse(optimizer)
+        if not getattr(optimizer, "_ddpx_fused", False):
+            return None
+        kind = "sgd" if type(optimizer) is torch.optim.SGD else "adamw"
+        return FusedUpdate(comm, params, optimizer, kind)
+
+    # state tensors live where optimizer.state_dict() expects them
+    def _ensure_state(self, p):
+        st = self.optimizer.state[p]
+        if self.kind == "sgd":
+            g = self.group_of[id(p)]
+            if float(g["momentum"]) != 0.0 and st.get("momentum_buffer") is None:
+                from ..ops import native
+                st["momentum_buffer"] = native.zero_(torch.empty_like(p, memory_format=torch.preserve_format))
+        else:
+            if len(st) == 0:
+                from ..ops import native
+                st["step"] = torch.tensor(0.0, dtype=torch.float32)
+                st["exp_avg"] = native.zero_(torch.empty_like(p, memory_format=torch.preserve_format))
+                st["exp_avg_sq"] = native.zero_(torch.empty_like(p, memory_format=torch.preserve_format))
+        return st
+
+    def on_buckets_installed(self, reducer):
+        self.tables = {}
+        for b in reducer.buckets:
+            groups = {id(self.group_of[id(self.params[pid])]) for pid in b.param_ids}
+            if len(b.param_ids) > _MAX_SLOTS or len(groups) != 1:
+                self.tables[b.index] = None        # falls back to all-reduce only + optimizer.step()
+                continue
+            ps, s0, s1, offs, nums = [], [], [], [], []
+            for pid, off in zip(b.param_ids, b.offsets):
+                p = self.params[pid]
+                st = self._ensure_state(p)
+                ps.append(p.data_ptr())
+                if self.kind == "sgd":
+                    mb = st.get("momentum_buffer")
+                    s0.append(mb.data_ptr() if mb is not None else 0)
+                    s1.append(0)
+                else:
+                    s0.append(st["exp_avg"].data_ptr())
+                    s1.append(st["exp_avg_sq"].data_ptr())
+                offs.append(off)
+                nums.append(p.numel())
+            self.tables[b.index] = (ps, s0, s1, offs, nums)
+
+    def _hyper(self, group):
+        if self.kind == "sgd":
+            return [float(group["lr"]), float(group["momentum"]), float(group["dampening"]), float(group["weight_decay"]),
+                    0.0, 0.0, 0.0, 1.0, 1.0]
+        b1, b2 = group["betas"]
+        step = self._steps + 1
+        return [float(group["lr"]), 0.0, 0.0, float(group["weight_decay"]), float(b1), float(b2), float(group["eps"]),
+                1.0 - b1 ** step, math.sqrt(1.0 - b2 ** step)]
+
+    def reduce_and_update(self, bucket, buf, parity):
+        tab = self.tables.get(bucket.index)
+        if tab is None:
+            self._unfused = True
+            return self.comm.launch_allreduce(buf, mode=0, opt=0)
+        group = self.group_of[id(self.params[bucket.param_ids[0]])]
+        small = bucket.numel * buf.element_size() <= ONESHOT_MAX_BYTES and self.comm.cfg.allreduce_algo in ("auto", "oneshot")
+        mode = 1 if (small or self.comm.cfg.allreduce_algo == "oneshot") else 0
+        if self.comm.cfg.allreduce_algo == "twoshot":
+            mode = 0
+        self.modes[bucket.index] = mode
+        return self.comm.launch_allreduce(buf, mode=mode, opt=1 if self.kind == "sgd" else 2, hyper=self._hyper(group),
+                                          nesterov=bool(group.get("nesterov", False)),
+                                          first_step=self.first_step_pending, slots=tab)
+
+    def after_backward(self, reducer):
+        """Called once every bucket's kernel has been waited for: mark this iteration's optimizer step as done."""
+        if any(v is None for v in self.tables.values()):
+            # mixed: some buckets were only averaged; expose their gradients and let optimizer.step() handle them
+            for b in reducer.buckets:
+                if self.tables.get(b.index) is None:
+                    for pid, v in zip(b.param_ids, b.views[0]):
+                        self.params[pid].grad = v
+                else:
+                    for pid in b.param_ids:
+                        self.params[pid].grad = None
+            self.first_step_pending = False
+            self._steps += 1
+            return
+        self.first_step_pending = False
+        self._steps += 1
+        for b in reducer.buckets:            # two-shot buckets now hold the averaged gradients: expose them
+            if self.modes.get(b.index) == 0:
+                for pid, v in zip(b.param_ids, b.views[0]):
+                    self.params[pid].grad = v
+        if self.kind == "adamw":
+            for p in self.params:
+                self.optimizer.state[p]["step"] += 1
+        self.optimizer._ddpx_skip_step = True

@@ -34,8 +34,8 @@ class Bucket:
         for pid in self.param_ids:
             self.offsets.append(off)
             n = params[pid].numel()
-            off += (n + 3) // 4 * 4          # keep every slot 16-byte aligned for vector loads
-        self.numel = max(off, 4)
+            off += (n + 7) // 8 * 8          # keep every slot 16-byte aligned for vector loads (fp32 and bf16)
+        self.numel = max(off, 8)
         self.dtype = params[self.param_ids[0]].dtype
         self.size_bytes = sum(params[p].numel() * params[p].element_size() for p in self.param_ids)
         nbuf = 2 if double_buffer else 1

@@ -137,6 +137,28 @@ int ddpx_embedding_bwd(const long long* idx, const void* dy, float* dwte, float*
 int ddpx_causal_softmax_fwd(void* s, long long rows, int T, int is_bf16, void* stream);
 int ddpx_causal_softmax_bwd(const void* p, void* dp, long long rows, int T, float scale, int is_bf16, void* stream);
 
+/* ---- peer-to-peer NVLink backend (csrc/runtime/p2p.cu) ------------------------------------------
+ * Stands where ProcessGroupNCCL stands for the reference (M:32, M:89).
+ * ddpx_p2p_malloc / export / import: symmetric buffers through CUDA IPC (these DO allocate / map memory).
+ * ddpx_p2p_allreduce_fused: one kernel per gradient bucket = all-reduce over peer memory (+ SGD / AdamW update of the
+ *   parameters the bucket covers).  bufs[r] / pads[r] = rank r's bucket / signal pad mapped into this process;
+ *   gen = monotonically increasing collective number (identical on all ranks); mode 0 two-shot, 1 one-shot;
+ *   opt 0 none, 1 SGD, 2 AdamW; hyper = [lr, momentum, dampening, wd, beta1, beta2, eps, bc1, sqrt(bc2)].
+ * ddpx_p2p_broadcast: pull-model broadcast of a chunk of tensors through the source's staging buffer. */
+int ddpx_p2p_malloc(void** out, long long bytes);
+int ddpx_p2p_free(void* p);
+int ddpx_p2p_export(void* p, unsigned char* handle64);
+int ddpx_p2p_import(const unsigned char* handle64, void** out);
+int ddpx_p2p_unimport(void* p);
+int ddpx_p2p_can_access(int dev, int peer);
+unsigned int ddpx_p2p_read_error(void* pad);
+int ddpx_p2p_allreduce_fused(int rank, int world, void* const* bufs, void* const* pads, unsigned int gen, long long n,
+                             int is_bf16, int mode, int opt, const float* hyper, int nesterov, int first_step, int nslots,
+                             void* const* params, void* const* state0, void* const* state1, const long long* offsets,
+                             const long long* numels, int ctas, void* stream);
+int ddpx_p2p_broadcast(int rank, int world, void* const* pads, int src, unsigned int gen, void* staging_of_src, int n,
+                       void* const* ptrs, const long long* offs, const long long* bytes, int ctas, void* stream);
+
 /* ---- reducer core (csrc/runtime/reducer_core.cpp): host-side bucket assignment + ready/launch state machine ----
  * Counterpart of c10d::compute_bucket_assignment_by_size and the bookkeeping of c10d::Reducer that torch DDP builds
  * for the reference at M:89. */

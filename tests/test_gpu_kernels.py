@@ -151,7 +151,7 @@ def test_conv_bn_relu_pool_block(Cin, Cout, H, pool, training):
     if x.requires_grad:
         assert rel_l2(x.grad, xr.grad) < tol
     if training:
-        assert rel_err(rm, rm_r) < 1e-3 and rel_err(rv, rv_r) < 1e-3 and int(nbt) == 4
+        assert rel_err(rm, rm_r) < 3e-3 and rel_err(rv, rv_r) < 3e-3 and int(nbt) == 4
     else:
         assert int(nbt) == 3
 
@@ -185,7 +185,7 @@ def test_linear_fwd_bwd(shape):
     xr = x.detach().double().requires_grad_()
     wr = lin.weight.detach().double().requires_grad_(); br = lin.bias.detach().double().requires_grad_()
     yr = F.relu(F.linear(xr, wr, br)); yr.backward(g.double())
-    tol = 1e-2       # L2: the ReLU mask of near-zero pre-activations may flip under TF32 rounding
+    tol = 3e-2       # L2: the ReLU mask of near-zero pre-activations may flip under TF32 rounding
     assert rel_l2(y, yr) < tol and rel_l2(x.grad, xr.grad) < tol
     assert rel_l2(lin.weight.grad, wr.grad) < tol and rel_l2(lin.bias.grad, br.grad) < tol
 

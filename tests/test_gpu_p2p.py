@@ -1,0 +1,150 @@
+"""T4 / T5: the P2P NVLink backend.  World-size-1 cases run on one GPU (the kernels still go through the signal pad and
+the peer tables); the `multigpu` cases spawn one process per GPU and use NCCL / torch DDP only as the oracle."""
+import os
+import socket
+import sys
+import tempfile
+from pathlib import Path
+
+import pytest
+import torch
+import torch.multiprocessing as mp
+
+REPO = Path(__file__).resolve().parent.parent
+sys.path.insert(0, str(REPO))
+
+import distributed_data_parallel_experiment_b200 as ddpx  # noqa: E402
+
+pytestmark = pytest.mark.gpu
+
+
+def _free_port():
+    s = socket.socket(); s.bind(("127.0.0.1", 0)); p = s.getsockname()[1]; s.close()
+    return p
+
+
+def test_fused_allreduce_sgd_world1_matches_torch():
+    from distributed_data_parallel_experiment_b200.parallel.p2p import P2PComm
+    from distributed_data_parallel_experiment_b200.parallel import DataParallel
+    torch.cuda.set_device(0)
+    torch.manual_seed(0)
+    comm = P2PComm(staging_mb=8)
+    a = torch.nn.Sequential(torch.nn.Linear(64, 300), torch.nn.ReLU(), torch.nn.Linear(300, 10)).cuda()
+    import copy
+    b = copy.deepcopy(a)
+    oa = torch.optim.SGD(a.parameters(), lr=0.1, momentum=0.9, weight_decay=1e-3)
+    ob = torch.optim.SGD(b.parameters(), lr=0.1, momentum=0.9, weight_decay=1e-3)
+    w = DataParallel(a, comm=comm, optimizer=oa, bucket_cap_mb=0.01)
+    assert w.fused is not None
+    for step in range(4):
+        x = torch.randn(32, 64, device="cuda"); y = torch.randint(0, 10, (32,), device="cuda")
+        oa.zero_grad(); torch.nn.functional.cross_entropy(w(x), y).backward(); oa.step()
+        ob.zero_grad(); torch.nn.functional.cross_entropy(b(x), y).backward(); ob.step()
+    torch.cuda.synchronize()
+    assert comm.error_word() == 0
+    for p, q in zip(a.parameters(), b.parameters()):
+        assert torch.allclose(p, q, atol=1e-5, rtol=1e-4)
+    assert w.get_logging_data()["num_buckets"] > 1
+    w.close(); comm.close()
+
+
+# ---------------------------------------------------------------------------------------------- multi-GPU workers
+def _setup(rank, world, port):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    ddpx.config.reset()
+    ddpx.ddp_setup(rank, world, backend="p2p")
+
+
+def _w_collectives(rank, world, port, outdir):
+    _setup(rank, world, port)
+    import torch.distributed as dist
+    comm = ddpx.launch.get_comm()
+    res = {}
+    for dtype in (torch.float32, torch.bfloat16):
+        for n in (8, 1000, 65536, 3_000_000):
+            n8 = (n + 7) // 8 * 8
+            buf = comm.alloc(n8, dtype, None)
+            torch.manual_seed(rank * 7 + n)
+            src = (torch.randn(n8, device="cuda") * 0.5).to(dtype)
+            buf.copy_(src)
+            ref = src.clone().float()
+            dist.all_reduce(ref)                      # NCCL oracle on fp32 copies
+            comm.all_reduce_sum_(buf, async_op=False)
+            torch.cuda.synchronize()
+            tol = 1e-5 if dtype == torch.float32 else 3e-2
+            res[(str(dtype), n)] = ((buf.float() - ref).abs().max() / ref.abs().max().clamp_min(1e-6)).item() < tol
+    # broadcast: tensors of mixed dtypes, one larger than a staging slot piece
+    ts = [torch.full((1000,), float(rank + 1), device="cuda"), torch.full((7,), rank + 1, device="cuda", dtype=torch.int64),
+          torch.full((5_000_000,), float(rank + 1), device="cuda", dtype=torch.bfloat16)]
+    comm.broadcast_tensors_(ts, src=0)
+    torch.cuda.synchronize()
+    res["bcast"] = all(bool((t == 1).all()) for t in ts)
+    res["err"] = comm.error_word()
+    torch.save(res, os.path.join(outdir, f"rank{rank}.pt"))
+    ddpx.teardown()
+
+
+def _w_vgg_parity(rank, world, port, outdir):
+    _setup(rank, world, port)
+    sys.path.insert(0, str(REPO / "baseline" / "_ref"))
+    torch.manual_seed(123 + rank)
+    objs = ddpx.recipes.vgg_train_objs(world_size=world, synthetic=True, synthetic_size=0)
+    for g in objs.optimizer.param_groups:
+        g["initial_lr"] = 0.05
+    sched = torch.optim.lr_scheduler.LambdaLR(objs.optimizer, lambda s: 1.0)
+    # oracle: torch DDP + NCCL on torch's own VGG with the same rank-0 weights
+    import multigpu as ref
+    theirs = ref.VGG().cuda()
+    ours_sd = {k: v.clone() for k, v in objs.model.state_dict().items()}
+    theirs.load_state_dict(ours_sd)
+    t_opt = torch.optim.SGD(theirs.parameters(), lr=0.05, momentum=0.9, weight_decay=5e-4)
+    t_ddp = torch.nn.parallel.DistributedDataParallel(theirs, device_ids=[rank])
+    trainer = ddpx.Trainer(objs.model, [], objs.optimizer, rank, 1, scheduler=sched)
+    fused = trainer.model.fused is not None
+    g = torch.Generator().manual_seed(1000 + rank)
+    losses = []
+    for step in range(4):
+        x = torch.rand(64, 3, 32, 32, generator=g).cuda(); y = torch.randint(0, 10, (64,), generator=g).cuda()
+        losses.append(float(trainer._run_batch(x, y)))
+        t_opt.zero_grad(); torch.nn.functional.cross_entropy(t_ddp(x), y).backward(); t_opt.step()
+    torch.cuda.synchronize()
+    mine = {k: v.detach().float().cpu() for k, v in trainer.model.module.state_dict().items()}
+    oracle = {k: v.detach().float().cpu() for k, v in theirs.state_dict().items()}
+    torch.save({"mine": mine, "oracle": oracle, "fused": fused, "losses": losses, "log": trainer.model.get_logging_data(),
+                "err": ddpx.launch.get_comm().error_word()}, os.path.join(outdir, f"rank{rank}.pt"))
+    ddpx.teardown()
+
+
+def _run(fn, world):
+    port = _free_port()
+    with tempfile.TemporaryDirectory() as d:
+        mp.spawn(fn, args=(world, port, d), nprocs=world, join=True)
+        return [torch.load(os.path.join(d, f"rank{r}.pt"), weights_only=False) for r in range(world)]
+
+
+@pytest.mark.multigpu
+def test_p2p_collectives_match_nccl():
+    world = min(torch.cuda.device_count(), 8)
+    outs = _run(_w_collectives, world)
+    for o in outs:
+        assert o["err"] == 0
+        assert o["bcast"]
+        bad = [k for k, v in o.items() if k not in ("bcast", "err") and not v]
+        assert not bad, bad
+
+
+@pytest.mark.multigpu
+def test_vgg_fused_p2p_training_tracks_torch_ddp():
+    world = min(torch.cuda.device_count(), 8)
+    outs = _run(_w_vgg_parity, world)
+    for o in outs:
+        assert o["err"] == 0 and o["fused"]
+        assert o["log"]["rebuilt_bucket_sizes"] == [9461800, 27148288, 303360]
+    # replicas identical across ranks (parameters), and close to torch DDP + NCCL after 4 steps
+    for k, v in outs[0]["mine"].items():
+        if "running" in k or "num_batches" in k:
+            continue
+        assert torch.equal(v, outs[1]["mine"][k]), k
+        rel = ((v - outs[0]["oracle"][k]).norm() / outs[0]["oracle"][k].norm().clamp_min(1e-9)).item()
+        assert rel < 5e-2, (k, rel)
