@@ -196,7 +196,10 @@ def run_reference(args):
     torch.cuda.set_device(local_rank)
     if world > 1:
         # ddp_setup (multigpu.py:24-33) rewrites MASTER_ADDR/PORT to localhost:12355 for every rank and calls
-        # init_process_group("nccl") - the reference's own bootstrap.
+        # init_process_group("nccl") - the reference's own bootstrap.  torchrun tells workers to reuse the agent's store
+        # (TORCHELASTIC_USE_AGENT_STORE) at its own MASTER_PORT; the reference overwrites the port with 12355, where no
+        # agent store listens, so let rank 0 host the store itself exactly as under the reference's mp.spawn launch.
+        os.environ.pop("TORCHELASTIC_USE_AGENT_STORE", None)
         ref.ddp_setup(rank, world)
     torch.manual_seed(1234 + rank)
     # load_train_objs() (multigpu.py:122-144) minus the CIFAR-10 download (no network): same literals.

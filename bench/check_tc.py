@@ -147,6 +147,9 @@ CASES = {
     "gemm_big_bf16": lambda: run_gemm(0, 0, 1, M=8192, N=8192, K=8192, out_bf16=1, timing=True),
     "gemm_big_tf32": lambda: run_gemm(0, 0, 0, M=4096, N=4096, K=4096, timing=True),
     "gemm_mlp_bf16": lambda: run_gemm(0, 0, 1, M=256, N=8192, K=8192, out_bf16=1, timing=True),
+    "gemm_big_tf32_nn": lambda: run_gemm(0, 1, 0, M=4096, N=4096, K=4096, timing=True),
+    "gemm_big_tf32_nt": lambda: run_gemm(1, 1, 0, M=4096, N=4096, K=4096, timing=True),
+    "gemm_big_bf16_nt": lambda: run_gemm(1, 1, 1, M=8192, N=8192, K=8192, out_bf16=1, timing=True),
     "conv_f_32": lambda: run_conv(4, 32, 32, 64, 128),
     "conv_f_16": lambda: run_conv(4, 16, 16, 128, 256),
     "conv_f_8": lambda: run_conv(8, 8, 8, 256, 512),

@@ -351,3 +351,22 @@ extern "C" int ddpx_bn_bwd_apply(const float* x, const float* dout, const float*
         x, dout, mean, rstd, gamma, beta, sum_dz, sum_dzx, inv_count, Nimg, H, W, C, relu, use_batch_stats, dx);
   return cudaGetLastError() == cudaSuccess ? DDPX_OK : DDPX_ERR_LAUNCH;
 }
+
+// Training-mode BatchNorm2d forward in ONE call: batch statistics -> mean / rstd (+ running-stat update) -> normalise
+// (+ReLU, +2x2 max-pool).  `workspace` is scratch for the per-channel sum / sum-of-squares accumulators: 2*C floats that
+// this call clears itself; `mean_rstd` ([2][C]) is an output kept for the backward.  Used by the stand-alone
+// nn.BatchNorm2d path (inputs that do not come out of the fused conv epilogue).
+extern "C" int ddpx_bn_train_fwd(const float* x, float* y, const float* gamma, const float* beta, float* running_mean,
+                                 float* running_var, long long* num_batches_tracked, float momentum, float eps, int Nimg,
+                                 int H, int W, int C, int relu, int pool, float* mean_rstd, float* workspace, void* stream) {
+  if (C % 4 || C > 1024) return DDPX_ERR_SHAPE;
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  if (cudaMemsetAsync(workspace, 0, sizeof(float) * 2 * C, s) != cudaSuccess) return DDPX_ERR_LAUNCH;
+  const long long P = static_cast<long long>(Nimg) * H * W;
+  int rc = ddpx_bn_stats(x, P, C, workspace, workspace + C, stream);
+  if (rc != DDPX_OK) return rc;
+  rc = ddpx_bn_finalize(workspace, workspace + C, static_cast<float>(P), mean_rstd, mean_rstd + C, running_mean, running_var,
+                        num_batches_tracked, momentum, eps, C, stream);
+  if (rc != DDPX_OK) return rc;
+  return ddpx_bn_apply(x, y, mean_rstd, mean_rstd + C, gamma, beta, Nimg, H, W, C, relu, pool, stream);
+}

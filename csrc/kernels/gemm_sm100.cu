@@ -19,6 +19,7 @@
 
 #include <cudaTypedefs.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include <mutex>
 
 namespace ddpx {
@@ -49,6 +50,9 @@ struct TcParams {
   int box_w, box_h, box_n;
   int cin_total;
   int conv_taps;            // FPROP: 9 (3x3) or 1 (1x1 over pre-gathered patches)
+  int tpi;                  // filter taps per work item: WGRAD handles one filter row (3 taps) per item so the dY tile
+                            // is loaded once for three accumulators; 1 everywhere else
+  int acc_stages;           // TMEM accumulator buffers in flight (2 when 2*tpi*block_n <= 512 columns, else 1)
   // epilogue
   void* out;
   long long ldo;
@@ -72,7 +76,9 @@ __global__ void __launch_bounds__(kNumThreads, 1)
 tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const TcParams p) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   // carve shared memory: [stages x (A | B)] | barriers | tmem ptr
-  const uint32_t stage_b_bytes = static_cast<uint32_t>(p.block_n) * 128u;
+  const uint32_t tap_b_bytes = static_cast<uint32_t>(p.block_n) * 128u;
+  const uint32_t stage_b_bytes = tap_b_bytes * static_cast<uint32_t>(p.tpi);
+  const uint32_t acc_cols = static_cast<uint32_t>(p.block_n * p.tpi);
   const uint32_t stage_bytes = kStageABytes + stage_b_bytes;
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + static_cast<size_t>(p.num_stages) * stage_bytes);
@@ -114,7 +120,7 @@ tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
 
   const int tiles_mn = p.m_blocks * p.n_blocks;
   // "tap" doubles as the batch index in MODE_GEMM
-  const int taps = (kMode == MODE_WGRAD) ? 9 : (kMode == MODE_GEMM ? p.batch1 * p.batch2 : 1);
+  const int taps = (kMode == MODE_WGRAD) ? 9 / p.tpi : (kMode == MODE_GEMM ? p.batch1 * p.batch2 : 1);
   const int num_items = tiles_mn * taps * p.num_splits;
 
   auto decode = [&](int item, int& m_blk, int& n_blk, int& tap, int& split) {
@@ -183,15 +189,20 @@ tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
             tma_load_4d(sb, &tmB, &full_bar[stage], cb * kBK, s - 1, h0 + r - 1, img);
           } else {
             // WGRAD: K step = 32 consecutive pixels.  A = dY [pixels][Cout] (MN-major), B = shifted X.
-            const int r = tap / 3, s = tap - r * 3;
+            // item "tap" = first tap of the group (tpi = 3: one filter row r, s = 0..2; tpi = 1: a single tap)
+            const int tap0 = tap * p.tpi;
             const int p0 = kk * 32;
             const int hw = p.H * p.W;
             const int img = p0 / hw;
             const int h0 = (p0 - img * hw) / p.W;
             for (int j = 0; j < kBlockM / kChunk; ++j)
               tma_load_2d(sa + j * (kBK * 128), &tmA, &full_bar[stage], m0 + j * kChunk, p0);
-            for (int j = 0; j < p.block_n / kChunk; ++j)
-              tma_load_4d(sb + j * (kBK * 128), &tmB, &full_bar[stage], n0 + j * kChunk, s - 1, h0 + r - 1, img);
+            for (int t = 0; t < p.tpi; ++t) {
+              const int r = (tap0 + t) / 3, s = (tap0 + t) - r * 3;
+              for (int j = 0; j < p.block_n / kChunk; ++j)
+                tma_load_4d(sb + t * tap_b_bytes + j * (kBK * 128), &tmB, &full_bar[stage], n0 + j * kChunk, s - 1,
+                            h0 + r - 1, img);
+            }
           }
           if (++stage == p.num_stages) { stage = 0; phase ^= 1u; }
         }
@@ -220,23 +231,25 @@ tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
         if (skipped(m_blk, n_blk)) continue;
         mbar_wait(&tempty_bar[acc], acc_phase ^ 1u, 0x200u + acc);
         tc_fence_after();
-        const uint32_t tmem_d = tmem_base + static_cast<uint32_t>(acc * p.block_n);
+        const uint32_t tmem_d = tmem_base + static_cast<uint32_t>(acc) * acc_cols;
         for (int i = 0; i < nk; ++i) {
           mbar_wait(&full_bar[stage], phase, 0x300u + stage);
           tc_fence_after();
           const uint32_t sa = smem_u32(smem + static_cast<size_t>(stage) * stage_bytes);
           const uint32_t sb = sa + kStageABytes;
+          for (int t = 0; t < p.tpi; ++t) {      // one accumulator per tap, all fed by the same A tile
 #pragma unroll
-          for (int k = 0; k < kBK / kUmmaK; ++k) {
-            const uint64_t adesc = make_smem_desc_sw128(sa + k * a_kadv, a_lbo, a_sbo, a_lay);
-            const uint64_t bdesc = make_smem_desc_sw128(sb + k * b_kadv, b_lbo, b_sbo, b_lay);
-            tc_mma<kBF16>(tmem_d, adesc, bdesc, idesc, (i > 0 || k > 0) ? 1u : 0u);
+            for (int k = 0; k < kBK / kUmmaK; ++k) {
+              const uint64_t adesc = make_smem_desc_sw128(sa + k * a_kadv, a_lbo, a_sbo, a_lay);
+              const uint64_t bdesc = make_smem_desc_sw128(sb + t * tap_b_bytes + k * b_kadv, b_lbo, b_sbo, b_lay);
+              tc_mma<kBF16>(tmem_d + t * p.block_n, adesc, bdesc, idesc, (i > 0 || k > 0) ? 1u : 0u);
+            }
           }
           tc_commit(&empty_bar[stage]);   // smem slot is free once these MMAs retire
           if (++stage == p.num_stages) { stage = 0; phase ^= 1u; }
         }
         tc_commit(&tfull_bar[acc]);       // accumulator complete -> epilogue
-        if (++acc == 2) { acc = 0; acc_phase ^= 1u; }
+        if (++acc == p.acc_stages) { acc = 0; acc_phase ^= 1u; }
       }
     }
   } else if (warp >= 4) {
@@ -256,11 +269,14 @@ tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
       const int n0 = n_blk * p.block_n;
       mbar_wait(&tfull_bar[acc], acc_phase, 0x400u + acc);
       tc_fence_after();
-      const uint32_t taddr = tmem_base + (static_cast<uint32_t>(ew * 32) << 16) + static_cast<uint32_t>(acc * p.block_n);
+      const uint32_t taddr = tmem_base + (static_cast<uint32_t>(ew * 32) << 16) + static_cast<uint32_t>(acc) * acc_cols;
       float ssum = 0.f, ssq = 0.f;
-      for (int c0 = 0; c0 < p.block_n; c0 += 32) {
+      for (int cc = 0; cc < static_cast<int>(acc_cols); cc += 32) {
+        // cc walks all accumulator columns of the item; c0 is the column inside the current tap's tile
+        const int tsub = cc / p.block_n;
+        const int c0 = cc - tsub * p.block_n;
         uint32_t v[32];
-        tmem_ld_32x32(taddr + c0, v);
+        tmem_ld_32x32(taddr + cc, v);
         tmem_ld_wait();
         if (nk == 0) {
 #pragma unroll
@@ -339,7 +355,8 @@ tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
         } else {
           // WGRAD: row = Cout, column = Cin; scatter-accumulate into the torch-layout gradient [Cout][Cin][3][3]
           if (row < p.M) {
-            float* o = reinterpret_cast<float*>(p.out) + (static_cast<long long>(row) * p.cin_total + n0 + c0) * 9 + tap;
+            float* o = reinterpret_cast<float*>(p.out) + (static_cast<long long>(row) * p.cin_total + n0 + c0) * 9 +
+                       tap * p.tpi + tsub;
 #pragma unroll
             for (int j = 0; j < 32; ++j)
               if (n0 + c0 + j < p.N) atomicAdd(o + j * 9, __uint_as_float(v[j]));
@@ -355,7 +372,7 @@ tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&tempty_bar[acc]);
-      if (++acc == 2) { acc = 0; acc_phase ^= 1u; }
+      if (++acc == p.acc_stages) { acc = 0; acc_phase ^= 1u; }
     }
   }
 
@@ -412,8 +429,8 @@ static int num_sms() {
   return g_num_sms;
 }
 
-static int pick_stages(int block_n) {
-  const int stage = kStageABytes + block_n * 128;
+static int pick_stages(int block_n, int tpi) {
+  const int stage = kStageABytes + block_n * 128 * tpi;
   int s = (220 * 1024) / stage;
   if (s > kMaxStages) s = kMaxStages;
   if (s < 2) s = 2;
@@ -422,15 +439,17 @@ static int pick_stages(int block_n) {
 
 template <int kMode, bool kBF16>
 static int launch_tc(const CUtensorMap& a, const CUtensorMap& b, TcParams& p, cudaStream_t stream) {
-  p.num_stages = pick_stages(p.block_n);
-  const size_t smem = static_cast<size_t>(p.num_stages) * (kStageABytes + p.block_n * 128) + 1024 /*align*/ + 256;
+  if (p.tpi < 1) p.tpi = 1;
+  p.acc_stages = (2 * p.tpi * p.block_n <= 512) ? 2 : 1;
+  p.num_stages = pick_stages(p.block_n, p.tpi);
+  const size_t smem = static_cast<size_t>(p.num_stages) * (kStageABytes + p.block_n * 128 * p.tpi) + 1024 /*align*/ + 256;
   static bool attr_set = false;
   if (!attr_set) {
     cudaError_t e = cudaFuncSetAttribute(tc_kernel<kMode, kBF16>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
     if (e != cudaSuccess) return DDPX_ERR_LAUNCH;
     attr_set = true;
   }
-  const int taps = (kMode == MODE_WGRAD) ? 9 : (kMode == MODE_GEMM ? p.batch1 * p.batch2 : 1);
+  const int taps = (kMode == MODE_WGRAD) ? 9 / p.tpi : (kMode == MODE_GEMM ? p.batch1 * p.batch2 : 1);
   const int items = p.m_blocks * p.n_blocks * taps * p.num_splits;
   int grid = items < num_sms() ? items : num_sms();
   if (grid < 1) grid = 1;
@@ -589,14 +608,22 @@ extern "C" int ddpx_conv3x3_wgrad(const float* dy, const float* x, float* dw, in
   if ((rc = conv_box(32, H, W, Nimg, &bw, &bh, &bnn)) != DDPX_OK) return rc;
   TcParams p{};
   p.M = Cout; p.N = Cin;
-  int bn = Cin >= 256 ? 256 : Cin;      // Cin is a multiple of 32
-  if (Cin > 256 && Cin % 256) bn = 128;
-  if (bn % 32) return DDPX_ERR_SHAPE;
+  // taps per work item: 3 (one filter row; the dY tile is loaded once for three accumulators) unless overridden
+  static int tpi_cfg = -1;
+  if (tpi_cfg < 0) {
+    const char* e = getenv("DDPX_WGRAD_TPI");
+    tpi_cfg = (e && (e[0] == '1')) ? 1 : 3;
+  }
+  p.tpi = tpi_cfg;
+  const int max_bn = p.tpi == 3 ? 128 : 256;   // 3 accumulators of block_n columns must fit the 512 TMEM columns
+  int bn = Cin >= max_bn ? max_bn : Cin;       // Cin is a multiple of 32
+  while (Cin % bn) bn -= 32;
+  if (bn < 32 || bn % 32) return DDPX_ERR_SHAPE;
   p.block_n = bn;
   p.m_blocks = (Cout + kBlockM - 1) / kBlockM;
   p.n_blocks = (Cin + bn - 1) / bn;
   p.k_steps_total = static_cast<int>(P / 32);
-  const int tiles = p.m_blocks * p.n_blocks * 9;
+  const int tiles = p.m_blocks * p.n_blocks * (9 / p.tpi);
   int splits = split_k;
   if (splits <= 0) {   // fill the machine about twice over
     splits = (2 * num_sms() + tiles - 1) / tiles;

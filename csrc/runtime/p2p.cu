@@ -180,22 +180,40 @@ allreduce_fused_kernel(const Peers P, const uint32_t gen, const long long n, con
     //         store it into every rank's bucket
     const long long per = (nvec + P.world - 1) / P.world;
     const long long v0 = per * P.rank, v1 = min(v0 + per, nvec);
-    for (long long i = v0 + static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < v1;
-         i += static_cast<long long>(gridDim.x) * blockDim.x) {
-      float acc[V];
+    // U vectors per thread per trip, all peer loads issued before the first add: the ~2 us NVLink load latency needs
+    // tens of 16-byte requests in flight per thread to reach link bandwidth
+    constexpr int U = 2;
+    const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+    for (long long i0 = v0 + static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i0 < v1; i0 += stride * U) {
+      uint4 in[U][kMaxRanks];
 #pragma unroll
-      for (int k = 0; k < V; ++k) acc[k] = 0.f;
-#pragma unroll 1
-      for (int r = 0; r < P.world; ++r) {
-        const uint4 u = reinterpret_cast<const uint4*>(P.buf[r])[i];
-        float f[V];
-        unpack<T>(u, f);
+      for (int u = 0; u < U; ++u) {
+        const long long i = i0 + u * stride;
 #pragma unroll
-        for (int k = 0; k < V; ++k) acc[k] += f[k];
+        for (int r = 0; r < kMaxRanks; ++r)
+          if (r < P.world && i < v1) in[u][r] = reinterpret_cast<const uint4*>(P.buf[r])[i];
       }
-      const uint4 o = pack<T>(acc);
-#pragma unroll 1
-      for (int r = 0; r < P.world; ++r) reinterpret_cast<uint4*>(P.buf[r])[i] = o;
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const long long i = i0 + u * stride;
+        if (i >= v1) break;
+        float acc[V];
+#pragma unroll
+        for (int k = 0; k < V; ++k) acc[k] = 0.f;
+#pragma unroll
+        for (int r = 0; r < kMaxRanks; ++r) {
+          if (r < P.world) {
+            float f[V];
+            unpack<T>(in[u][r], f);
+#pragma unroll
+            for (int k = 0; k < V; ++k) acc[k] += f[k];
+          }
+        }
+        const uint4 o = pack<T>(acc);
+#pragma unroll
+        for (int r = 0; r < kMaxRanks; ++r)
+          if (r < P.world) reinterpret_cast<uint4*>(P.buf[r])[i] = o;
+      }
     }
     // ---- 3. when the whole grid is done with the shard, tell every peer
     last_cta_does(pad + PAD_COUNTER, [&] {

@@ -221,15 +221,14 @@ class _BatchNorm(Function):
         xin = to_nhwc(x)
         dev = x.device
         mr = torch.empty((2, C), device=dev, dtype=torch.float32)
+        out = torch.empty_like(xin)
         if training:
-            stats = _zeros((2, C), dev)
-            native.bn_stats(xin, N * H * W_, C, stats[0], stats[1])
-            native.bn_finalize(stats[0], stats[1], float(N * H * W_), mr[0], mr[1], running_mean, running_var, nbt, momentum,
-                               eps, C)
+            work = torch.empty((2, C), device=dev, dtype=torch.float32)      # scratch: cleared inside the call
+            native.bn_train_fwd(xin, out, gamma, beta, running_mean, running_var, nbt, momentum, eps, N, H, W_, C, 0, 0,
+                                mr, work)
         else:
             native.bn_eval_stats(running_mean, running_var, eps, mr[0], mr[1], C)
-        out = torch.empty_like(xin)
-        native.bn_apply(xin, out, mr[0], mr[1], gamma, beta, N, H, W_, C, 0, 0)
+            native.bn_apply(xin, out, mr[0], mr[1], gamma, beta, N, H, W_, C, 0, 0)
         ctx.save_for_backward(xin, mr, gamma, beta)
         ctx.cfg = (N, H, W_, C, bool(training))
         return from_nhwc(out)

@@ -174,6 +174,12 @@ def bn_apply(x, y, mean, rstd, gamma, beta, N, H, W, C, relu, pool):
           c_int(relu), c_int(pool), _st(), tag=f"[{C}@{H}]")
 
 
+def bn_train_fwd(x, y, gamma, beta, running_mean, running_var, nbt, momentum, eps, N, H, W, C, relu, pool, mean_rstd, work):
+    _call("ddpx_bn_train_fwd", _P(x), _P(y), _P(gamma), _P(beta), _P(running_mean), _P(running_var), _P(nbt),
+          c_float(momentum), c_float(eps), c_int(N), c_int(H), c_int(W), c_int(C), c_int(relu), c_int(pool), _P(mean_rstd),
+          _P(work), _st(), launches=3)
+
+
 def bn_bwd_reduce(x, dout, mean, rstd, gamma, beta, N, H, W, C, relu, pool, sum_dz, sum_dzx):
     _call("ddpx_bn_bwd_reduce", _P(x), _P(dout), _P(mean), _P(rstd), _P(gamma), _P(beta), c_int(N), c_int(H), c_int(W),
           c_int(C), c_int(relu), c_int(pool), _P(sum_dz), _P(sum_dzx), _st(), tag=f"[{C}@{H}]")

@@ -96,6 +96,7 @@ def fuse(optimizer: torch.optim.Optimizer) -> torch.optim.Optimizer:
     @torch.no_grad()
     def step(self, closure=None):
         loss = None
+        self._opt_called = True          # what LambdaLR's own wrapper records (lr_scheduler.py:165)
         if closure is not None:
             with torch.enable_grad():
                 loss = closure()
@@ -105,6 +106,7 @@ def fuse(optimizer: torch.optim.Optimizer) -> torch.optim.Optimizer:
         inner(self)
         return loss
 
+    step._wrapped_by_lr_sched = True     # keep lr_scheduler's call-order check quiet: we preserve its bookkeeping
     optimizer._ddpx_orig_step = orig_step
     optimizer.step = types.MethodType(step, optimizer)
     optimizer._ddpx_fused = True

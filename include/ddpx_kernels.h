@@ -95,6 +95,11 @@ int ddpx_bn_eval_stats(const float* running_mean, const float* running_var, floa
 int ddpx_bn_stats(const float* x, long long P, int C, float* sum, float* sq, void* stream);
 int ddpx_bn_apply(const float* x, float* y, const float* mean, const float* rstd, const float* gamma, const float* beta,
                   int Nimg, int H, int W, int C, int relu, int pool, void* stream);
+/* one-call training forward: statistics -> finalize -> apply; `workspace` = 2*C floats of scratch (cleared by the call),
+ * `mean_rstd` = [2][C] output saved for the backward */
+int ddpx_bn_train_fwd(const float* x, float* y, const float* gamma, const float* beta, float* running_mean,
+                      float* running_var, long long* num_batches_tracked, float momentum, float eps, int Nimg, int H, int W,
+                      int C, int relu, int pool, float* mean_rstd, float* workspace, void* stream);
 int ddpx_bn_bwd_reduce(const float* x, const float* dout, const float* mean, const float* rstd, const float* gamma,
                        const float* beta, int Nimg, int H, int W, int C, int relu, int pool, float* sum_dz, float* sum_dzx,
                        void* stream);
