@@ -283,11 +283,24 @@ def run_ours(args):
     for i in range(2):
         e2e_step(i)
     e2e_ms = timed_loop(e2e_step, args.steps, world)
+    extra = {"stack": "hand-written sm_100a kernels (tcgen05/TMEM/TMA conv+GEMM, fused BN/ReLU/pool/CE/SGD)"
+                      + (", P2P fused all-reduce+SGD over NVLink" if world > 1 else "")}
+    if world > 1 and hasattr(trainer.model, "measure_exposed_comm"):
+        # outside the timed regions: how long the compute stream stalls for the last gradient buckets, per step
+        trainer.model.measure_exposed_comm(True)
+        for i in range(8):
+            dev_step(i)
+        ex = trainer.model.exposed_comm_ms()
+        trainer.model.measure_exposed_comm(False)
+        if ex:
+            ex_t = torch.tensor([sum(ex) / len(ex)], device="cuda", dtype=torch.float64)
+            import torch.distributed as dist
+            dist.all_reduce(ex_t, op=dist.ReduceOp.MAX)
+            extra["exposed_comm_ms_per_step"] = round(float(ex_t.item()), 4)
+            extra["exposed_comm_frac_of_step"] = round(float(ex_t.item()) / (total_ms / args.steps), 4)
     if rank == 0:
         h2d = xs[0].numel() * 4 + ys[0].numel() * 8
-        emit(args, world, "ddpx_b200", total_ms, e2e_ms, h2d, 4, launches, clocks,
-             {"stack": "hand-written sm_100a kernels (tcgen05/TMEM/TMA conv+GEMM, fused BN/ReLU/pool/CE/SGD)"
-                       + (", P2P fused all-reduce+SGD over NVLink" if world > 1 else "")})
+        emit(args, world, "ddpx_b200", total_ms, e2e_ms, h2d, 4, launches, clocks, extra)
     if world > 1:
         ddpx.launch.teardown()
 

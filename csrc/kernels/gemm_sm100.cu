@@ -608,13 +608,16 @@ extern "C" int ddpx_conv3x3_wgrad(const float* dy, const float* x, float* dw, in
   if ((rc = conv_box(32, H, W, Nimg, &bw, &bh, &bnn)) != DDPX_OK) return rc;
   TcParams p{};
   p.M = Cout; p.N = Cin;
-  // taps per work item: 3 (one filter row; the dY tile is loaded once for three accumulators) unless overridden
+  // taps per work item.  Narrow layers (Cin <= 64) are bound by re-reading dY once per tap: handle one filter row
+  // (3 taps, three accumulators fed by one dY tile) per item - measured 803 -> 391 us on 64->128 @ 32x32.  Wide layers
+  // keep one tap per item with a 256-column tile and double-buffered accumulators (3 taps there measured slower).
+  // DDPX_WGRAD_TPI=1|3 forces either.
   static int tpi_cfg = -1;
   if (tpi_cfg < 0) {
     const char* e = getenv("DDPX_WGRAD_TPI");
-    tpi_cfg = (e && (e[0] == '1')) ? 1 : 3;
+    tpi_cfg = (e && e[0] == '1') ? 1 : ((e && e[0] == '3') ? 3 : 0);
   }
-  p.tpi = tpi_cfg;
+  p.tpi = tpi_cfg ? tpi_cfg : (Cin <= 64 ? 3 : 1);
   const int max_bn = p.tpi == 3 ? 128 : 256;   // 3 accumulators of block_n columns must fit the 512 TMEM columns
   int bn = Cin >= max_bn ? max_bn : Cin;       // Cin is a multiple of 32
   while (Cin % bn) bn -= 32;

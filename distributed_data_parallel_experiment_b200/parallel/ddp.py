@@ -152,5 +152,19 @@ class DataParallel(nn.Module):
                 "rebuilt_bucket_sizes": r.stats["rebuilt_bucket_sizes"], "has_rebuilt_buckets": r.has_rebuilt,
                 "iteration": r.iteration, "fused_optimizer": self.fused is not None}
 
+    def measure_exposed_comm(self, on: bool = True):
+        """Start / stop recording the exposed-communication time of every synchronised backward."""
+        self.reducer.measure_exposed = on
+        if on:
+            self.reducer.stats["exposed_events"] = []
+
+    def exposed_comm_ms(self):
+        """Per-iteration milliseconds the compute stream waited for gradient buckets after backward's last kernel."""
+        evs = self.reducer.stats.get("exposed_events", [])
+        if not evs:
+            return []
+        torch.cuda.synchronize()
+        return [a.elapsed_time(b) for a, b in evs]
+
     def close(self):
         self.reducer.close()

@@ -181,10 +181,18 @@ class Reducer:
 
     def finalize_backward(self):
         parity = self.step_parity if self.double_buffer else 0
+        timing = getattr(self, "measure_exposed", False) and self.device.type == "cuda"
+        if timing:      # exposed communication = how long the compute stream stalls here for the last buckets
+            t0 = torch.cuda.Event(enable_timing=True)
+            t0.record()
         for b in self.buckets:
             if b.handle is not None:
                 b.handle.wait()
                 b.handle = None
+        if timing:
+            t1 = torch.cuda.Event(enable_timing=True)
+            t1.record()
+            self.stats.setdefault("exposed_events", []).append((t0, t1))
             if self.fused is None:
                 for pid, v in zip(b.param_ids, b.views[parity]):
                     self.params[pid].grad = v          # averaged gradient lives in the bucket (no copy back)
