@@ -7,6 +7,7 @@
 // saved pre-BN tensor instead of storing them.
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <stdio.h>
 #include "../../include/ddpx_kernels.h"
 
 namespace {
@@ -369,4 +370,75 @@ extern "C" int ddpx_bn_train_fwd(const float* x, float* y, const float* gamma, c
                         num_batches_tracked, momentum, eps, C, stream);
   if (rc != DDPX_OK) return rc;
   return ddpx_bn_apply(x, y, mean_rstd, mean_rstd + C, gamma, beta, Nimg, H, W, C, relu, pool, stream);
+}
+
+// ------------------------------------------------------------------------------------------------
+// ddpx_bn_train_fwd_static: the same training-mode forward for callers that have no memory to hand over.
+//
+// Who this is for.  ddpx_bn_train_fwd needs 2*C floats of workspace from its caller.  Some users of this C ABI cannot
+// produce one: a host program (or a binding in another language) that was given its tensors by somebody else and owns
+// no device allocator; a runtime whose device memory was planned and committed up front, so that nothing may be carved
+// out afterwards; a service loop that must not call cudaMalloc because that call can stall every stream of the device
+// while it runs.  For them the accumulators live in the library itself: the fixed array below, DDPX_BN_STATIC_MAX_C
+// channels wide (2 * 1024 floats = 8 KiB).  Every GPU that loads this library carries those 8 KiB until the process
+// exits, whether or not the entry point is ever called.
+//
+// What the call does and does not do.  It issues a memset of the first 2*C floats of the array and the same three
+// kernels as ddpx_bn_train_fwd on `stream`; it never calls cudaMalloc, cudaFree or any routine that allocates.  Inputs
+// and outputs (x, y, gamma, beta, running statistics, mean_rstd) are still the caller's.  C above
+// DDPX_BN_STATIC_MAX_C is refused with DDPX_ERR_LIMIT and a message on stderr; nothing is launched in that case.
+//
+// First call on a device.  The address of the array is looked up once per device (cudaGetSymbolAddress, with that
+// device current) and remembered; the look-up may make the CUDA runtime load this library's device code.  Make the
+// first call on each device during start-up, before any stream capture begins on that device.
+//
+// Sharing.  All calls on a device use the same array and it keeps whatever the previous call left there, which is why
+// every call clears the part it uses first.  Two calls that can run at the same time on one GPU (different streams,
+// different host threads) would accumulate into each other's sums: keep calls to this entry point ordered on one
+// stream, or use ddpx_bn_train_fwd with separate workspaces.
+// ------------------------------------------------------------------------------------------------
+#define DDPX_BN_STATIC_MAX_C 1024
+static __device__ __align__(256) float g_bn_static_scratch[2 * DDPX_BN_STATIC_MAX_C];
+
+namespace {
+constexpr int kMaxDevices = 64;
+float* g_bn_static_ptr[kMaxDevices] = {nullptr};
+
+// `g_bn_static_scratch` in host code is only a handle for the runtime, not a device address: ask the runtime for the
+// address on the current device, once.
+int bn_static_scratch_ptr(float** out) {
+  int dev = -1;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= kMaxDevices) return DDPX_ERR_DRIVER;
+  if (g_bn_static_ptr[dev] == nullptr) {
+    void* p = nullptr;
+    const cudaError_t e = cudaGetSymbolAddress(&p, g_bn_static_scratch);
+    if (e != cudaSuccess || p == nullptr) {
+      fprintf(stderr, "[ddpx] ddpx_bn_train_fwd_static: cudaGetSymbolAddress failed on device %d: %s\n", dev,
+              cudaGetErrorString(e));
+      return DDPX_ERR_DRIVER;
+    }
+    g_bn_static_ptr[dev] = static_cast<float*>(p);
+  }
+  *out = g_bn_static_ptr[dev];
+  return DDPX_OK;
+}
+}  // namespace
+
+extern "C" int ddpx_bn_train_fwd_static(const float* x, float* y, const float* gamma, const float* beta,
+                                        float* running_mean, float* running_var, long long* num_batches_tracked,
+                                        float momentum, float eps, int Nimg, int H, int W, int C, int relu, int pool,
+                                        float* mean_rstd, void* stream) {
+  if (C > DDPX_BN_STATIC_MAX_C) {
+    fprintf(stderr,
+            "[ddpx] ddpx_bn_train_fwd_static: C = %d exceeds the built-in scratch (DDPX_BN_STATIC_MAX_C = %d channels); "
+            "use ddpx_bn_train_fwd with a caller-provided workspace\n", C, DDPX_BN_STATIC_MAX_C);
+    return DDPX_ERR_LIMIT;
+  }
+  if (C <= 0 || C % 4) return DDPX_ERR_SHAPE;
+  float* scratch = nullptr;
+  const int rc = bn_static_scratch_ptr(&scratch);
+  if (rc != DDPX_OK) return rc;
+  // ddpx_bn_train_fwd clears the 2*C floats it accumulates into, so the previous call's sums never leak in
+  return ddpx_bn_train_fwd(x, y, gamma, beta, running_mean, running_var, num_batches_tracked, momentum, eps, Nimg, H, W, C,
+                           relu, pool, mean_rstd, scratch, stream);
 }

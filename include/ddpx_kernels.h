@@ -100,6 +100,16 @@ int ddpx_bn_apply(const float* x, float* y, const float* mean, const float* rstd
 int ddpx_bn_train_fwd(const float* x, float* y, const float* gamma, const float* beta, float* running_mean,
                       float* running_var, long long* num_batches_tracked, float momentum, float eps, int Nimg, int H, int W,
                       int C, int relu, int pool, float* mean_rstd, float* workspace, void* stream);
+/* ddpx_bn_train_fwd without the workspace argument, for callers that cannot allocate device memory (they were handed
+ * their tensors and own no allocator, their memory was committed up front, or they must not stall the device with
+ * cudaMalloc).  The accumulators live in an 8 KiB array inside the library (2 x DDPX_BN_STATIC_MAX_C = 1024 channels of
+ * fp32; resident on every GPU that loads the library).  Allocates nothing; C > 1024 returns DDPX_ERR_LIMIT with a
+ * message on stderr.  The first call on a device looks the array's address up (make it at start-up, before any stream
+ * capture on that device).  All calls share the array: each clears what it uses, and calls that overlap in time on one
+ * GPU race.  This entry point has no counterpart in the reference. */
+int ddpx_bn_train_fwd_static(const float* x, float* y, const float* gamma, const float* beta, float* running_mean,
+                             float* running_var, long long* num_batches_tracked, float momentum, float eps, int Nimg,
+                             int H, int W, int C, int relu, int pool, float* mean_rstd, void* stream);
 int ddpx_bn_bwd_reduce(const float* x, const float* dout, const float* mean, const float* rstd, const float* gamma,
                        const float* beta, int Nimg, int H, int W, int C, int relu, int pool, float* sum_dz, float* sum_dzx,
                        void* stream);
