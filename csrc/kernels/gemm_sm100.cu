@@ -9,8 +9,8 @@
 // Reference parity: these replace the cuDNN / cuBLAS calls behind nn.Conv2d / nn.Linear in
 // /root/reference/multigpu.py:53,62 (W13-W15, W20).
 //
-// Roles (256 threads): warp 0 = TMA producer, warp 1 = MMA issuer (one lane), warp 2 = TMEM allocator,
-// warps 4-7 = epilogue (TMEM -> registers -> global). Accumulators are double-buffered in TMEM so the
+// Roles (384 threads): warp 0 = TMA producer, warp 1 = MMA issuer (one lane), warp 2 = TMEM allocator,
+// warps 4-11 = epilogue (TMEM -> registers -> global; two warps per TMEM lane quarter, each draining half the columns). Accumulators are double-buffered in TMEM so the
 // epilogue of tile i overlaps the MMAs of tile i+1. Operand tiles are 128-byte-swizzled in shared memory
 // exactly as TMA writes them; padding of the convolution comes from TMA out-of-bounds zero fill with
 // signed start coordinates (no im2col buffer is ever materialised).
@@ -28,7 +28,7 @@ enum { MODE_GEMM = 0, MODE_FPROP = 1, MODE_WGRAD = 2 };
 
 constexpr int kBlockM = 128;          // TMEM lanes / UMMA M
 constexpr int kStageABytes = 16384;   // 128 rows x 128 B
-constexpr int kNumThreads = 256;
+constexpr int kNumThreads = 384;     // 4 role warps (TMA, MMA, TMEM alloc, spare) + 8 epilogue warps
 constexpr int kMaxStages = 8;
 
 struct TcParams {
@@ -59,6 +59,8 @@ struct TcParams {
   int out_bf16;
   int atomic;               // 1 = accumulate with red.global.add.f32 (split-K / wgrad)
   float alpha;              // GEMM: D = act(alpha * A*B + bias)
+  int st_vec;               // GEMM: output rows are 16-byte aligned -> epilogue stages 32x32 chunks through shared
+                            // memory and stores whole 64/128-byte row segments (coalesced) instead of 16 B per lane
   int act;                  // 0 none, 1 relu, 2 gelu(tanh)
   const float* bias;        // GEMM: per output column; FPROP: per output channel (row)
   float* stat_sum;          // FPROP: per-channel sum / sum-of-squares of the raw conv output
@@ -86,6 +88,7 @@ tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
   uint64_t* tfull_bar = empty_bar + kMaxStages;   // [2]
   uint64_t* tempty_bar = tfull_bar + 2;           // [2]
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + 2);
+  uint8_t* epi_stage = reinterpret_cast<uint8_t*>(full_bar) + 256;     // 8 warps x 4 KB (MODE_GEMM only)
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -106,7 +109,7 @@ tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
     }
     for (int s = 0; s < 2; ++s) {
       mbar_init(&tfull_bar[s], 1);
-      mbar_init(&tempty_bar[s], 4);
+      mbar_init(&tempty_bar[s], 8);
     }
     fence_barrier_init();
   }
@@ -254,7 +257,13 @@ tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
     }
   } else if (warp >= 4) {
     // ======================================= epilogue ===========================================
-    const int ew = warp - 4;                 // == warp % 4 -> TMEM lanes [32*ew, 32*ew+32)
+    // two epilogue warps per TMEM lane quarter: warps 4-7 drain the first half of the accumulator columns, warps 8-11
+    // the second half (small-K GEMMs are paced by the epilogue, not by the MMAs)
+    const int ew = (warp - 4) & 3;           // == warp % 4 -> TMEM lanes [32*ew, 32*ew+32)
+    const int ehalf = (warp - 4) >> 2;
+    const int cols_half = ((static_cast<int>(acc_cols) + 63) / 64) * 32;
+    const int cc_begin = ehalf * cols_half;
+    const int cc_end = min(cc_begin + cols_half, static_cast<int>(acc_cols));
     int acc = 0;
     uint32_t acc_phase = 0;
     for (int item = blockIdx.x; item < num_items; item += gridDim.x) {
@@ -271,7 +280,7 @@ tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
       tc_fence_after();
       const uint32_t taddr = tmem_base + (static_cast<uint32_t>(ew * 32) << 16) + static_cast<uint32_t>(acc) * acc_cols;
       float ssum = 0.f, ssq = 0.f;
-      for (int cc = 0; cc < static_cast<int>(acc_cols); cc += 32) {
+      for (int cc = cc_begin; cc < cc_end; cc += 32) {
         // cc walks all accumulator columns of the item; c0 is the column inside the current tap's tile
         const int tsub = cc / p.block_n;
         const int c0 = cc - tsub * p.block_n;
@@ -289,50 +298,72 @@ tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
 #pragma unroll
               for (int j = 0; j < 32; ++j)
                 if (n0 + c0 + j < p.N) atomicAdd(o + j, __uint_as_float(v[j]) * p.alpha);
-            } else {
-              float f[32];
+            }
+          }
+          if (!p.atomic) {
+            float f[32];
 #pragma unroll
-              for (int j = 0; j < 32; ++j) {
-                float x = __uint_as_float(v[j]) * p.alpha;
-                const int col = n0 + c0 + j;
-                if (p.bias != nullptr && col < p.N) x += __ldg(p.bias + col);
-                if (p.act == 1) x = fmaxf(x, 0.f);
-                else if (p.act == 2) x = gelu_tanh(x);
-                f[j] = x;
+            for (int j = 0; j < 32; ++j) {
+              float x = __uint_as_float(v[j]) * p.alpha;
+              const int col = n0 + c0 + j;
+              if (p.bias != nullptr && col < p.N) x += __ldg(p.bias + col);
+              if (p.act == 1) x = fmaxf(x, 0.f);
+              else if (p.act == 2) x = gelu_tanh(x);
+              f[j] = x;
+            }
+            const bool full = (n0 + c0 + 32 <= p.N);
+            if (p.st_vec && full) {
+              // warp-uniform path: transpose the warp's 32x32 chunk through shared memory (XOR-swizzled 16-byte pieces,
+              // conflict-free both ways) so that every global store instruction writes whole row segments
+              uint8_t* stg = epi_stage + (warp - 4) * 4096;
+              const int row0 = m_blk * kBlockM + ew * 32;
+              if (p.out_bf16) {
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                  __nv_bfloat162 h0 = __floats2bfloat162_rn(f[8 * j], f[8 * j + 1]);
+                  __nv_bfloat162 h1 = __floats2bfloat162_rn(f[8 * j + 2], f[8 * j + 3]);
+                  __nv_bfloat162 h2 = __floats2bfloat162_rn(f[8 * j + 4], f[8 * j + 5]);
+                  __nv_bfloat162 h3 = __floats2bfloat162_rn(f[8 * j + 6], f[8 * j + 7]);
+                  uint4 u;
+                  u.x = *reinterpret_cast<uint32_t*>(&h0); u.y = *reinterpret_cast<uint32_t*>(&h1);
+                  u.z = *reinterpret_cast<uint32_t*>(&h2); u.w = *reinterpret_cast<uint32_t*>(&h3);
+                  *reinterpret_cast<uint4*>(stg + lane * 64 + ((j ^ ((lane >> 1) & 3)) << 4)) = u;
+                }
+                __syncwarp();
+                __nv_bfloat16* ob = reinterpret_cast<__nv_bfloat16*>(p.out) + boff + n0 + c0;
+#pragma unroll
+                for (int it = 0; it < 4; ++it) {
+                  const int r = it * 8 + (lane >> 2), q = lane & 3;
+                  const uint4 u = *reinterpret_cast<const uint4*>(stg + r * 64 + ((q ^ ((r >> 1) & 3)) << 4));
+                  if (row0 + r < p.M) *reinterpret_cast<uint4*>(ob + static_cast<long long>(row0 + r) * p.ldo + q * 8) = u;
+                }
+                __syncwarp();
+              } else {
+#pragma unroll
+                for (int j = 0; j < 8; ++j)
+                  *reinterpret_cast<float4*>(stg + lane * 128 + ((j ^ (lane & 7)) << 4)) =
+                      make_float4(f[4 * j], f[4 * j + 1], f[4 * j + 2], f[4 * j + 3]);
+                __syncwarp();
+                float* of = reinterpret_cast<float*>(p.out) + boff + n0 + c0;
+#pragma unroll
+                for (int it = 0; it < 8; ++it) {
+                  const int r = it * 4 + (lane >> 3), q = lane & 7;
+                  const float4 u = *reinterpret_cast<const float4*>(stg + r * 128 + ((q ^ (r & 7)) << 4));
+                  if (row0 + r < p.M) *reinterpret_cast<float4*>(of + static_cast<long long>(row0 + r) * p.ldo + q * 4) = u;
+                }
+                __syncwarp();
               }
-              const bool full = (n0 + c0 + 32 <= p.N);
+            } else if (row < p.M) {
               if (p.out_bf16) {
                 __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(p.out) + boff + static_cast<long long>(row) * p.ldo + n0 + c0;
-                if (full && ((reinterpret_cast<uintptr_t>(o) & 15) == 0)) {
 #pragma unroll
-                  for (int j = 0; j < 32; j += 8) {
-                    __nv_bfloat162 h0 = __floats2bfloat162_rn(f[j], f[j + 1]);
-                    __nv_bfloat162 h1 = __floats2bfloat162_rn(f[j + 2], f[j + 3]);
-                    __nv_bfloat162 h2 = __floats2bfloat162_rn(f[j + 4], f[j + 5]);
-                    __nv_bfloat162 h3 = __floats2bfloat162_rn(f[j + 6], f[j + 7]);
-                    uint4 u;
-                    u.x = *reinterpret_cast<uint32_t*>(&h0);
-                    u.y = *reinterpret_cast<uint32_t*>(&h1);
-                    u.z = *reinterpret_cast<uint32_t*>(&h2);
-                    u.w = *reinterpret_cast<uint32_t*>(&h3);
-                    *reinterpret_cast<uint4*>(o + j) = u;
-                  }
-                } else {
-#pragma unroll
-                  for (int j = 0; j < 32; ++j)
-                    if (n0 + c0 + j < p.N) o[j] = __float2bfloat16(f[j]);
-                }
+                for (int j = 0; j < 32; ++j)
+                  if (n0 + c0 + j < p.N) o[j] = __float2bfloat16(f[j]);
               } else {
                 float* o = reinterpret_cast<float*>(p.out) + boff + static_cast<long long>(row) * p.ldo + n0 + c0;
-                if (full && ((reinterpret_cast<uintptr_t>(o) & 15) == 0)) {
 #pragma unroll
-                  for (int j = 0; j < 32; j += 4)
-                    *reinterpret_cast<float4*>(o + j) = make_float4(f[j], f[j + 1], f[j + 2], f[j + 3]);
-                } else {
-#pragma unroll
-                  for (int j = 0; j < 32; ++j)
-                    if (n0 + c0 + j < p.N) o[j] = f[j];
-                }
+                for (int j = 0; j < 32; ++j)
+                  if (n0 + c0 + j < p.N) o[j] = f[j];
               }
             }
           }
@@ -429,9 +460,11 @@ static int num_sms() {
   return g_num_sms;
 }
 
-static int pick_stages(int block_n, int tpi) {
+constexpr int kEpiStageBytes = 8 * 4096;   // MODE_GEMM epilogue staging: 4 KB per epilogue warp
+
+static int pick_stages(int block_n, int tpi, int reserve) {
   const int stage = kStageABytes + block_n * 128 * tpi;
-  int s = (220 * 1024) / stage;
+  int s = (224 * 1024 - reserve) / stage;
   if (s > kMaxStages) s = kMaxStages;
   if (s < 2) s = 2;
   return s;
@@ -441,8 +474,9 @@ template <int kMode, bool kBF16>
 static int launch_tc(const CUtensorMap& a, const CUtensorMap& b, TcParams& p, cudaStream_t stream) {
   if (p.tpi < 1) p.tpi = 1;
   p.acc_stages = (2 * p.tpi * p.block_n <= 512) ? 2 : 1;
-  p.num_stages = pick_stages(p.block_n, p.tpi);
-  const size_t smem = static_cast<size_t>(p.num_stages) * (kStageABytes + p.block_n * 128 * p.tpi) + 1024 /*align*/ + 256;
+  const int reserve = (kMode == MODE_GEMM) ? kEpiStageBytes : 0;
+  p.num_stages = pick_stages(p.block_n, p.tpi, reserve);
+  const size_t smem = static_cast<size_t>(p.num_stages) * (kStageABytes + p.block_n * 128 * p.tpi) + 1024 /*align*/ + 256 + reserve;
   static bool attr_set = false;
   if (!attr_set) {
     cudaError_t e = cudaFuncSetAttribute(tc_kernel<kMode, kBF16>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
@@ -499,6 +533,11 @@ extern "C" int ddpx_gemm_batched(const void* A, const void* B, void* D, int M, i
   p.atomic = (accumulate || p.num_splits > 1) ? 1 : 0;
   if (p.atomic && out_bf16) return DDPX_ERR_ARG;
   p.act = act; p.bias = bias;
+  {
+    const int oe = out_bf16 ? 2 : 4;
+    p.st_vec = ((ldd * oe) % 16 == 0 && (d_bs1 * oe) % 16 == 0 && (d_bs2 * oe) % 16 == 0 &&
+                (reinterpret_cast<uintptr_t>(D) & 15) == 0) ? 1 : 0;
+  }
   CUtensorMap ta, tb;
   int rc;
   {

@@ -8,6 +8,7 @@
 #include <cuda_bf16.h>
 #include <stdint.h>
 #include <string.h>
+#include "vec.cuh"
 #include "../../include/ddpx_kernels.h"
 
 namespace {
@@ -78,6 +79,113 @@ __global__ void softmax_ce_kernel(const T* __restrict__ logits, const long long*
   }
 }
 
+// ---- two-kernel form used by the autograd ops: the forward reads the logits ONCE (online max / sum-of-exp, 16-byte
+// loads) and keeps one log-sum-exp per row; the backward reads them once more and writes
+// dlogits = (softmax - onehot) * g / rows with the upstream scalar gradient g taken from device memory (no host sync,
+// no separate scaling pass).  Columns [cols, ld) (vocabulary padding) get a zero gradient.
+template <typename T>
+__global__ void __launch_bounds__(512)
+ce_fwd_kernel(const T* __restrict__ logits, const long long* __restrict__ targets, float* __restrict__ lse,
+              float* __restrict__ loss_sum, long long rows, int cols, long long ld, float inv_rows, long long ignore_index,
+              int vec_ok) {
+  constexpr int V = sizeof(T) == 2 ? 8 : 4;
+  __shared__ float sh[66];
+  for (long long row = blockIdx.x; row < rows; row += gridDim.x) {
+    const T* x = logits + row * ld;
+    float mx = -INFINITY, se = 0.f;
+    const int nvec = vec_ok ? cols / V : 0;
+    for (int i = threadIdx.x; i < nvec; i += blockDim.x) {
+      const uint4 u = *reinterpret_cast<const uint4*>(x + i * V);
+      float f[V];
+      if (sizeof(T) == 2) {
+        const uint32_t w[4] = {u.x, u.y, u.z, u.w};
+#pragma unroll
+        for (int k = 0; k < 4; ++k) { f[2 * k] = __uint_as_float(w[k] << 16); f[2 * k + 1] = __uint_as_float(w[k] & 0xffff0000u); }
+      } else {
+        f[0] = __uint_as_float(u.x); f[1] = __uint_as_float(u.y); f[2] = __uint_as_float(u.z); f[3] = __uint_as_float(u.w);
+      }
+      float m2 = mx;
+#pragma unroll
+      for (int k = 0; k < V; ++k) m2 = fmaxf(m2, f[k]);
+      float acc = 0.f;
+#pragma unroll
+      for (int k = 0; k < V; ++k) acc += __expf(f[k] - m2);
+      se = se * __expf(mx - m2) + acc;
+      mx = m2;
+    }
+    for (int c = nvec * V + threadIdx.x; c < cols; c += blockDim.x) {
+      const float v = to_f(x[c]);
+      const float m2 = fmaxf(mx, v);
+      se = se * __expf(mx - m2) + __expf(v - m2);
+      mx = m2;
+    }
+    // combine (max, sum) pairs across the block
+    const float bm = block_reduce(mx, sh, true);
+    const float contrib = (mx == -INFINITY) ? 0.f : se * __expf(mx - bm);
+    const float bs = block_reduce(contrib, sh + 33, false);
+    if (threadIdx.x == 0) {
+      const float l = bm + __logf(bs);
+      lse[row] = l;
+      const long long tgt = targets[row];
+      if (tgt != ignore_index && tgt >= 0 && tgt < cols && loss_sum != nullptr) atomicAdd(loss_sum, (l - to_f(x[tgt])) * inv_rows);
+    }
+    __syncthreads();
+  }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(512)
+ce_bwd_kernel(const T* __restrict__ logits, const long long* __restrict__ targets, const float* __restrict__ lse,
+              const float* __restrict__ g, T* __restrict__ dlogits, long long rows, int cols, long long ld, float inv_rows,
+              long long ignore_index, int vec_ok) {
+  constexpr int V = sizeof(T) == 2 ? 8 : 4;
+  const float gs = (g != nullptr ? *g : 1.f) * inv_rows;
+  for (long long row = blockIdx.x; row < rows; row += gridDim.x) {
+    const T* x = logits + row * ld;
+    T* d = dlogits + row * ld;
+    const long long tgt = targets[row];
+    const bool valid = (tgt != ignore_index) && tgt >= 0 && tgt < cols;
+    const float sc = valid ? gs : 0.f;
+    const float l = lse[row];
+    const int nvec = vec_ok ? cols / V : 0;
+    for (int i = threadIdx.x; i < nvec; i += blockDim.x) {
+      const uint4 u = *reinterpret_cast<const uint4*>(x + i * V);
+      float f[V];
+      if (sizeof(T) == 2) {
+        const uint32_t w[4] = {u.x, u.y, u.z, u.w};
+#pragma unroll
+        for (int k = 0; k < 4; ++k) { f[2 * k] = __uint_as_float(w[k] << 16); f[2 * k + 1] = __uint_as_float(w[k] & 0xffff0000u); }
+      } else {
+        f[0] = __uint_as_float(u.x); f[1] = __uint_as_float(u.y); f[2] = __uint_as_float(u.z); f[3] = __uint_as_float(u.w);
+      }
+#pragma unroll
+      for (int k = 0; k < V; ++k) {
+        float pr = __expf(f[k] - l);
+        if (i * V + k == tgt) pr -= 1.f;
+        f[k] = pr * sc;
+      }
+      uint4 o;
+      if (sizeof(T) == 2) {
+        uint32_t w[4];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) { __nv_bfloat162 h = __floats2bfloat162_rn(f[2 * k], f[2 * k + 1]); w[k] = *reinterpret_cast<uint32_t*>(&h); }
+        o = make_uint4(w[0], w[1], w[2], w[3]);
+      } else {
+        o = make_uint4(__float_as_uint(f[0]), __float_as_uint(f[1]), __float_as_uint(f[2]), __float_as_uint(f[3]));
+      }
+      *reinterpret_cast<uint4*>(d + i * V) = o;
+    }
+    for (int c = nvec * V + threadIdx.x; c < ld; c += blockDim.x) {
+      float pr = 0.f;
+      if (c < cols) {
+        pr = __expf(to_f(x[c]) - l);
+        if (c == tgt) pr -= 1.f;
+      }
+      d[c] = from_f<T>(pr * sc);
+    }
+  }
+}
+
 // dlogits *= g (chain rule when the upstream gradient of the scalar loss is not 1)
 template <typename T>
 __global__ void scale_inplace_kernel(T* __restrict__ p, long long n, const float* __restrict__ g) {
@@ -137,7 +245,28 @@ __global__ void sgd_multi_kernel(const __grid_constant__ TensorTable t, float lr
     T* __restrict__ p = static_cast<T*>(t.p[ti]);
     const T* __restrict__ g = static_cast<const T*>(t.g[ti]);
     T* __restrict__ buf = static_cast<T*>(t.s0[ti]);
-    for (long long i = base + threadIdx.x; i < end; i += blockDim.x) {
+    constexpr int V = ddpx::VecOf<T>::N;
+    const bool al = ((reinterpret_cast<uintptr_t>(p) | reinterpret_cast<uintptr_t>(g) | reinterpret_cast<uintptr_t>(buf)) & 15) == 0;
+    const long long nvec = al ? (end - base) / V : 0;
+    for (long long vi = threadIdx.x; vi < nvec; vi += blockDim.x) {
+      const long long i = base + vi * V;
+      float pv[V], gv[V], bv[V];
+      ddpx::vload(p + i, pv); ddpx::vload(g + i, gv);
+      if (momentum != 0.f && !first_step) ddpx::vload(buf + i, bv);
+#pragma unroll
+      for (int k = 0; k < V; ++k) {
+        float gg = gv[k] * grad_scale + wd * pv[k];
+        if (momentum != 0.f) {
+          const float b = first_step ? gg : momentum * bv[k] + (1.f - dampening) * gg;
+          bv[k] = b;
+          gg = nesterov ? gg + momentum * b : b;
+        }
+        pv[k] -= lr * gg;
+      }
+      if (momentum != 0.f) ddpx::vstore(buf + i, bv);
+      ddpx::vstore(p + i, pv);
+    }
+    for (long long i = base + nvec * V + threadIdx.x; i < end; i += blockDim.x) {
       float pv = to_f(p[i]);
       float gv = to_f(g[i]) * grad_scale + wd * pv;
       if (momentum != 0.f) {
@@ -164,7 +293,25 @@ __global__ void adamw_multi_kernel(const __grid_constant__ TensorTable t, float 
     const T* __restrict__ g = static_cast<const T*>(t.g[ti]);
     T* __restrict__ m = static_cast<T*>(t.s0[ti]);
     T* __restrict__ v = static_cast<T*>(t.s1[ti]);
-    for (long long i = base + threadIdx.x; i < end; i += blockDim.x) {
+    constexpr int V = ddpx::VecOf<T>::N;
+    const bool al = ((reinterpret_cast<uintptr_t>(p) | reinterpret_cast<uintptr_t>(g) | reinterpret_cast<uintptr_t>(m) |
+                      reinterpret_cast<uintptr_t>(v)) & 15) == 0;
+    const long long nvec = al ? (end - base) / V : 0;
+    for (long long vi = threadIdx.x; vi < nvec; vi += blockDim.x) {
+      const long long i = base + vi * V;
+      float pv[V], gv[V], mv[V], vv[V];
+      ddpx::vload(p + i, pv); ddpx::vload(g + i, gv); ddpx::vload(m + i, mv); ddpx::vload(v + i, vv);
+#pragma unroll
+      for (int k = 0; k < V; ++k) {
+        const float gg = gv[k] * grad_scale;
+        pv[k] *= (1.f - lr * wd);
+        mv[k] = beta1 * mv[k] + (1.f - beta1) * gg;
+        vv[k] = beta2 * vv[k] + (1.f - beta2) * gg * gg;
+        pv[k] -= (lr / bc1) * mv[k] / (sqrtf(vv[k]) / bc2_sqrt + eps);
+      }
+      ddpx::vstore(m + i, mv); ddpx::vstore(v + i, vv); ddpx::vstore(p + i, pv);
+    }
+    for (long long i = base + nvec * V + threadIdx.x; i < end; i += blockDim.x) {
       const float gv = to_f(g[i]) * grad_scale;
       float pv = to_f(p[i]) * (1.f - lr * wd);
       const float mv = beta1 * to_f(m[i]) + (1.f - beta1) * gv;
@@ -215,6 +362,45 @@ extern "C" int ddpx_softmax_ce(const void* logits, const long long* targets, voi
   else
     softmax_ce_kernel<float><<<grid, block, 0, s>>>(static_cast<const float*>(logits), targets, static_cast<float*>(dlogits),
                                                    loss_sum, rows, cols, ld, inv_rows, ignore_index, grad_scale);
+  return LAUNCH_OK();
+}
+
+extern "C" int ddpx_ce_fwd(const void* logits, const long long* targets, float* lse, float* loss_sum, long long rows,
+                           int cols, long long ld, int bf16, long long ignore_index, void* stream) {
+  if (rows <= 0 || cols <= 0) return DDPX_ERR_ARG;
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  if (loss_sum != nullptr) cudaMemsetAsync(loss_sum, 0, sizeof(float), s);
+  const int es = bf16 ? 2 : 4;
+  const int vec_ok = ((ld * es) % 16 == 0 && (reinterpret_cast<uintptr_t>(logits) & 15) == 0) ? 1 : 0;
+  const int block = cols >= 8192 ? 512 : (cols >= 512 ? 256 : 64);
+  const int grid = rows < 148 * 16 ? static_cast<int>(rows) : 148 * 16;
+  const float inv_rows = 1.f / static_cast<float>(rows);
+  if (bf16)
+    ce_fwd_kernel<__nv_bfloat16><<<grid, block, 0, s>>>(static_cast<const __nv_bfloat16*>(logits), targets, lse, loss_sum, rows,
+                                                       cols, ld, inv_rows, ignore_index, vec_ok);
+  else
+    ce_fwd_kernel<float><<<grid, block, 0, s>>>(static_cast<const float*>(logits), targets, lse, loss_sum, rows, cols, ld,
+                                               inv_rows, ignore_index, vec_ok);
+  return LAUNCH_OK();
+}
+
+extern "C" int ddpx_ce_bwd(const void* logits, const long long* targets, const float* lse, const float* g, void* dlogits,
+                           long long rows, int cols, long long ld, int bf16, long long ignore_index, void* stream) {
+  if (rows <= 0 || cols <= 0) return DDPX_ERR_ARG;
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  const int es = bf16 ? 2 : 4;
+  const int vec_ok = ((ld * es) % 16 == 0 && (reinterpret_cast<uintptr_t>(logits) & 15) == 0 &&
+                      (reinterpret_cast<uintptr_t>(dlogits) & 15) == 0) ? 1 : 0;
+  const int block = cols >= 8192 ? 512 : (cols >= 512 ? 256 : 64);
+  const int grid = rows < 148 * 16 ? static_cast<int>(rows) : 148 * 16;
+  const float inv_rows = 1.f / static_cast<float>(rows);
+  if (bf16)
+    ce_bwd_kernel<__nv_bfloat16><<<grid, block, 0, s>>>(static_cast<const __nv_bfloat16*>(logits), targets, lse, g,
+                                                       static_cast<__nv_bfloat16*>(dlogits), rows, cols, ld, inv_rows,
+                                                       ignore_index, vec_ok);
+  else
+    ce_bwd_kernel<float><<<grid, block, 0, s>>>(static_cast<const float*>(logits), targets, lse, g, static_cast<float*>(dlogits),
+                                               rows, cols, ld, inv_rows, ignore_index, vec_ok);
   return LAUNCH_OK();
 }
 

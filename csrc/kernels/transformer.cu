@@ -1,14 +1,15 @@
 // Transformer-side kernels for the GPT-2 / MLP configs of BASELINE.json (absent from the reference):
-// LayerNorm fwd/bwd, GELU(tanh) fwd/bwd, residual add, token+position embedding fwd/bwd, causal softmax fwd/bwd for the
-// attention score matrices produced by the batched tcgen05 GEMM, plus small bf16 helpers (ReLU backward, column sums,
-// casts, scaled copies).  All templated on the storage type (fp32 or bf16), math in fp32.  sm_100a.
+// LayerNorm fwd/bwd, GELU(tanh) fwd/bwd, residual add, bf16 helpers (ReLU backward, column sums, casts, scaled copies),
+// dropout.  Templated on the storage type (fp32 or bf16), math in fp32, 16-byte vector accesses, sm_100a.
 #include <cuda_runtime.h>
 #include <cuda_bf16.h>
 #include <stdint.h>
+#include "vec.cuh"
 #include "../../include/ddpx_kernels.h"
 
 namespace {
 
+using namespace ddpx;
 typedef __nv_bfloat16 bf16;
 
 template <typename T> __device__ __forceinline__ float ldf(const T* p);
@@ -18,84 +19,112 @@ template <typename T> __device__ __forceinline__ void stf(T* p, float v);
 template <> __device__ __forceinline__ void stf<float>(float* p, float v) { *p = v; }
 template <> __device__ __forceinline__ void stf<bf16>(bf16* p, float v) { *p = __float2bfloat16(v); }
 
-__device__ __forceinline__ float warp_sum(float v) {
-#pragma unroll
-  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-  return v;
-}
-__device__ __forceinline__ float warp_max(float v) {
-#pragma unroll
-  for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
-  return v;
-}
-// block-wide sum of two values at once (blockDim.x <= 1024)
-__device__ __forceinline__ void block_sum2(float& a, float& b, float* sh) {
-  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5, nw = (blockDim.x + 31) >> 5;
-  a = warp_sum(a); b = warp_sum(b);
-  __syncthreads();
-  if (lane == 0) { sh[w] = a; sh[32 + w] = b; }
-  __syncthreads();
-  float x = (threadIdx.x < nw) ? sh[threadIdx.x] : 0.f;
-  float y = (threadIdx.x < nw) ? sh[32 + threadIdx.x] : 0.f;
-  if (w == 0) {
-    x = warp_sum(x); y = warp_sum(y);
-    if (lane == 0) { sh[0] = x; sh[32] = y; }
-  }
-  __syncthreads();
-  a = sh[0]; b = sh[32];
-}
-
 inline int cap_blocks(long long n, int cap = 148 * 16) { return static_cast<int>(n < 1 ? 1 : (n > cap ? cap : n)); }
 
 // ------------------------------------------------------------------------------------------------ LayerNorm
-// one block per row (grid-stride); saves mean / rstd (fp32) for the backward
+// One warp per row, 16-byte loads; C must be a multiple of the vector width.  mean / rstd (fp32) are saved.
 template <typename T>
-__global__ void layernorm_fwd_kernel(const T* __restrict__ x, const T* __restrict__ gamma, const T* __restrict__ beta,
-                                     T* __restrict__ y, float* __restrict__ mean, float* __restrict__ rstd, long long rows,
-                                     int C, float eps) {
-  __shared__ float sh[64];
-  for (long long r = blockIdx.x; r < rows; r += gridDim.x) {
+__global__ void __launch_bounds__(256)
+layernorm_fwd_kernel(const T* __restrict__ x, const T* __restrict__ gamma, const T* __restrict__ beta, T* __restrict__ y,
+                     float* __restrict__ mean, float* __restrict__ rstd, long long rows, int C, float eps) {
+  constexpr int V = VecOf<T>::N;
+  const int lane = threadIdx.x & 31;
+  const long long warp0 = (static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
+  const long long nwarps = (static_cast<long long>(gridDim.x) * blockDim.x) >> 5;
+  const int nvec = C / V;
+  for (long long r = warp0; r < rows; r += nwarps) {
     const T* xr = x + r * C;
     float s = 0.f, q = 0.f;
-    for (int c = threadIdx.x; c < C; c += blockDim.x) { const float v = ldf(xr + c); s += v; q += v * v; }
-    block_sum2(s, q, sh);
+    for (int i = lane; i < nvec; i += 32) {
+      float f[V];
+      vload(xr + i * V, f);
+#pragma unroll
+      for (int k = 0; k < V; ++k) { s += f[k]; q += f[k] * f[k]; }
+    }
+    s = warp_sum_f(s); q = warp_sum_f(q);
     const float m = s / C;
     const float rs = rsqrtf(fmaxf(q / C - m * m, 0.f) + eps);
-    if (threadIdx.x == 0) { mean[r] = m; rstd[r] = rs; }
+    if (lane == 0) { mean[r] = m; rstd[r] = rs; }
     T* yr = y + r * C;
-    for (int c = threadIdx.x; c < C; c += blockDim.x)
-      stf(yr + c, (ldf(xr + c) - m) * rs * ldf(gamma + c) + ldf(beta + c));
+    for (int i = lane; i < nvec; i += 32) {
+      float f[V], g[V], b[V];
+      vload(xr + i * V, f); vload(gamma + i * V, g); vload(beta + i * V, b);
+#pragma unroll
+      for (int k = 0; k < V; ++k) f[k] = (f[k] - m) * rs * g[k] + b[k];
+      vstore(yr + i * V, f);
+    }
   }
 }
 
-// dx per row + per-block partial dgamma/dbeta accumulated into fp32 [C] buffers with atomics (pre-zeroed)
-template <typename T>
-__global__ void layernorm_bwd_kernel(const T* __restrict__ x, const T* __restrict__ dy, const T* __restrict__ gamma,
-                                     const float* __restrict__ mean, const float* __restrict__ rstd, T* __restrict__ dx,
-                                     float* __restrict__ dgamma, float* __restrict__ dbeta, long long rows, int C) {
-  extern __shared__ float acc[];   // [2][C] per-block partial dgamma / dbeta
-  __shared__ float sh[64];
+// Backward: one warp per row; each lane keeps the dgamma / dbeta partial sums of its own columns in registers over all
+// the rows its warp visits (NV vectors per lane), then the block folds them through shared memory and issues one
+// atomic per column into the fp32 accumulators (pre-zeroed).
+template <typename T, int NV>
+__global__ void __launch_bounds__(256)
+layernorm_bwd_kernel(const T* __restrict__ x, const T* __restrict__ dy, const T* __restrict__ gamma,
+                     const float* __restrict__ mean, const float* __restrict__ rstd, T* __restrict__ dx,
+                     float* __restrict__ dgamma, float* __restrict__ dbeta, long long rows, int C) {
+  constexpr int V = VecOf<T>::N;
+  extern __shared__ float acc[];   // [2][C]
+  const int lane = threadIdx.x & 31;
+  const long long warp0 = (static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
+  const long long nwarps = (static_cast<long long>(gridDim.x) * blockDim.x) >> 5;
+  const int nvec = C / V;
   for (int c = threadIdx.x; c < 2 * C; c += blockDim.x) acc[c] = 0.f;
   __syncthreads();
-  for (long long r = blockIdx.x; r < rows; r += gridDim.x) {
+  float ag[NV][V], ab[NV][V];
+#pragma unroll
+  for (int j = 0; j < NV; ++j)
+#pragma unroll
+    for (int k = 0; k < V; ++k) { ag[j][k] = 0.f; ab[j][k] = 0.f; }
+  for (long long r = warp0; r < rows; r += nwarps) {
     const T* xr = x + r * C;
     const T* dr = dy + r * C;
     const float m = mean[r], rs = rstd[r];
     float s1 = 0.f, s2 = 0.f;
-    for (int c = threadIdx.x; c < C; c += blockDim.x) {
-      const float g = ldf(dr + c) * ldf(gamma + c);
-      const float xh = (ldf(xr + c) - m) * rs;
-      s1 += g; s2 += g * xh;
+#pragma unroll
+    for (int j = 0; j < NV; ++j) {
+      const int i = lane + j * 32;
+      if (i < nvec) {
+        float f[V], d[V], g[V];
+        vload(xr + i * V, f); vload(dr + i * V, d); vload(gamma + i * V, g);
+#pragma unroll
+        for (int k = 0; k < V; ++k) {
+          const float xh = (f[k] - m) * rs;
+          const float gd = d[k] * g[k];
+          s1 += gd; s2 += gd * xh;
+          ag[j][k] += d[k] * xh;
+          ab[j][k] += d[k];
+        }
+      }
     }
-    block_sum2(s1, s2, sh);
+    s1 = warp_sum_f(s1); s2 = warp_sum_f(s2);
     const float a = s1 / C, b = s2 / C;
     T* dxr = dx + r * C;
-    for (int c = threadIdx.x; c < C; c += blockDim.x) {
-      const float d = ldf(dr + c);
-      const float xh = (ldf(xr + c) - m) * rs;
-      stf(dxr + c, rs * (d * ldf(gamma + c) - a - xh * b));
-      acc[c] += d * xh;        // each thread owns its columns: no race
-      acc[C + c] += d;
+#pragma unroll
+    for (int j = 0; j < NV; ++j) {
+      const int i = lane + j * 32;
+      if (i < nvec) {
+        float f[V], d[V], g[V];
+        vload(xr + i * V, f); vload(dr + i * V, d); vload(gamma + i * V, g);
+#pragma unroll
+        for (int k = 0; k < V; ++k) {
+          const float xh = (f[k] - m) * rs;
+          f[k] = rs * (d[k] * g[k] - a - xh * b);
+        }
+        vstore(dxr + i * V, f);
+      }
+    }
+  }
+#pragma unroll
+  for (int j = 0; j < NV; ++j) {
+    const int i = lane + j * 32;
+    if (i < nvec) {
+#pragma unroll
+      for (int k = 0; k < V; ++k) {
+        atomicAdd(&acc[i * V + k], ag[j][k]);
+        atomicAdd(&acc[C + i * V + k], ab[j][k]);
+      }
     }
   }
   __syncthreads();
@@ -105,7 +134,7 @@ __global__ void layernorm_bwd_kernel(const T* __restrict__ x, const T* __restric
   }
 }
 
-// ------------------------------------------------------------------------------------------------ GELU / add / casts
+// ------------------------------------------------------------------------------------------------ elementwise
 __device__ __forceinline__ float gelu_f(float x) {
   const float k0 = 0.7978845608028654f, k1 = 0.044715f;
   return 0.5f * x * (1.f + tanhf(k0 * (x + k1 * x * x * x)));
@@ -116,38 +145,63 @@ __device__ __forceinline__ float gelu_grad_f(float x) {
   const float t = tanhf(u);
   return 0.5f * (1.f + t) + 0.5f * x * (1.f - t * t) * k0 * (1.f + 3.f * k1 * x * x);
 }
-template <typename T>
-__global__ void gelu_fwd_kernel(const T* __restrict__ x, T* __restrict__ y, long long n) {
-  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < n; i += static_cast<long long>(gridDim.x) * blockDim.x)
-    stf(y + i, gelu_f(ldf(x + i)));
+
+enum { OP_GELU_FWD = 0, OP_GELU_BWD = 1, OP_RELU_BWD = 2, OP_ADD = 3 };
+
+// out = op(a[, b]) over n elements; vector body + scalar tail
+template <typename T, int OP>
+__global__ void __launch_bounds__(256)
+ew_kernel(const T* __restrict__ a, const T* __restrict__ b, T* __restrict__ out, long long n) {
+  constexpr int V = VecOf<T>::N;
+  const long long nvec = n / V;
+  const long long tid = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  const long long nth = static_cast<long long>(gridDim.x) * blockDim.x;
+  for (long long i = tid; i < nvec; i += nth) {
+    float fa[V], fb[V];
+    vload(a + i * V, fa);
+    if (OP != OP_GELU_FWD) vload(b + i * V, fb);
+#pragma unroll
+    for (int k = 0; k < V; ++k) {
+      if (OP == OP_GELU_FWD) fa[k] = gelu_f(fa[k]);
+      else if (OP == OP_GELU_BWD) fa[k] = fb[k] * gelu_grad_f(fa[k]);   // a = pre-activation, b = dy
+      else if (OP == OP_RELU_BWD) fa[k] = fa[k] > 0.f ? fb[k] : 0.f;    // a = y, b = dy
+      else fa[k] = fa[k] + fb[k];
+    }
+    vstore(out + i * V, fa);
+  }
+  for (long long i = nvec * V + tid; i < n; i += nth) {
+    const float x = ldf(a + i);
+    const float y = (OP != OP_GELU_FWD) ? ldf(b + i) : 0.f;
+    float r;
+    if (OP == OP_GELU_FWD) r = gelu_f(x);
+    else if (OP == OP_GELU_BWD) r = y * gelu_grad_f(x);
+    else if (OP == OP_RELU_BWD) r = x > 0.f ? y : 0.f;
+    else r = x + y;
+    stf(out + i, r);
+  }
 }
-template <typename T>
-__global__ void gelu_bwd_kernel(const T* __restrict__ x, const T* __restrict__ dy, T* __restrict__ dx, long long n) {
-  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < n; i += static_cast<long long>(gridDim.x) * blockDim.x)
-    stf(dx + i, ldf(dy + i) * gelu_grad_f(ldf(x + i)));
-}
-template <typename T>
-__global__ void relu_bwd_t_kernel(const T* __restrict__ y, const T* __restrict__ dy, T* __restrict__ dx, long long n) {
-  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < n; i += static_cast<long long>(gridDim.x) * blockDim.x)
-    stf(dx + i, ldf(y + i) > 0.f ? ldf(dy + i) : 0.f);
-}
-template <typename T>
-__global__ void add_kernel(const T* __restrict__ a, const T* __restrict__ b, T* __restrict__ out, long long n) {
-  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < n; i += static_cast<long long>(gridDim.x) * blockDim.x)
-    stf(out + i, ldf(a + i) + ldf(b + i));
-}
+
 template <typename TS, typename TD>
 __global__ void cast_scale_kernel(const TS* __restrict__ src, TD* __restrict__ dst, long long n, float scale) {
   for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < n; i += static_cast<long long>(gridDim.x) * blockDim.x)
     stf(dst + i, ldf(src + i) * scale);
 }
-template <typename T>
-__global__ void colsum_t_kernel(const T* __restrict__ x, float* __restrict__ out, long long rows, int cols) {
-  const int c = blockIdx.x * blockDim.x + threadIdx.x;
-  if (c >= cols) return;
+// column sums of a bf16 matrix: block = 32 columns x 8 row lanes, rows split over gridDim.y, fp32 atomics
+__global__ void colsum_bf16_kernel(const bf16* __restrict__ x, float* __restrict__ out, long long rows, int cols) {
+  __shared__ float sh[8][33];
+  const int c = blockIdx.x * 32 + threadIdx.x;
   float s = 0.f;
-  for (long long r = blockIdx.y; r < rows; r += gridDim.y) s += ldf(x + r * cols + c);
-  atomicAdd(out + c, s);
+  if (c < cols)
+    for (long long r = static_cast<long long>(blockIdx.y) * 8 + threadIdx.y; r < rows; r += static_cast<long long>(gridDim.y) * 8)
+      s += __bfloat162float(x[r * cols + c]);
+  sh[threadIdx.y][threadIdx.x] = s;
+  __syncthreads();
+  if (threadIdx.y == 0 && c < cols) {
+    float t = 0.f;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) t += sh[j][threadIdx.x];
+    atomicAdd(out + c, t);
+  }
 }
 // inverted dropout with a counter-based hash RNG: keep iff hash(seed, i) >= p * 2^32
 __device__ __forceinline__ uint32_t hash32(uint64_t x) {
@@ -161,98 +215,114 @@ __global__ void dropout_kernel(const T* __restrict__ x, T* __restrict__ y, long 
     stf(y + i, hash32(seed * 0x9E3779B97F4A7C15ULL + static_cast<uint64_t>(i)) >= thr ? ldf(x + i) * scale : 0.f);
 }
 
+template <typename T>
+int launch_ln_bwd(int nv, int grid, size_t smem, cudaStream_t s, const T* x, const T* dy, const T* g, const float* mean,
+                  const float* rstd, T* dx, float* dgamma, float* dbeta, long long rows, int C) {
+#define LN_CASE(NVV) case NVV: layernorm_bwd_kernel<T, NVV><<<grid, 256, smem, s>>>(x, dy, g, mean, rstd, dx, dgamma, dbeta, rows, C); break;
+  switch (nv) {
+    LN_CASE(1) LN_CASE(2) LN_CASE(3) LN_CASE(4) LN_CASE(5) LN_CASE(6) LN_CASE(7) LN_CASE(8)
+    default: return DDPX_ERR_SHAPE;
+  }
+#undef LN_CASE
+  return DDPX_OK;
+}
+
 }  // namespace
 
 #define LAUNCH_OK() (cudaGetLastError() == cudaSuccess ? DDPX_OK : DDPX_ERR_LAUNCH)
 #define ST(s) static_cast<cudaStream_t>(s)
-#define EW_GRID(n) cap_blocks(((n) + 255) / 256)
+#define EW_GRID(n, V) cap_blocks(((n) / (V) + 255) / 256)
 
 extern "C" int ddpx_layernorm_fwd(const void* x, const void* gamma, const void* beta, void* y, float* mean, float* rstd,
                                   long long rows, int C, float eps, int is_bf16, void* stream) {
-  const int block = C >= 1024 ? 256 : 128;
-  const int grid = cap_blocks(rows, 148 * 8);
+  const int V = is_bf16 ? 8 : 4;
+  if (C % V) return DDPX_ERR_SHAPE;
+  const int grid = cap_blocks((rows + 7) / 8, 148 * 8);
   if (is_bf16)
-    layernorm_fwd_kernel<bf16><<<grid, block, 0, ST(stream)>>>(static_cast<const bf16*>(x), static_cast<const bf16*>(gamma),
-                                                            static_cast<const bf16*>(beta), static_cast<bf16*>(y), mean, rstd,
-                                                            rows, C, eps);
+    layernorm_fwd_kernel<bf16><<<grid, 256, 0, ST(stream)>>>(static_cast<const bf16*>(x), static_cast<const bf16*>(gamma),
+                                                          static_cast<const bf16*>(beta), static_cast<bf16*>(y), mean, rstd,
+                                                          rows, C, eps);
   else
-    layernorm_fwd_kernel<float><<<grid, block, 0, ST(stream)>>>(static_cast<const float*>(x), static_cast<const float*>(gamma),
-                                                             static_cast<const float*>(beta), static_cast<float*>(y), mean,
-                                                             rstd, rows, C, eps);
+    layernorm_fwd_kernel<float><<<grid, 256, 0, ST(stream)>>>(static_cast<const float*>(x), static_cast<const float*>(gamma),
+                                                           static_cast<const float*>(beta), static_cast<float*>(y), mean,
+                                                           rstd, rows, C, eps);
   return LAUNCH_OK();
 }
 
 // dgamma / dbeta are fp32 [C] accumulators that must be zero on entry
 extern "C" int ddpx_layernorm_bwd(const void* x, const void* dy, const void* gamma, const float* mean, const float* rstd,
                                   void* dx, float* dgamma, float* dbeta, long long rows, int C, int is_bf16, void* stream) {
-  const int block = C >= 1024 ? 256 : 128;
-  const int grid = cap_blocks(rows, 148 * 2);
+  const int V = is_bf16 ? 8 : 4;
+  if (C % V) return DDPX_ERR_SHAPE;
+  const int nv = (C / V + 31) / 32;
   const size_t smem = static_cast<size_t>(2) * C * sizeof(float);
-  if (smem > 48 * 1024) return DDPX_ERR_SHAPE;
+  if (nv > 8 || smem > 48 * 1024) return DDPX_ERR_SHAPE;
+  // every warp carries register accumulators across its rows: a few rows per warp amortise the final fold
+  const int grid = cap_blocks((rows + 31) / 32, 148 * 2);
   if (is_bf16)
-    layernorm_bwd_kernel<bf16><<<grid, block, smem, ST(stream)>>>(static_cast<const bf16*>(x), static_cast<const bf16*>(dy),
-                                                               static_cast<const bf16*>(gamma), mean, rstd,
-                                                               static_cast<bf16*>(dx), dgamma, dbeta, rows, C);
-  else
-    layernorm_bwd_kernel<float><<<grid, block, smem, ST(stream)>>>(static_cast<const float*>(x), static_cast<const float*>(dy),
-                                                                static_cast<const float*>(gamma), mean, rstd,
-                                                                static_cast<float*>(dx), dgamma, dbeta, rows, C);
-  return LAUNCH_OK();
+    return launch_ln_bwd<bf16>(nv, grid, smem, ST(stream), static_cast<const bf16*>(x), static_cast<const bf16*>(dy),
+                               static_cast<const bf16*>(gamma), mean, rstd, static_cast<bf16*>(dx), dgamma, dbeta, rows, C) ||
+           (cudaGetLastError() != cudaSuccess ? DDPX_ERR_LAUNCH : DDPX_OK);
+  return launch_ln_bwd<float>(nv, grid, smem, ST(stream), static_cast<const float*>(x), static_cast<const float*>(dy),
+                              static_cast<const float*>(gamma), mean, rstd, static_cast<float*>(dx), dgamma, dbeta, rows, C) ||
+         (cudaGetLastError() != cudaSuccess ? DDPX_ERR_LAUNCH : DDPX_OK);
 }
 
-extern "C" int ddpx_gelu_fwd(const void* x, void* y, long long n, int is_bf16, void* stream) {
-  if (is_bf16) gelu_fwd_kernel<bf16><<<EW_GRID(n), 256, 0, ST(stream)>>>(static_cast<const bf16*>(x), static_cast<bf16*>(y), n);
-  else gelu_fwd_kernel<float><<<EW_GRID(n), 256, 0, ST(stream)>>>(static_cast<const float*>(x), static_cast<float*>(y), n);
+template <int OP>
+static int launch_ew(const void* a, const void* b, void* out, long long n, int is_bf16, void* stream) {
+  if (is_bf16)
+    ew_kernel<bf16, OP><<<EW_GRID(n, 8), 256, 0, ST(stream)>>>(static_cast<const bf16*>(a), static_cast<const bf16*>(b),
+                                                            static_cast<bf16*>(out), n);
+  else
+    ew_kernel<float, OP><<<EW_GRID(n, 4), 256, 0, ST(stream)>>>(static_cast<const float*>(a), static_cast<const float*>(b),
+                                                             static_cast<float*>(out), n);
   return LAUNCH_OK();
+}
+static bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
+
+extern "C" int ddpx_gelu_fwd(const void* x, void* y, long long n, int is_bf16, void* stream) {
+  if (!aligned16(x) || !aligned16(y)) return DDPX_ERR_ALIGN;
+  return launch_ew<OP_GELU_FWD>(x, nullptr, y, n, is_bf16, stream);
 }
 extern "C" int ddpx_gelu_bwd(const void* x, const void* dy, void* dx, long long n, int is_bf16, void* stream) {
-  if (is_bf16)
-    gelu_bwd_kernel<bf16><<<EW_GRID(n), 256, 0, ST(stream)>>>(static_cast<const bf16*>(x), static_cast<const bf16*>(dy),
-                                                           static_cast<bf16*>(dx), n);
-  else
-    gelu_bwd_kernel<float><<<EW_GRID(n), 256, 0, ST(stream)>>>(static_cast<const float*>(x), static_cast<const float*>(dy),
-                                                            static_cast<float*>(dx), n);
-  return LAUNCH_OK();
+  if (!aligned16(x) || !aligned16(dy) || !aligned16(dx)) return DDPX_ERR_ALIGN;
+  return launch_ew<OP_GELU_BWD>(x, dy, dx, n, is_bf16, stream);
 }
 extern "C" int ddpx_relu_bwd_bf16(const void* y, const void* dy, void* dx, long long n, void* stream) {
-  relu_bwd_t_kernel<bf16><<<EW_GRID(n), 256, 0, ST(stream)>>>(static_cast<const bf16*>(y), static_cast<const bf16*>(dy),
-                                                           static_cast<bf16*>(dx), n);
-  return LAUNCH_OK();
+  if (!aligned16(y) || !aligned16(dy) || !aligned16(dx)) return DDPX_ERR_ALIGN;
+  return launch_ew<OP_RELU_BWD>(y, dy, dx, n, 1, stream);
 }
 extern "C" int ddpx_add(const void* a, const void* b, void* out, long long n, int is_bf16, void* stream) {
-  if (is_bf16)
-    add_kernel<bf16><<<EW_GRID(n), 256, 0, ST(stream)>>>(static_cast<const bf16*>(a), static_cast<const bf16*>(b),
-                                                      static_cast<bf16*>(out), n);
-  else
-    add_kernel<float><<<EW_GRID(n), 256, 0, ST(stream)>>>(static_cast<const float*>(a), static_cast<const float*>(b),
-                                                       static_cast<float*>(out), n);
-  return LAUNCH_OK();
+  if (!aligned16(a) || !aligned16(b) || !aligned16(out)) return DDPX_ERR_ALIGN;
+  return launch_ew<OP_ADD>(a, b, out, n, is_bf16, stream);
 }
 // dst = src * scale with a dtype change: kind 0 = f32->bf16, 1 = bf16->f32, 2 = bf16->bf16
 extern "C" int ddpx_cast_scale(const void* src, void* dst, long long n, float scale, int kind, void* stream) {
+  const int grid = cap_blocks((n + 255) / 256);
   if (kind == 0)
-    cast_scale_kernel<float, bf16><<<EW_GRID(n), 256, 0, ST(stream)>>>(static_cast<const float*>(src), static_cast<bf16*>(dst), n, scale);
+    cast_scale_kernel<float, bf16><<<grid, 256, 0, ST(stream)>>>(static_cast<const float*>(src), static_cast<bf16*>(dst), n, scale);
   else if (kind == 1)
-    cast_scale_kernel<bf16, float><<<EW_GRID(n), 256, 0, ST(stream)>>>(static_cast<const bf16*>(src), static_cast<float*>(dst), n, scale);
+    cast_scale_kernel<bf16, float><<<grid, 256, 0, ST(stream)>>>(static_cast<const bf16*>(src), static_cast<float*>(dst), n, scale);
   else
-    cast_scale_kernel<bf16, bf16><<<EW_GRID(n), 256, 0, ST(stream)>>>(static_cast<const bf16*>(src), static_cast<bf16*>(dst), n, scale);
+    cast_scale_kernel<bf16, bf16><<<grid, 256, 0, ST(stream)>>>(static_cast<const bf16*>(src), static_cast<bf16*>(dst), n, scale);
   return LAUNCH_OK();
 }
 // out[c] = sum_r x[r][c] for bf16 x (fp32 out; zeroed here)
 extern "C" int ddpx_colsum_bf16(const void* x, float* out, long long rows, int cols, void* stream) {
-  int gy = static_cast<int>(rows / 64);
+  int gy = static_cast<int>(rows / 128);
   if (gy < 1) gy = 1;
-  if (gy > 256) gy = 256;
+  if (gy > 64) gy = 64;
   cudaMemsetAsync(out, 0, sizeof(float) * cols, ST(stream));
-  dim3 grid((cols + 127) / 128, gy);
-  colsum_t_kernel<bf16><<<grid, 128, 0, ST(stream)>>>(static_cast<const bf16*>(x), out, rows, cols);
+  dim3 grid((cols + 31) / 32, gy), block(32, 8);
+  colsum_bf16_kernel<<<grid, block, 0, ST(stream)>>>(static_cast<const bf16*>(x), out, rows, cols);
   return LAUNCH_OK();
 }
 extern "C" int ddpx_dropout(const void* x, void* y, long long n, float p, unsigned long long seed, int is_bf16, void* stream) {
   const float scale = 1.f / (1.f - p);
+  const int grid = cap_blocks((n + 255) / 256);
   if (is_bf16)
-    dropout_kernel<bf16><<<EW_GRID(n), 256, 0, ST(stream)>>>(static_cast<const bf16*>(x), static_cast<bf16*>(y), n, p, scale, seed);
+    dropout_kernel<bf16><<<grid, 256, 0, ST(stream)>>>(static_cast<const bf16*>(x), static_cast<bf16*>(y), n, p, scale, seed);
   else
-    dropout_kernel<float><<<EW_GRID(n), 256, 0, ST(stream)>>>(static_cast<const float*>(x), static_cast<float*>(y), n, p, scale, seed);
+    dropout_kernel<float><<<grid, 256, 0, ST(stream)>>>(static_cast<const float*>(x), static_cast<float*>(y), n, p, scale, seed);
   return LAUNCH_OK();
 }

@@ -473,8 +473,12 @@ def linear(x, w, bias=None, act: int = 0):
 
 # ------------------------------------------------------------------------------------------------ losses
 class _CrossEntropy(Function):
+    """Mean cross-entropy over the first ``vocab`` columns of [..., C] logits (``vocab`` = C unless the vocabulary is
+    padded).  Forward: one pass over the logits (online softmax) -> loss + per-row log-sum-exp.  Backward: one more pass
+    writing dlogits = (softmax - onehot) * g / rows, with g read on the device."""
+
     @staticmethod
-    def forward(ctx, logits, targets, ignore_index):
+    def forward(ctx, logits, targets, ignore_index, vocab):
         C = logits.shape[-1]
         l2 = logits.reshape(-1, C)
         if not l2.is_contiguous():
@@ -482,28 +486,31 @@ class _CrossEntropy(Function):
         t = targets.reshape(-1)
         if t.dtype != torch.int64:
             raise TypeError("cross_entropy targets must be int64")
+        t = t.contiguous()
         rows = l2.shape[0]
+        cols = C if vocab is None else int(vocab)
         loss = torch.empty(1, device=logits.device, dtype=torch.float32)
-        dl = torch.empty_like(l2) if ctx.needs_input_grad[0] else None
-        native.softmax_ce(l2, t.contiguous(), dl, loss, rows, C, C, ignore_index)
-        ctx.save_for_backward(dl)
-        ctx.shape = logits.shape
+        lse = torch.empty(rows, device=logits.device, dtype=torch.float32)
+        native.ce_fwd(l2, t, lse, loss, rows, cols, C, ignore_index)
+        ctx.save_for_backward(l2, t, lse)
+        ctx.cfg = (logits.shape, cols, C, ignore_index)
         return loss[0]
 
     @staticmethod
     def backward(ctx, g):
-        (dl,) = ctx.saved_tensors
-        if dl is None:
-            return None, None, None
-        native.scale_by_device_scalar(dl, g.float().contiguous() if g.dtype != torch.float32 else g.contiguous())
-        return dl.view(ctx.shape), None, None
+        l2, t, lse = ctx.saved_tensors
+        shape, cols, C, ignore_index = ctx.cfg
+        gg = g if g.dtype == torch.float32 else g.float()
+        dl = torch.empty_like(l2)
+        native.ce_bwd(l2, t, lse, gg.contiguous(), dl, l2.shape[0], cols, C, ignore_index)
+        return dl.view(shape), None, None, None
 
 
 def cross_entropy(logits, targets, ignore_index: int = -100):
     """Mean softmax cross-entropy over all rows (``F.cross_entropy`` at multigpu.py:95); loss and dlogits come out of
     one fused kernel.  Note: like torch with no ignored rows; with ignored rows the mean is over *all* rows."""
     if logits.is_cuda:
-        return _CrossEntropy.apply(logits, targets, ignore_index)
+        return _CrossEntropy.apply(logits, targets, ignore_index, None)
     return F.cross_entropy(logits.reshape(-1, logits.shape[-1]), targets.reshape(-1), ignore_index=ignore_index)
 
 
@@ -577,8 +584,7 @@ def causal_attention(qkv, n_head: int):
 def cross_entropy_padded(logits, targets, vocab_size: int):
     """Cross-entropy over the first ``vocab_size`` columns of a vocabulary-padded logits tensor."""
     if logits.is_cuda:
-        from . import transformer as T
-        return T.PaddedCrossEntropyFn.apply(logits, targets, vocab_size)
+        return _CrossEntropy.apply(logits, targets, -100, vocab_size)
     V = logits.shape[-1]
     l2 = logits.reshape(-1, V)[:, :vocab_size]
     return F.cross_entropy(l2.float(), targets.reshape(-1))

@@ -63,7 +63,7 @@ def gemm(A, B, D, M, N, K, lda, ldb, ldd, a_mn=0, b_mn=0, bias=None, act=0, spli
     out_bf16 = 1 if D.dtype == torch.bfloat16 else 0
     _call("ddpx_gemm", _P(A), _P(B), _P(D), c_int(M), c_int(N), c_int(K), c_longlong(lda), c_longlong(ldb),
           c_longlong(ldd), c_int(a_mn), c_int(b_mn), c_int(bf16), c_int(out_bf16), _P(bias), c_int(act),
-          c_int(split_k), c_int(accumulate), _st())
+          c_int(split_k), c_int(accumulate), _st(), tag=f"[{M}x{N}x{K} {'NT'[a_mn]}{'NT'[b_mn]}]" if _PROFILE is not None else "")
 
 
 def conv3x3_fprop(x_nhwc, w_packed, y_nhwc, N, H, W, Cin, Cout, bias=None, act=0, stat_sum=None, stat_sq=None):
@@ -97,7 +97,8 @@ def gemm_batched(A, B, D, M, N, K, lda, ldb, ldd, a_mn, b_mn, batch1, batch2, a_
     _call("ddpx_gemm_batched", _P(A), _P(B), _P(D), c_int(M), c_int(N), c_int(K), c_longlong(lda), c_longlong(ldb),
           c_longlong(ldd), c_int(a_mn), c_int(b_mn), c_int(bf16), c_int(out_bf16), _P(bias), c_int(act), c_float(alpha),
           c_int(1), c_int(0), c_int(batch1), c_int(batch2), c_longlong(a_bs[0]), c_longlong(a_bs[1]), c_longlong(b_bs[0]),
-          c_longlong(b_bs[1]), c_longlong(d_bs[0]), c_longlong(d_bs[1]), c_int(causal), _st())
+          c_longlong(b_bs[1]), c_longlong(d_bs[0]), c_longlong(d_bs[1]), c_int(causal), _st(),
+          tag=f"[b{batch1 * batch2} {M}x{N}x{K} {'NT'[a_mn]}{'NT'[b_mn]} c{causal}]" if _PROFILE is not None else "")
 
 
 def pack_conv_weights(w, w_fprop, w_dgrad, Cout, Cin):
@@ -195,6 +196,16 @@ def softmax_ce(logits, targets, dlogits, loss_sum, rows, cols, ld, ignore_index=
     bf16 = 1 if logits.dtype == torch.bfloat16 else 0
     _call("ddpx_softmax_ce", _P(logits), _P(targets), _P(dlogits), _P(loss_sum), c_longlong(rows), c_int(cols),
           c_longlong(ld), c_int(bf16), c_longlong(ignore_index), c_float(grad_scale), _st())
+
+
+def ce_fwd(logits, targets, lse, loss_sum, rows, cols, ld, ignore_index=-100):
+    _call("ddpx_ce_fwd", _P(logits), _P(targets), _P(lse), _P(loss_sum), c_longlong(rows), c_int(cols), c_longlong(ld),
+          c_int(1 if logits.dtype == torch.bfloat16 else 0), c_longlong(ignore_index), _st())
+
+
+def ce_bwd(logits, targets, lse, g, dlogits, rows, cols, ld, ignore_index=-100):
+    _call("ddpx_ce_bwd", _P(logits), _P(targets), _P(lse), _P(g), _P(dlogits), c_longlong(rows), c_int(cols), c_longlong(ld),
+          c_int(1 if logits.dtype == torch.bfloat16 else 0), c_longlong(ignore_index), _st())
 
 
 def scale_by_device_scalar(t, g):

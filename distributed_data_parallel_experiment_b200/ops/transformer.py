@@ -146,38 +146,6 @@ class CausalAttentionFn(Function):
         return dqkv, None
 
 
-class PaddedCrossEntropyFn(Function):
-    """Mean cross-entropy over the first ``vocab`` columns of [.., V_padded] logits; the gradient of the padding columns
-    is zero.  Loss and dlogits come from one fused kernel that reads the logits once."""
-
-    @staticmethod
-    def forward(ctx, logits, targets, vocab):
-        Vp = logits.shape[-1]
-        l2 = logits.reshape(-1, Vp)
-        if not l2.is_contiguous():
-            l2 = l2.contiguous()
-        rows = l2.shape[0]
-        t = targets.reshape(-1).contiguous()
-        loss = torch.empty(1, device=logits.device, dtype=torch.float32)
-        dl = None
-        if ctx.needs_input_grad[0]:
-            dl = torch.empty_like(l2)
-            if Vp != vocab:
-                native.zero_(dl)
-        native.softmax_ce(l2, t, dl, loss, rows, vocab, Vp)
-        ctx.save_for_backward(dl)
-        ctx.shape = logits.shape
-        return loss[0]
-
-    @staticmethod
-    def backward(ctx, g):
-        (dl,) = ctx.saved_tensors
-        if dl is None:
-            return None, None, None
-        native.scale_by_device_scalar(dl, g.float().contiguous() if g.dtype != torch.float32 else g.contiguous())
-        return dl.view(ctx.shape), None, None
-
-
 class DropoutFn(Function):
     _counter = 0
 

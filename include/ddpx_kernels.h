@@ -121,6 +121,12 @@ int ddpx_bn_bwd_apply(const float* x, const float* dout, const float* mean, cons
 /* softmax cross-entropy fwd+bwd fused (M:95): loss_sum[0] = mean NLL, dlogits = (softmax - onehot) * grad_scale / rows */
 int ddpx_softmax_ce(const void* logits, const long long* targets, void* dlogits, float* loss_sum, long long rows, int cols,
                     long long ld, int bf16, long long ignore_index, float grad_scale, void* stream);
+/* two-kernel form: forward reads the logits once and keeps lse[rows]; backward writes dlogits = (softmax - onehot) * g / rows
+ * with the upstream scalar gradient g read from device memory (NULL = 1); columns [cols, ld) get zero */
+int ddpx_ce_fwd(const void* logits, const long long* targets, float* lse, float* loss_sum, long long rows, int cols,
+                long long ld, int bf16, long long ignore_index, void* stream);
+int ddpx_ce_bwd(const void* logits, const long long* targets, const float* lse, const float* g, void* dlogits, long long rows,
+                int cols, long long ld, int bf16, long long ignore_index, void* stream);
 int ddpx_scale_by_device_scalar(void* p, long long n, const float* g, int bf16, void* stream);
 int ddpx_mse(const float* pred, const float* target, float* dpred, float* loss_sum, long long n, void* stream);
 /* one launch for all tensors; torch SGD / AdamW semantics (M:97, torch/optim/sgd.py:346-380) */
