@@ -73,12 +73,19 @@ __device__ __forceinline__ float gelu_tanh(float x) {
   return 0.5f * x * (1.f + tanhf(u));
 }
 
-template <int kMode, bool kBF16>
+// kCG = 1: one CTA per tile (128 rows).  kCG = 2: a CTA pair (cluster of 2 on one TPC) per 256-row tile with
+// tcgen05 cta_group::2 - each CTA stages its own 128 rows of A and HALF of the B tile, so a k-step costs 32 KB instead
+// of 48 KB of L2->SM traffic per CTA and the same shared memory holds 6 stages instead of 4 (ncu on the 1-CTA kernel:
+// tensor pipe 58 % active, paced by operand delivery - profiles/ncu_conv_fprop.md).
+template <int kMode, bool kBF16, int kCG>
 __global__ void __launch_bounds__(kNumThreads, 1)
 tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const TcParams p) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   // carve shared memory: [stages x (A | B)] | barriers | tmem ptr
-  const uint32_t tap_b_bytes = static_cast<uint32_t>(p.block_n) * 128u;
+  const uint32_t cta_rank = (kCG == 2) ? cluster_ctarank() : 0u;
+  const bool leader = cta_rank == 0;
+  const int bn_local = p.block_n / kCG;                 // B rows staged by this CTA
+  const uint32_t tap_b_bytes = static_cast<uint32_t>(bn_local) * 128u;
   const uint32_t stage_b_bytes = tap_b_bytes * static_cast<uint32_t>(p.tpi);
   const uint32_t acc_cols = static_cast<uint32_t>(p.block_n * p.tpi);
   const uint32_t stage_bytes = kStageABytes + stage_b_bytes;
@@ -109,15 +116,15 @@ tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
     }
     for (int s = 0; s < 2; ++s) {
       mbar_init(&tfull_bar[s], 1);
-      mbar_init(&tempty_bar[s], 8);
+      mbar_init(&tempty_bar[s], 8 * kCG);       // the leader's barrier also collects the peer CTA's epilogue warps
     }
     fence_barrier_init();
   }
   if (warp == 2) {
-    tmem_alloc(tmem_slot, 512);
+    if constexpr (kCG == 2) tmem_alloc_2sm(tmem_slot, 512); else tmem_alloc(tmem_slot, 512);
   }
   tc_fence_before();
-  __syncthreads();
+  if constexpr (kCG == 2) cluster_sync_all(); else __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
@@ -134,26 +141,32 @@ tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
     tap = t % taps;
     split = t / taps;
   };
+  constexpr int kTileM = kBlockM * kCG;       // rows per work item (p.m_blocks counts tiles of this height)
   auto ksteps_of = [&](int split, int m_blk) {
     int k0 = split * p.k_steps_per_split;
     int k1 = min(k0 + p.k_steps_per_split, p.k_steps_total);
-    if (kMode == MODE_GEMM && p.causal == 2) k1 = min(k1, ((m_blk + 1) * kBlockM + kBK - 1) / kBK);
+    if (kMode == MODE_GEMM && p.causal == 2) k1 = min(k1, ((m_blk + 1) * kTileM + kBK - 1) / kBK);
     return max(k1 - k0, 0);
   };
   auto skipped = [&](int m_blk, int n_blk) {
-    return kMode == MODE_GEMM && p.causal == 1 && n_blk * p.block_n >= (m_blk + 1) * kBlockM;
+    return kMode == MODE_GEMM && p.causal == 1 && n_blk * p.block_n >= (m_blk + 1) * kTileM;
   };
+  const int first_item = blockIdx.x / kCG;    // work is dealt to clusters
+  const int item_stride = gridDim.x / kCG;
 
+  auto ld4 = [&](void* dst, const CUtensorMap* m, uint64_t* bar, int c0, int c1, int c2, int c3) {
+    if constexpr (kCG == 2) tma_load_4d_2sm(dst, m, bar, c0, c1, c2, c3); else tma_load_4d(dst, m, bar, c0, c1, c2, c3);
+  };
   if (warp == 0) {
     // ======================================= TMA producer =======================================
     if (lane == 0) {
       int stage = 0;
       uint32_t phase = 0;
-      for (int item = blockIdx.x; item < num_items; item += gridDim.x) {
+      for (int item = first_item; item < num_items; item += item_stride) {
         int m_blk, n_blk, tap, split;
         decode(item, m_blk, n_blk, tap, split);
-        const int m0 = m_blk * kBlockM;
-        const int n0 = n_blk * p.block_n;
+        const int m0 = m_blk * kTileM + static_cast<int>(cta_rank) * kBlockM;   // this CTA's 128 rows of A
+        const int n0 = n_blk * p.block_n + static_cast<int>(cta_rank) * bn_local; // this CTA's part of the B tile
         const int kbeg = split * p.k_steps_per_split;
         const int nk = ksteps_of(split, m_blk);
         if (skipped(m_blk, n_blk)) continue;
@@ -163,20 +176,20 @@ tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
           mbar_wait(&empty_bar[stage], phase ^ 1u, 0x100u + stage);
           uint8_t* sa = smem + static_cast<size_t>(stage) * stage_bytes;
           uint8_t* sb = sa + kStageABytes;
-          mbar_arrive_expect_tx(&full_bar[stage], stage_bytes);
+          if (leader) mbar_arrive_expect_tx(&full_bar[stage], stage_bytes * kCG);   // both CTAs' bytes land here
           if constexpr (kMode == MODE_GEMM) {
             const int k0 = kk * kBK;
             if (!p.a_mn) {
-              tma_load_4d(sa, &tmA, &full_bar[stage], k0, m0, b1, b2);
+              ld4(sa, &tmA, &full_bar[stage], k0, m0, b1, b2);
             } else {
               for (int j = 0; j < kBlockM / kChunk; ++j)
-                tma_load_4d(sa + j * (kBK * 128), &tmA, &full_bar[stage], m0 + j * kChunk, k0, b1, b2);
+                ld4(sa + j * (kBK * 128), &tmA, &full_bar[stage], m0 + j * kChunk, k0, b1, b2);
             }
             if (!p.b_mn) {
-              tma_load_4d(sb, &tmB, &full_bar[stage], k0, n0, b1, b2);
+              ld4(sb, &tmB, &full_bar[stage], k0, n0, b1, b2);
             } else {
-              for (int j = 0; j < p.block_n / kChunk; ++j)
-                tma_load_4d(sb + j * (kBK * 128), &tmB, &full_bar[stage], n0 + j * kChunk, k0, b1, b2);
+              for (int j = 0; j < bn_local / kChunk; ++j)
+                ld4(sb + j * (kBK * 128), &tmB, &full_bar[stage], n0 + j * kChunk, k0, b1, b2);
             }
           } else if constexpr (kMode == MODE_FPROP) {
             // K order: tap-major, then input-channel block.  A = packed weights [tap][Cout][Cin].
@@ -184,12 +197,13 @@ tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
             const int cb = kk - t9 * p.cin_blocks;
             // a single-tap problem (cin_total taps == 1: pre-gathered patches, i.e. a 1x1 conv) reads the centre
             const int r = (p.conv_taps == 1) ? 1 : t9 / 3, s = (p.conv_taps == 1) ? 1 : t9 - (t9 / 3) * 3;
-            tma_load_3d(sa, &tmA, &full_bar[stage], cb * kBK, m0, t9);
+            if constexpr (kCG == 2) tma_load_3d_2sm(sa, &tmA, &full_bar[stage], cb * kBK, m0, t9);
+            else tma_load_3d(sa, &tmA, &full_bar[stage], cb * kBK, m0, t9);
             // B = NHWC activations; tile of block_n consecutive pixels = box (box_w, box_h, box_n)
             const int hw = p.H * p.W;
             const int img = n0 / hw;
             const int h0 = (n0 - img * hw) / p.W;
-            tma_load_4d(sb, &tmB, &full_bar[stage], cb * kBK, s - 1, h0 + r - 1, img);
+            ld4(sb, &tmB, &full_bar[stage], cb * kBK, s - 1, h0 + r - 1, img);
           } else {
             // WGRAD: K step = 32 consecutive pixels.  A = dY [pixels][Cout] (MN-major), B = shifted X.
             // item "tap" = first tap of the group (tpi = 3: one filter row r, s = 0..2; tpi = 1: a single tap)
@@ -199,12 +213,12 @@ tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
             const int img = p0 / hw;
             const int h0 = (p0 - img * hw) / p.W;
             for (int j = 0; j < kBlockM / kChunk; ++j)
-              tma_load_2d(sa + j * (kBK * 128), &tmA, &full_bar[stage], m0 + j * kChunk, p0);
+              if constexpr (kCG == 2) tma_load_2d_2sm(sa + j * (kBK * 128), &tmA, &full_bar[stage], m0 + j * kChunk, p0);
+              else tma_load_2d(sa + j * (kBK * 128), &tmA, &full_bar[stage], m0 + j * kChunk, p0);
             for (int t = 0; t < p.tpi; ++t) {
               const int r = (tap0 + t) / 3, s = (tap0 + t) - r * 3;
-              for (int j = 0; j < p.block_n / kChunk; ++j)
-                tma_load_4d(sb + t * tap_b_bytes + j * (kBK * 128), &tmB, &full_bar[stage], n0 + j * kChunk, s - 1,
-                            h0 + r - 1, img);
+              for (int j = 0; j < bn_local / kChunk; ++j)
+                ld4(sb + t * tap_b_bytes + j * (kBK * 128), &tmB, &full_bar[stage], n0 + j * kChunk, s - 1, h0 + r - 1, img);
             }
           }
           if (++stage == p.num_stages) { stage = 0; phase ^= 1u; }
@@ -213,10 +227,10 @@ tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
     }
   } else if (warp == 1) {
     // ======================================= MMA issuer =========================================
-    if (lane == 0) {
+    if (lane == 0 && leader) {
       const bool a_mn = (kMode == MODE_WGRAD) ? true : (kMode == MODE_FPROP ? false : (p.a_mn != 0));
       const bool b_mn = (kMode == MODE_WGRAD) ? true : (kMode == MODE_FPROP ? false : (p.b_mn != 0));
-      const uint32_t idesc = make_idesc(kBF16, a_mn, b_mn, kBlockM, static_cast<uint32_t>(p.block_n));
+      const uint32_t idesc = make_idesc(kBF16, a_mn, b_mn, kTileM, static_cast<uint32_t>(p.block_n));
       // descriptor strides: K-major -> 8-row groups 1024 B apart; MN-major -> 128-B-wide chunks kBK*128 apart
       const uint32_t a_lbo = a_mn ? kBK * 128u : 16u, b_lbo = b_mn ? kBK * 128u : 16u;
       const uint32_t a_kadv = a_mn ? kUmmaK * 128u : 32u, b_kadv = b_mn ? kUmmaK * 128u : 32u;
@@ -227,7 +241,7 @@ tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
       uint32_t phase = 0;
       int acc = 0;
       uint32_t acc_phase = 0;
-      for (int item = blockIdx.x; item < num_items; item += gridDim.x) {
+      for (int item = first_item; item < num_items; item += item_stride) {
         int m_blk, n_blk, tap, split;
         decode(item, m_blk, n_blk, tap, split);
         const int nk = ksteps_of(split, m_blk);
@@ -245,13 +259,14 @@ tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
             for (int k = 0; k < kBK / kUmmaK; ++k) {
               const uint64_t adesc = make_smem_desc_sw128(sa + k * a_kadv, a_lbo, a_sbo, a_lay);
               const uint64_t bdesc = make_smem_desc_sw128(sb + t * tap_b_bytes + k * b_kadv, b_lbo, b_sbo, b_lay);
-              tc_mma<kBF16>(tmem_d + t * p.block_n, adesc, bdesc, idesc, (i > 0 || k > 0) ? 1u : 0u);
+              if constexpr (kCG == 2) tc_mma_2sm<kBF16>(tmem_d + t * p.block_n, adesc, bdesc, idesc, (i > 0 || k > 0) ? 1u : 0u);
+              else tc_mma<kBF16>(tmem_d + t * p.block_n, adesc, bdesc, idesc, (i > 0 || k > 0) ? 1u : 0u);
             }
           }
-          tc_commit(&empty_bar[stage]);   // smem slot is free once these MMAs retire
+          if constexpr (kCG == 2) tc_commit_2sm(&empty_bar[stage]); else tc_commit(&empty_bar[stage]);   // slot free (both CTAs)
           if (++stage == p.num_stages) { stage = 0; phase ^= 1u; }
         }
-        tc_commit(&tfull_bar[acc]);       // accumulator complete -> epilogue
+        if constexpr (kCG == 2) tc_commit_2sm(&tfull_bar[acc]); else tc_commit(&tfull_bar[acc]);   // accumulator complete
         if (++acc == p.acc_stages) { acc = 0; acc_phase ^= 1u; }
       }
     }
@@ -266,7 +281,7 @@ tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
     const int cc_end = min(cc_begin + cols_half, static_cast<int>(acc_cols));
     int acc = 0;
     uint32_t acc_phase = 0;
-    for (int item = blockIdx.x; item < num_items; item += gridDim.x) {
+    for (int item = first_item; item < num_items; item += item_stride) {
       int m_blk, n_blk, tap, split;
       decode(item, m_blk, n_blk, tap, split);
       const int nk = ksteps_of(split, m_blk);
@@ -274,8 +289,8 @@ tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
       const long long boff = (kMode == MODE_GEMM)
                                  ? static_cast<long long>(tap % p.batch1) * p.out_bs1 + static_cast<long long>(tap / p.batch1) * p.out_bs2
                                  : 0;
-      const int row = m_blk * kBlockM + ew * 32 + lane;     // output row owned by this thread
-      const int n0 = n_blk * p.block_n;
+      const int row = m_blk * kTileM + static_cast<int>(cta_rank) * kBlockM + ew * 32 + lane;   // this thread's output row
+      const int n0 = n_blk * p.block_n;     // the epilogue sees all block_n columns of this CTA's 128 rows
       mbar_wait(&tfull_bar[acc], acc_phase, 0x400u + acc);
       tc_fence_after();
       const uint32_t taddr = tmem_base + (static_cast<uint32_t>(ew * 32) << 16) + static_cast<uint32_t>(acc) * acc_cols;
@@ -301,22 +316,26 @@ tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
             }
           }
           if (!p.atomic) {
+            // one bias load per lane per 32-column chunk, handed round with shuffles: a per-element __ldg put a
+            // load-latency stall (and a branch) on every output element and paced the whole kernel (ncu: 25% long_sb)
+            float bl = 0.f;
+            if (p.bias != nullptr && n0 + c0 + lane < p.N) bl = __ldg(p.bias + n0 + c0 + lane);
             float f[32];
 #pragma unroll
-            for (int j = 0; j < 32; ++j) {
-              float x = __uint_as_float(v[j]) * p.alpha;
-              const int col = n0 + c0 + j;
-              if (p.bias != nullptr && col < p.N) x += __ldg(p.bias + col);
-              if (p.act == 1) x = fmaxf(x, 0.f);
-              else if (p.act == 2) x = gelu_tanh(x);
-              f[j] = x;
+            for (int j = 0; j < 32; ++j) f[j] = fmaf(__uint_as_float(v[j]), p.alpha, __shfl_sync(0xffffffffu, bl, j));
+            if (p.act == 1) {
+#pragma unroll
+              for (int j = 0; j < 32; ++j) f[j] = fmaxf(f[j], 0.f);
+            } else if (p.act == 2) {
+#pragma unroll
+              for (int j = 0; j < 32; ++j) f[j] = gelu_tanh(f[j]);
             }
             const bool full = (n0 + c0 + 32 <= p.N);
             if (p.st_vec && full) {
               // warp-uniform path: transpose the warp's 32x32 chunk through shared memory (XOR-swizzled 16-byte pieces,
               // conflict-free both ways) so that every global store instruction writes whole row segments
               uint8_t* stg = epi_stage + (warp - 4) * 4096;
-              const int row0 = m_blk * kBlockM + ew * 32;
+              const int row0 = m_blk * kTileM + static_cast<int>(cta_rank) * kBlockM + ew * 32;
               if (p.out_bf16) {
 #pragma unroll
                 for (int j = 0; j < 4; ++j) {
@@ -372,13 +391,21 @@ tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
           if (row < p.M) {
             float* o = reinterpret_cast<float*>(p.out) + static_cast<long long>(n0 + c0) * p.ldo + row;
             const float b = (p.bias != nullptr) ? __ldg(p.bias + row) : 0.f;
+            // the host guarantees that pixel tiles are whole (P % block_n == 0): no per-element bound check
+            if (p.act == 1) {
 #pragma unroll
-            for (int j = 0; j < 32; ++j) {
-              if (n0 + c0 + j < p.N) {
-                float x = __uint_as_float(v[j]) + b;
+              for (int j = 0; j < 32; ++j) {
+                const float x = __uint_as_float(v[j]) + b;
                 ssum += x;
                 ssq += x * x;
-                if (p.act == 1) x = fmaxf(x, 0.f);
+                o[static_cast<long long>(j) * p.ldo] = fmaxf(x, 0.f);
+              }
+            } else {
+#pragma unroll
+              for (int j = 0; j < 32; ++j) {
+                const float x = __uint_as_float(v[j]) + b;
+                ssum += x;
+                ssq += x * x;
                 o[static_cast<long long>(j) * p.ldo] = x;
               }
             }
@@ -388,9 +415,10 @@ tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
           if (row < p.M) {
             float* o = reinterpret_cast<float*>(p.out) + (static_cast<long long>(row) * p.cin_total + n0 + c0) * 9 +
                        tap * p.tpi + tsub;
+            if (n0 + c0 + 32 <= p.N) {        // Cin is a multiple of 32: whole chunks only
 #pragma unroll
-            for (int j = 0; j < 32; ++j)
-              if (n0 + c0 + j < p.N) atomicAdd(o + j * 9, __uint_as_float(v[j]));
+              for (int j = 0; j < 32; ++j) atomicAdd(o + j * 9, __uint_as_float(v[j]));
+            }
           }
         }
       }
@@ -402,15 +430,19 @@ tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
       }
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(&tempty_bar[acc]);
+      if (lane == 0) {
+        if (kCG == 2 && !leader) mbar_arrive_cluster(&tempty_bar[acc], 0); else mbar_arrive(&tempty_bar[acc]);
+      }
       if (++acc == p.acc_stages) { acc = 0; acc_phase ^= 1u; }
     }
   }
 
   tc_fence_before();
-  __syncthreads();
+  if constexpr (kCG == 2) cluster_sync_all(); else __syncthreads();   // the peer may still read this CTA's smem / barriers
   tc_fence_after();
-  if (warp == 2) tmem_dealloc(tmem_base, 512);
+  if (warp == 2) {
+    if constexpr (kCG == 2) tmem_dealloc_2sm(tmem_base, 512); else tmem_dealloc(tmem_base, 512);
+  }
 }
 
 // =================================================================================================
@@ -470,25 +502,55 @@ static int pick_stages(int block_n, int tpi, int reserve) {
   return s;
 }
 
-template <int kMode, bool kBF16>
-static int launch_tc(const CUtensorMap& a, const CUtensorMap& b, TcParams& p, cudaStream_t stream) {
+template <int kMode, bool kBF16, int kCG>
+static int launch_tc_cg(const CUtensorMap& a, const CUtensorMap& b, TcParams& p, cudaStream_t stream) {
   if (p.tpi < 1) p.tpi = 1;
   p.acc_stages = (2 * p.tpi * p.block_n <= 512) ? 2 : 1;
   const int reserve = (kMode == MODE_GEMM) ? kEpiStageBytes : 0;
-  p.num_stages = pick_stages(p.block_n, p.tpi, reserve);
-  const size_t smem = static_cast<size_t>(p.num_stages) * (kStageABytes + p.block_n * 128 * p.tpi) + 1024 /*align*/ + 256 + reserve;
+  const int bn_local = p.block_n / kCG;
+  p.num_stages = pick_stages(bn_local, p.tpi, reserve);
+  const size_t smem = static_cast<size_t>(p.num_stages) * (kStageABytes + bn_local * 128 * p.tpi) + 1024 /*align*/ + 256 + reserve;
   static bool attr_set = false;
   if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(tc_kernel<kMode, kBF16>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    cudaError_t e = cudaFuncSetAttribute(tc_kernel<kMode, kBF16, kCG>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
     if (e != cudaSuccess) return DDPX_ERR_LAUNCH;
     attr_set = true;
   }
   const int taps = (kMode == MODE_WGRAD) ? 9 / p.tpi : (kMode == MODE_GEMM ? p.batch1 * p.batch2 : 1);
   const int items = p.m_blocks * p.n_blocks * taps * p.num_splits;
-  int grid = items < num_sms() ? items : num_sms();
-  if (grid < 1) grid = 1;
-  tc_kernel<kMode, kBF16><<<grid, kNumThreads, smem, stream>>>(a, b, p);
+  const int max_clusters = num_sms() / kCG;
+  int clusters = items < max_clusters ? items : max_clusters;
+  if (clusters < 1) clusters = 1;
+  if (kCG == 1) {
+    tc_kernel<kMode, kBF16, kCG><<<clusters, kNumThreads, smem, stream>>>(a, b, p);
+  } else {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(clusters * kCG);
+    cfg.blockDim = dim3(kNumThreads);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = kCG; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr; cfg.numAttrs = 1;
+    if (cudaLaunchKernelEx(&cfg, tc_kernel<kMode, kBF16, kCG>, a, b, p) != cudaSuccess) return DDPX_ERR_LAUNCH;
+  }
   return cudaGetLastError() == cudaSuccess ? DDPX_OK : DDPX_ERR_LAUNCH;
+}
+
+// DDPX_CTA_PAIRS=0 forces single-CTA tiles everywhere (A/B comparisons, fallback)
+static bool pairs_enabled() {
+  static int v = -1;
+  if (v < 0) { const char* e = getenv("DDPX_CTA_PAIRS"); v = (e && e[0] == '0') ? 0 : 1; }
+  return v == 1;
+}
+
+// cg = 2 asks for CTA pairs: the caller has laid the problem out in 256-row tiles (p.m_blocks) and built the B tensor
+// map with a box of block_n / 2 rows.
+template <int kMode, bool kBF16>
+static int launch_tc(const CUtensorMap& a, const CUtensorMap& b, TcParams& p, cudaStream_t stream, int cg = 1) {
+  if (cg == 2) return launch_tc_cg<kMode, kBF16, 2>(a, b, p, stream);
+  return launch_tc_cg<kMode, kBF16, 1>(a, b, p, stream);
 }
 
 }  // namespace ddpx
@@ -520,8 +582,11 @@ extern "C" int ddpx_gemm_batched(const void* A, const void* B, void* D, int M, i
   while (bn > min_bn && bn / 2 >= N) bn /= 2;
   if (causal == 1 && bn > kBlockM) bn = kBlockM;      // square tiles so whole tiles fall above the diagonal
   if (bn < min_bn) bn = min_bn;
+  // CTA pairs (256-row tiles) whenever the problem is tall and wide enough for 256x256 tiles to fill the machine
+  const int cg = (pairs_enabled() && bn == 256 && M >= 256 && causal == 0 &&
+                  static_cast<long long>((M + 255) / 256) * ((N + 255) / 256) * nb_total >= num_sms() / 2) ? 2 : 1;
   p.block_n = bn;
-  p.m_blocks = mb;
+  p.m_blocks = cg == 2 ? (M + 255) / 256 : mb;
   p.n_blocks = (N + bn - 1) / bn;
   p.k_steps_total = (K + bk - 1) / bk;
   int splits = split_k > 0 ? split_k : 1;
@@ -549,14 +614,14 @@ extern "C" int ddpx_gemm_batched(const void* A, const void* B, void* D, int M, i
     str[1] = batch1 > 1 ? static_cast<uint64_t>(a_bs1) * elt : str[0] * dims[1];
     str[2] = batch2 > 1 ? static_cast<uint64_t>(a_bs2) * elt : str[1] * dims[2];
     if ((rc = make_tmap(&ta, A, bf16, 4, dims, str, box, a_mn && !bf16)) != DDPX_OK) return rc;
-    if (!b_mn) { dims[0] = K; dims[1] = N; box[0] = bk; box[1] = bn; }
+    if (!b_mn) { dims[0] = K; dims[1] = N; box[0] = bk; box[1] = bn / cg; }
     else       { dims[0] = N; dims[1] = K; box[0] = chunk; box[1] = bk; }
     str[0] = static_cast<uint64_t>(ldb) * elt;
     str[1] = batch1 > 1 ? static_cast<uint64_t>(b_bs1) * elt : str[0] * dims[1];
     str[2] = batch2 > 1 ? static_cast<uint64_t>(b_bs2) * elt : str[1] * dims[2];
     if ((rc = make_tmap(&tb, B, bf16, 4, dims, str, box, b_mn && !bf16)) != DDPX_OK) return rc;
   }
-  return bf16 ? launch_tc<MODE_GEMM, true>(ta, tb, p, stream) : launch_tc<MODE_GEMM, false>(ta, tb, p, stream);
+  return bf16 ? launch_tc<MODE_GEMM, true>(ta, tb, p, stream, cg) : launch_tc<MODE_GEMM, false>(ta, tb, p, stream, cg);
 }
 
 extern "C" int ddpx_gemm(const void* A, const void* B, void* D, int M, int N, int K, long long lda, long long ldb,
@@ -592,10 +657,15 @@ static int conv_fprop_impl(const float* x, const float* wpacked, float* y, int N
   int bw, bh, bnn;
   while (bn >= 32 && conv_box(bn, H, W, Nimg, &bw, &bh, &bnn) != DDPX_OK) bn /= 2;
   if (bn < 32 || P % bn) return DDPX_ERR_SHAPE;
+  int cg = 1;
+  if (pairs_enabled() && bn == 256 && Cout % 256 == 0) {
+    int bw2, bh2, bn2;       // each CTA of a pair stages 128 of the tile's 256 pixels
+    if (conv_box(128, H, W, Nimg, &bw2, &bh2, &bn2) == DDPX_OK) { cg = 2; bw = bw2; bh = bh2; bnn = bn2; }
+  }
   TcParams p{};
   p.M = Cout; p.N = static_cast<int>(P);
   p.block_n = bn;
-  p.m_blocks = (Cout + kBlockM - 1) / kBlockM;
+  p.m_blocks = (Cout + kBlockM * cg - 1) / (kBlockM * cg);
   p.n_blocks = static_cast<int>(P / bn);
   p.cin_blocks = Cin / 32;
   p.k_steps_total = taps * p.cin_blocks;
@@ -620,7 +690,7 @@ static int conv_fprop_impl(const float* x, const float* wpacked, float* y, int N
     uint32_t box[4] = {32, static_cast<uint32_t>(bw), static_cast<uint32_t>(bh), static_cast<uint32_t>(bnn)};
     if ((rc = make_tmap(&tb, x, false, 4, dims, str, box)) != DDPX_OK) return rc;
   }
-  return launch_tc<MODE_FPROP, false>(ta, tb, p, stream);
+  return launch_tc<MODE_FPROP, false>(ta, tb, p, stream, cg);
 }
 
 extern "C" int ddpx_conv3x3_fprop(const float* x, const float* wpacked, float* y, int Nimg, int H, int W, int Cin,
@@ -661,8 +731,9 @@ extern "C" int ddpx_conv3x3_wgrad(const float* dy, const float* x, float* dw, in
   int bn = Cin >= max_bn ? max_bn : Cin;       // Cin is a multiple of 32
   while (Cin % bn) bn -= 32;
   if (bn < 32 || bn % 32) return DDPX_ERR_SHAPE;
+  const int cg = (pairs_enabled() && p.tpi == 1 && bn == 256 && Cout % 256 == 0) ? 2 : 1;
   p.block_n = bn;
-  p.m_blocks = (Cout + kBlockM - 1) / kBlockM;
+  p.m_blocks = (Cout + kBlockM * cg - 1) / (kBlockM * cg);
   p.n_blocks = (Cin + bn - 1) / bn;
   p.k_steps_total = static_cast<int>(P / 32);
   const int tiles = p.m_blocks * p.n_blocks * (9 / p.tpi);
@@ -691,7 +762,7 @@ extern "C" int ddpx_conv3x3_wgrad(const float* dy, const float* x, float* dw, in
     uint32_t box[4] = {32, static_cast<uint32_t>(bw), static_cast<uint32_t>(bh), static_cast<uint32_t>(bnn)};
     if ((rc = make_tmap(&tb, x, false, 4, dims, str, box, true)) != DDPX_OK) return rc;
   }
-  return launch_tc<MODE_WGRAD, false>(ta, tb, p, stream);
+  return launch_tc<MODE_WGRAD, false>(ta, tb, p, stream, cg);
 }
 
 extern "C" unsigned int ddpx_read_error_word(void) {

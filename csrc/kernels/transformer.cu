@@ -221,6 +221,7 @@ int launch_ln_bwd(int nv, int grid, size_t smem, cudaStream_t s, const T* x, con
 #define LN_CASE(NVV) case NVV: layernorm_bwd_kernel<T, NVV><<<grid, 256, smem, s>>>(x, dy, g, mean, rstd, dx, dgamma, dbeta, rows, C); break;
   switch (nv) {
     LN_CASE(1) LN_CASE(2) LN_CASE(3) LN_CASE(4) LN_CASE(5) LN_CASE(6) LN_CASE(7) LN_CASE(8)
+    LN_CASE(9) LN_CASE(10) LN_CASE(11) LN_CASE(12) LN_CASE(13) LN_CASE(14) LN_CASE(15) LN_CASE(16)
     default: return DDPX_ERR_SHAPE;
   }
 #undef LN_CASE
@@ -256,7 +257,7 @@ extern "C" int ddpx_layernorm_bwd(const void* x, const void* dy, const void* gam
   if (C % V) return DDPX_ERR_SHAPE;
   const int nv = (C / V + 31) / 32;
   const size_t smem = static_cast<size_t>(2) * C * sizeof(float);
-  if (nv > 8 || smem > 48 * 1024) return DDPX_ERR_SHAPE;
+  if (nv > 16 || smem > 48 * 1024) return DDPX_ERR_SHAPE;
   // every warp carries register accumulators across its rows: a few rows per warp amortise the final fold
   const int grid = cap_blocks((rows + 31) / 32, 148 * 2);
   if (is_bf16)
