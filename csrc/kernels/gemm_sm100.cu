@@ -578,13 +578,14 @@ extern "C" int ddpx_gemm_batched(const void* A, const void* B, void* D, int M, i
   const int nb_total = batch1 * batch2;
   const int min_bn = (b_mn && chunk > 32) ? chunk : 32;
   int bn = 256;
-  while (bn > 64 && static_cast<long long>(mb) * ((N + bn - 1) / bn) * nb_total < num_sms()) bn /= 2;
+  const int want_splits = split_k > 1 ? split_k : 1;      // split-K multiplies the number of work items
+  while (bn > 64 && static_cast<long long>(mb) * ((N + bn - 1) / bn) * nb_total * want_splits < num_sms()) bn /= 2;
   while (bn > min_bn && bn / 2 >= N) bn /= 2;
   if (causal == 1 && bn > kBlockM) bn = kBlockM;      // square tiles so whole tiles fall above the diagonal
   if (bn < min_bn) bn = min_bn;
   // CTA pairs (256-row tiles) whenever the problem is tall and wide enough for 256x256 tiles to fill the machine
   const int cg = (pairs_enabled() && bn == 256 && M >= 256 && causal == 0 &&
-                  static_cast<long long>((M + 255) / 256) * ((N + 255) / 256) * nb_total >= num_sms() / 2) ? 2 : 1;
+                  static_cast<long long>((M + 255) / 256) * ((N + 255) / 256) * nb_total * want_splits >= num_sms() / 4) ? 2 : 1;
   p.block_n = bn;
   p.m_blocks = cg == 2 ? (M + 255) / 256 : mb;
   p.n_blocks = (N + bn - 1) / bn;

@@ -438,13 +438,25 @@ class _Linear(Function):
             dx = dx.view(*xs)
         if ctx.needs_input_grad[1]:
             if big:
+                # dw = d^T[N,M] @ x[M,K] (both operands MN-major).  A weight gradient has few output tiles and a long
+                # reduction (the tokens): when 256x256 tiles cannot fill the 74 CTA pairs, split the reduction and
+                # accumulate in fp32 (then cast) instead of shrinking the tiles.
+                tiles = ((N + 255) // 256) * ((K + 255) // 256)
+                split = 1 if tiles >= 60 or M < 2048 else max(1, min(74 // tiles, M // 1024))
                 if d.dtype == torch.float32:
-                    dw = torch.empty((N, K), device=d.device, dtype=torch.float32)
-                    native.gemm(d, x2, dw, N, K, M, N, K, K, 1, 1)        # dw = d^T[N,M] @ x[M,K]
+                    if split > 1:
+                        dw = _zeros((N, K), d.device)
+                        native.gemm(d, x2, dw, N, K, M, N, K, K, 1, 1, None, 0, split, 1)
+                    else:
+                        dw = torch.empty((N, K), device=d.device, dtype=torch.float32)
+                        native.gemm(d, x2, dw, N, K, M, N, K, K, 1, 1)
+                elif split > 1:
+                    dw32 = _zeros((N, K), d.device)
+                    native.gemm(d, x2, dw32, N, K, M, N, K, K, 1, 1, None, 0, split, 1)
+                    dw = native.cast(dw32, w.dtype)
                 else:
-                    dwf = torch.empty((N, K), device=d.device, dtype=w.dtype)
-                    native.gemm(d, x2, dwf, N, K, M, N, K, K, 1, 1)
-                    dw = dwf
+                    dw = torch.empty((N, K), device=d.device, dtype=w.dtype)
+                    native.gemm(d, x2, dw, N, K, M, N, K, K, 1, 1)
             else:
                 dw = torch.empty((N, K), device=d.device, dtype=torch.float32)
                 native.gemm_small(d, x2, dw, N, K, M, 1, N, 1, K, K)
