@@ -63,6 +63,23 @@ def test_gemm_layouts(a_mn, b_mn, dtype, M, N, K):
     assert rel_err(D, ref) < (TF32_RTOL if dtype == torch.float32 else 1e-4)
 
 
+@pytest.mark.parametrize("a_mn,b_mn", [(0, 0), (0, 1), (1, 1)])
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_gemm_cta_pairs_large(a_mn, b_mn, dtype):
+    """Shapes big enough for the 256x256 CTA-pair (cta_group::2) tiles, including a ragged M and bf16 output + bias."""
+    torch.manual_seed(0)
+    M, N, K = 2304 + 40, 2048, 768
+    A = torch.randn(M, K, device="cuda").to(dtype)
+    B = torch.randn(N, K, device="cuda").to(dtype)
+    bias = torch.randn(N, device="cuda")
+    ref = A.double() @ B.double().t() + bias.double()
+    As = A.t().contiguous() if a_mn else A
+    Bs = B.t().contiguous() if b_mn else B
+    D = torch.empty(M, N, device="cuda", dtype=dtype)
+    native.gemm(As, Bs, D, M, N, K, As.stride(0), Bs.stride(0), N, a_mn, b_mn, bias, 0)
+    assert rel_err(D, ref) < (TF32_RTOL if dtype == torch.float32 else 1e-2)
+
+
 def test_gemm_epilogue_bias_gelu_bf16_out():
     M, N, K = 384, 1024, 512
     A = torch.randn(M, K, device="cuda").bfloat16(); B = torch.randn(N, K, device="cuda").bfloat16()
