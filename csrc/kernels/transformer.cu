@@ -203,6 +203,35 @@ __global__ void colsum_bf16_kernel(const bf16* __restrict__ x, float* __restrict
     atomicAdd(out + c, t);
   }
 }
+// vector flavour (cols % 8 == 0, 16-byte aligned rows): a thread owns 8 adjacent columns (one 16-byte load per row),
+// block = 32 column-groups x 8 row lanes = 256 columns wide
+__global__ void colsum_bf16_vec_kernel(const bf16* __restrict__ x, float* __restrict__ out, long long rows, int cols) {
+  __shared__ float sh[8][32][9];
+  const int cg = blockIdx.x * 32 + threadIdx.x;      // column group (8 columns)
+  float s[8];
+#pragma unroll
+  for (int k = 0; k < 8; ++k) s[k] = 0.f;
+  if (cg * 8 < cols)
+    for (long long r = static_cast<long long>(blockIdx.y) * 8 + threadIdx.y; r < rows; r += static_cast<long long>(gridDim.y) * 8) {
+      float f[8];
+      vload(x + r * cols + cg * 8, f);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) s[k] += f[k];
+    }
+#pragma unroll
+  for (int k = 0; k < 8; ++k) sh[threadIdx.y][threadIdx.x][k] = s[k];
+  __syncthreads();
+  // 256 threads fold the 8 row lanes of the block's 256 columns: one atomic per column
+  const int t = threadIdx.y * 32 + threadIdx.x;
+  const int g = t >> 3, k = t & 7;
+  const int c = (blockIdx.x * 32 + g) * 8 + k;
+  if (c < cols) {
+    float a = 0.f;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) a += sh[j][g][k];
+    atomicAdd(out + c, a);
+  }
+}
 // inverted dropout with a counter-based hash RNG: keep iff hash(seed, i) >= p * 2^32
 __device__ __forceinline__ uint32_t hash32(uint64_t x) {
   x ^= x >> 33; x *= 0xff51afd7ed558ccdULL; x ^= x >> 33; x *= 0xc4ceb9fe1a85ec53ULL; x ^= x >> 33;
@@ -314,7 +343,13 @@ extern "C" int ddpx_colsum_bf16(const void* x, float* out, long long rows, int c
   if (gy < 1) gy = 1;
   if (gy > 64) gy = 64;
   cudaMemsetAsync(out, 0, sizeof(float) * cols, ST(stream));
-  dim3 grid((cols + 31) / 32, gy), block(32, 8);
+  dim3 block(32, 8);
+  if (cols % 8 == 0 && (reinterpret_cast<uintptr_t>(x) & 15) == 0) {
+    dim3 grid((cols / 8 + 31) / 32, gy);
+    colsum_bf16_vec_kernel<<<grid, block, 0, ST(stream)>>>(static_cast<const bf16*>(x), out, rows, cols);
+    return LAUNCH_OK();
+  }
+  dim3 grid((cols + 31) / 32, gy);
   colsum_bf16_kernel<<<grid, block, 0, ST(stream)>>>(static_cast<const bf16*>(x), out, rows, cols);
   return LAUNCH_OK();
 }
