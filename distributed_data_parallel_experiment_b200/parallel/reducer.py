@@ -189,13 +189,13 @@ class Reducer:
             if b.handle is not None:
                 b.handle.wait()
                 b.handle = None
+            if self.fused is None:
+                for pid, v in zip(b.param_ids, b.views[parity]):
+                    self.params[pid].grad = v          # averaged gradient lives in the bucket (no copy back)
         if timing:
             t1 = torch.cuda.Event(enable_timing=True)
             t1.record()
             self.stats.setdefault("exposed_events", []).append((t0, t1))
-            if self.fused is None:
-                for pid, v in zip(b.param_ids, b.views[parity]):
-                    self.params[pid].grad = v          # averaged gradient lives in the bucket (no copy back)
         if self.fused is not None:
             self.fused.after_backward(self)
         self.armed = False
