@@ -285,6 +285,15 @@ def run_ours(args):
     e2e_ms = timed_loop(e2e_step, args.steps, world)
     extra = {"stack": "hand-written sm_100a kernels (tcgen05/TMEM/TMA conv+GEMM, fused BN/ReLU/pool/CE/SGD)"
                       + (", P2P fused all-reduce+SGD over NVLink" if world > 1 else "")}
+    # outside the timed regions: host time to enqueue one step (no synchronisation inside) - tells launch-bound from
+    # GPU-bound when the two arms or two GPU counts differ
+    import time as _time
+    torch.cuda.synchronize()
+    h0 = _time.perf_counter()
+    for i in range(10):
+        dev_step(i)
+    extra["host_enqueue_ms_per_step"] = round((_time.perf_counter() - h0) * 100.0, 3)
+    torch.cuda.synchronize()
     if world > 1 and hasattr(trainer.model, "measure_exposed_comm"):
         # outside the timed regions: how long the compute stream stalls for the last gradient buckets, per step
         trainer.model.measure_exposed_comm(True)

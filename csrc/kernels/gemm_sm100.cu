@@ -59,6 +59,7 @@ struct TcParams {
   int out_bf16;
   int atomic;               // 1 = accumulate with red.global.add.f32 (split-K / wgrad)
   float alpha;              // GEMM: D = act(alpha * A*B + bias)
+  int big_box;              // WGRAD: operand maps have the 32-channel chunk as outermost dim (one TMA per tile)
   int st_vec;               // GEMM: output rows are 16-byte aligned -> epilogue stages 32x32 chunks through shared
                             // memory and stores whole 64/128-byte row segments (coalesced) instead of 16 B per lane
   int act;                  // 0 none, 1 relu, 2 gelu(tanh)
@@ -212,13 +213,25 @@ tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
             const int hw = p.H * p.W;
             const int img = p0 / hw;
             const int h0 = (p0 - img * hw) / p.W;
-            for (int j = 0; j < kBlockM / kChunk; ++j)
-              if constexpr (kCG == 2) tma_load_2d_2sm(sa + j * (kBK * 128), &tmA, &full_bar[stage], m0 + j * kChunk, p0);
-              else tma_load_2d(sa + j * (kBK * 128), &tmA, &full_bar[stage], m0 + j * kChunk, p0);
-            for (int t = 0; t < p.tpi; ++t) {
-              const int r = (tap0 + t) / 3, s = (tap0 + t) - r * 3;
-              for (int j = 0; j < bn_local / kChunk; ++j)
-                ld4(sb + t * tap_b_bytes + j * (kBK * 128), &tmB, &full_bar[stage], n0 + j * kChunk, s - 1, h0 + r - 1, img);
+            if (p.big_box) {
+              // one TMA per operand tile: the maps carry the 32-channel chunk index as their outermost dimension, so a
+              // box of (32 ch, 32 pixels, n chunks) lands as n consecutive [32 pixels][128 B] swizzle tiles
+              if constexpr (kCG == 2) tma_load_3d_2sm(sa, &tmA, &full_bar[stage], 0, p0, m0 / kChunk);
+              else tma_load_3d(sa, &tmA, &full_bar[stage], 0, p0, m0 / kChunk);
+              for (int t = 0; t < p.tpi; ++t) {
+                const int r = (tap0 + t) / 3, s = (tap0 + t) - r * 3;
+                if constexpr (kCG == 2) tma_load_5d_2sm(sb + t * tap_b_bytes, &tmB, &full_bar[stage], 0, s - 1, h0 + r - 1, img, n0 / kChunk);
+                else tma_load_5d(sb + t * tap_b_bytes, &tmB, &full_bar[stage], 0, s - 1, h0 + r - 1, img, n0 / kChunk);
+              }
+            } else {
+              for (int j = 0; j < kBlockM / kChunk; ++j)
+                if constexpr (kCG == 2) tma_load_2d_2sm(sa + j * (kBK * 128), &tmA, &full_bar[stage], m0 + j * kChunk, p0);
+                else tma_load_2d(sa + j * (kBK * 128), &tmA, &full_bar[stage], m0 + j * kChunk, p0);
+              for (int t = 0; t < p.tpi; ++t) {
+                const int r = (tap0 + t) / 3, s = (tap0 + t) - r * 3;
+                for (int j = 0; j < bn_local / kChunk; ++j)
+                  ld4(sb + t * tap_b_bytes + j * (kBK * 128), &tmB, &full_bar[stage], n0 + j * kChunk, s - 1, h0 + r - 1, img);
+              }
             }
           }
           if (++stage == p.num_stages) { stage = 0; phase ^= 1u; }
@@ -749,6 +762,28 @@ extern "C" int ddpx_conv3x3_wgrad(const float* dy, const float* x, float* dw, in
   p.H = H; p.W = W; p.box_w = bw; p.box_h = bh; p.box_n = bnn; p.cin_total = Cin; p.cin_blocks = Cin / 32;
   p.out = dw; p.atomic = 1;
   CUtensorMap ta, tb;
+  static int big_cfg = -1;
+  if (big_cfg < 0) { const char* e = getenv("DDPX_WGRAD_BIGBOX"); big_cfg = (e && e[0] == '0') ? 0 : 1; }
+  p.big_box = (big_cfg && Cout % kBlockM == 0) ? 1 : 0;
+  if (p.big_box) {
+    // chunked views: (32 ch, pixels, Cout/32) and (32 ch, W, H, N, Cin/32); the chunk dimension has a 128-byte stride
+    {
+      uint64_t dims[3] = {32, static_cast<uint64_t>(P), static_cast<uint64_t>(Cout / 32)};
+      uint64_t str[2] = {static_cast<uint64_t>(Cout) * 4, 128};
+      uint32_t box[3] = {32, 32, static_cast<uint32_t>(kBlockM / 32)};
+      if ((rc = make_tmap(&ta, dy, false, 3, dims, str, box, true)) != DDPX_OK) { big_cfg = 0; p.big_box = 0; }
+    }
+    if (p.big_box) {
+      uint64_t dims[5] = {32, static_cast<uint64_t>(W), static_cast<uint64_t>(H), static_cast<uint64_t>(Nimg),
+                          static_cast<uint64_t>(Cin / 32)};
+      uint64_t str[4] = {static_cast<uint64_t>(Cin) * 4, static_cast<uint64_t>(Cin) * W * 4,
+                         static_cast<uint64_t>(Cin) * W * H * 4, 128};
+      uint32_t box[5] = {32, static_cast<uint32_t>(bw), static_cast<uint32_t>(bh), static_cast<uint32_t>(bnn),
+                         static_cast<uint32_t>(bn / cg / 32)};
+      if ((rc = make_tmap(&tb, x, false, 5, dims, str, box, true)) != DDPX_OK) { big_cfg = 0; p.big_box = 0; }
+    }
+    if (p.big_box) return launch_tc<MODE_WGRAD, false>(ta, tb, p, stream, cg);
+  }
   {
     uint64_t dims[2] = {static_cast<uint64_t>(Cout), static_cast<uint64_t>(P)};
     uint64_t str[1] = {static_cast<uint64_t>(Cout) * 4};
