@@ -131,7 +131,7 @@ tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
 
   const int tiles_mn = p.m_blocks * p.n_blocks;
   // "tap" doubles as the batch index in MODE_GEMM
-  const int taps = (kMode == MODE_WGRAD) ? 9 / p.tpi : (kMode == MODE_GEMM ? p.batch1 * p.batch2 : 1);
+  const int taps = (kMode == MODE_WGRAD) ? (9 + p.tpi - 1) / p.tpi : (kMode == MODE_GEMM ? p.batch1 * p.batch2 : 1);
   const int num_items = tiles_mn * taps * p.num_splits;
 
   auto decode = [&](int item, int& m_blk, int& n_blk, int& tap, int& split) {
@@ -172,14 +172,35 @@ tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
         const int nk = ksteps_of(split, m_blk);
         if (skipped(m_blk, n_blk)) continue;
         const int b1 = (kMode == MODE_GEMM) ? tap % p.batch1 : 0, b2 = (kMode == MODE_GEMM) ? tap / p.batch1 : 0;
+        // The producer is ONE thread: every instruction in its k-loop is latency-exposed, and with 235 of them (four
+        // integer divisions among them) it could not issue a k-step per 528 tensor-pipe cycles.  All divisions are
+        // done here, once per item; the loop only increments.
+        int cb = 0, t9 = 0, fr = 1, fs = 1;                 // FPROP: input-channel block, tap, filter row / column
+        int img = 0, h0 = 0, p0 = 0;                        // FPROP / WGRAD: image and first row of the pixel tile
+        if constexpr (kMode == MODE_FPROP) {
+          const int hw = p.H * p.W;
+          img = n0 / hw;
+          h0 = (n0 - img * hw) / p.W;
+          t9 = kbeg / p.cin_blocks;
+          cb = kbeg - t9 * p.cin_blocks;
+          if (p.conv_taps != 1) { fr = t9 / 3; fs = t9 - fr * 3; }
+        } else if constexpr (kMode == MODE_WGRAD) {
+          const int hw = p.H * p.W;
+          p0 = kbeg * 32;
+          img = p0 / hw;
+          h0 = (p0 - img * hw) / p.W;
+        }
+        const int tap0 = tap * p.tpi;                                   // WGRAD: first tap of the group
+        const int nt = (kMode == MODE_WGRAD) ? min(p.tpi, 9 - tap0) : 1; // taps in this group (the last may be short)
+        uint32_t tx_bytes = stage_bytes * kCG;                          // both CTAs' bytes land on the leader's barrier
+        if constexpr (kMode == MODE_WGRAD) tx_bytes = (kStageABytes + tap_b_bytes * static_cast<uint32_t>(nt)) * kCG;
         for (int i = 0; i < nk; ++i) {
-          const int kk = kbeg + i;
           mbar_wait(&empty_bar[stage], phase ^ 1u, 0x100u + stage);
           uint8_t* sa = smem + static_cast<size_t>(stage) * stage_bytes;
           uint8_t* sb = sa + kStageABytes;
-          if (leader) mbar_arrive_expect_tx(&full_bar[stage], stage_bytes * kCG);   // both CTAs' bytes land here
+          if (leader) mbar_arrive_expect_tx(&full_bar[stage], tx_bytes);
           if constexpr (kMode == MODE_GEMM) {
-            const int k0 = kk * kBK;
+            const int k0 = (kbeg + i) * kBK;
             if (!p.a_mn) {
               ld4(sa, &tmA, &full_bar[stage], k0, m0, b1, b2);
             } else {
@@ -193,32 +214,25 @@ tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
                 ld4(sb + j * (kBK * 128), &tmB, &full_bar[stage], n0 + j * kChunk, k0, b1, b2);
             }
           } else if constexpr (kMode == MODE_FPROP) {
-            // K order: tap-major, then input-channel block.  A = packed weights [tap][Cout][Cin].
-            const int t9 = kk / p.cin_blocks;
-            const int cb = kk - t9 * p.cin_blocks;
-            // a single-tap problem (cin_total taps == 1: pre-gathered patches, i.e. a 1x1 conv) reads the centre
-            const int r = (p.conv_taps == 1) ? 1 : t9 / 3, s = (p.conv_taps == 1) ? 1 : t9 - (t9 / 3) * 3;
+            // K order: tap-major, then input-channel block.  A = packed weights [tap][Cout][Cin]; a single-tap problem
+            // (pre-gathered patches, i.e. a 1x1 conv) reads the centre (fr = fs = 1).
             if constexpr (kCG == 2) tma_load_3d_2sm(sa, &tmA, &full_bar[stage], cb * kBK, m0, t9);
             else tma_load_3d(sa, &tmA, &full_bar[stage], cb * kBK, m0, t9);
-            // B = NHWC activations; tile of block_n consecutive pixels = box (box_w, box_h, box_n)
-            const int hw = p.H * p.W;
-            const int img = n0 / hw;
-            const int h0 = (n0 - img * hw) / p.W;
-            ld4(sb, &tmB, &full_bar[stage], cb * kBK, s - 1, h0 + r - 1, img);
+            // B = NHWC activations; tile of block_n consecutive pixels = box (box_w, box_h, box_n) shifted by the tap
+            ld4(sb, &tmB, &full_bar[stage], cb * kBK, fs - 1, h0 + fr - 1, img);
+            if (++cb == p.cin_blocks) {
+              cb = 0; ++t9;
+              if (p.conv_taps != 1 && ++fs == 3) { fs = 0; ++fr; }
+            }
           } else {
-            // WGRAD: K step = 32 consecutive pixels.  A = dY [pixels][Cout] (MN-major), B = shifted X.
-            // item "tap" = first tap of the group (tpi = 3: one filter row r, s = 0..2; tpi = 1: a single tap)
-            const int tap0 = tap * p.tpi;
-            const int p0 = kk * 32;
-            const int hw = p.H * p.W;
-            const int img = p0 / hw;
-            const int h0 = (p0 - img * hw) / p.W;
+            // WGRAD: K step = 32 consecutive pixels.  A = dY [pixels][Cout] (MN-major), B = shifted X; the item covers
+            // taps tap0 .. tap0+nt-1 (tpi = 3: one filter row; tpi = 2: pairs of taps; tpi = 1: a single tap)
             if (p.big_box) {
               // one TMA per operand tile: the maps carry the 32-channel chunk index as their outermost dimension, so a
               // box of (32 ch, 32 pixels, n chunks) lands as n consecutive [32 pixels][128 B] swizzle tiles
               if constexpr (kCG == 2) tma_load_3d_2sm(sa, &tmA, &full_bar[stage], 0, p0, m0 / kChunk);
               else tma_load_3d(sa, &tmA, &full_bar[stage], 0, p0, m0 / kChunk);
-              for (int t = 0; t < p.tpi; ++t) {
+              for (int t = 0; t < nt; ++t) {
                 const int r = (tap0 + t) / 3, s = (tap0 + t) - r * 3;
                 if constexpr (kCG == 2) tma_load_5d_2sm(sb + t * tap_b_bytes, &tmB, &full_bar[stage], 0, s - 1, h0 + r - 1, img, n0 / kChunk);
                 else tma_load_5d(sb + t * tap_b_bytes, &tmB, &full_bar[stage], 0, s - 1, h0 + r - 1, img, n0 / kChunk);
@@ -227,12 +241,15 @@ tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
               for (int j = 0; j < kBlockM / kChunk; ++j)
                 if constexpr (kCG == 2) tma_load_2d_2sm(sa + j * (kBK * 128), &tmA, &full_bar[stage], m0 + j * kChunk, p0);
                 else tma_load_2d(sa + j * (kBK * 128), &tmA, &full_bar[stage], m0 + j * kChunk, p0);
-              for (int t = 0; t < p.tpi; ++t) {
+              for (int t = 0; t < nt; ++t) {
                 const int r = (tap0 + t) / 3, s = (tap0 + t) - r * 3;
                 for (int j = 0; j < bn_local / kChunk; ++j)
                   ld4(sb + t * tap_b_bytes + j * (kBK * 128), &tmB, &full_bar[stage], n0 + j * kChunk, s - 1, h0 + r - 1, img);
               }
             }
+            p0 += 32;                       // next 32 pixels: box_h more rows of this image, or box_n whole images
+            if (p.box_n > 1) img += p.box_n;
+            else { h0 += p.box_h; if (h0 >= p.H) { h0 = 0; ++img; } }
           }
           if (++stage == p.num_stages) { stage = 0; phase ^= 1u; }
         }
@@ -262,19 +279,23 @@ tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
         mbar_wait(&tempty_bar[acc], acc_phase ^ 1u, 0x200u + acc);
         tc_fence_after();
         const uint32_t tmem_d = tmem_base + static_cast<uint32_t>(acc) * acc_cols;
+        uint32_t idesc_item = idesc;
+        if constexpr (kMode == MODE_WGRAD)
+          idesc_item = make_idesc(kBF16, a_mn, b_mn, kTileM, static_cast<uint32_t>(p.block_n * min(p.tpi, 9 - tap * p.tpi)));
         for (int i = 0; i < nk; ++i) {
           mbar_wait(&full_bar[stage], phase, 0x300u + stage);
           tc_fence_after();
           const uint32_t sa = smem_u32(smem + static_cast<size_t>(stage) * stage_bytes);
           const uint32_t sb = sa + kStageABytes;
-          for (int t = 0; t < p.tpi; ++t) {      // one accumulator per tap, all fed by the same A tile
+          // WGRAD with several taps per item: the taps' B tiles are consecutive 128-byte-wide chunks in the stage, so
+          // ONE instruction with N = taps * block_n covers them all.  (An SS-mode MMA costs ~118 cycles whatever its N -
+          // bench/mma_probe.cu - so three N=64 instructions were three times the price of one N=192.)
 #pragma unroll
-            for (int k = 0; k < kBK / kUmmaK; ++k) {
-              const uint64_t adesc = make_smem_desc_sw128(sa + k * a_kadv, a_lbo, a_sbo, a_lay);
-              const uint64_t bdesc = make_smem_desc_sw128(sb + t * tap_b_bytes + k * b_kadv, b_lbo, b_sbo, b_lay);
-              if constexpr (kCG == 2) tc_mma_2sm<kBF16>(tmem_d + t * p.block_n, adesc, bdesc, idesc, (i > 0 || k > 0) ? 1u : 0u);
-              else tc_mma<kBF16>(tmem_d + t * p.block_n, adesc, bdesc, idesc, (i > 0 || k > 0) ? 1u : 0u);
-            }
+          for (int k = 0; k < kBK / kUmmaK; ++k) {
+            const uint64_t adesc = make_smem_desc_sw128(sa + k * a_kadv, a_lbo, a_sbo, a_lay);
+            const uint64_t bdesc = make_smem_desc_sw128(sb + k * b_kadv, b_lbo, b_sbo, b_lay);
+            if constexpr (kCG == 2) tc_mma_2sm<kBF16>(tmem_d, adesc, bdesc, idesc_item, (i > 0 || k > 0) ? 1u : 0u);
+            else tc_mma<kBF16>(tmem_d, adesc, bdesc, idesc_item, (i > 0 || k > 0) ? 1u : 0u);
           }
           if constexpr (kCG == 2) tc_commit_2sm(&empty_bar[stage]); else tc_commit(&empty_bar[stage]);   // slot free (both CTAs)
           if (++stage == p.num_stages) { stage = 0; phase ^= 1u; }
@@ -291,7 +312,7 @@ tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
     const int ehalf = (warp - 4) >> 2;
     const int cols_half = ((static_cast<int>(acc_cols) + 63) / 64) * 32;
     const int cc_begin = ehalf * cols_half;
-    const int cc_end = min(cc_begin + cols_half, static_cast<int>(acc_cols));
+    const int cc_end_all = min(cc_begin + cols_half, static_cast<int>(acc_cols));
     int acc = 0;
     uint32_t acc_phase = 0;
     for (int item = first_item; item < num_items; item += item_stride) {
@@ -308,6 +329,8 @@ tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
       tc_fence_after();
       const uint32_t taddr = tmem_base + (static_cast<uint32_t>(ew * 32) << 16) + static_cast<uint32_t>(acc) * acc_cols;
       float ssum = 0.f, ssq = 0.f;
+      int cc_end = cc_end_all;
+      if constexpr (kMode == MODE_WGRAD) cc_end = min(cc_end_all, p.block_n * min(p.tpi, 9 - tap * p.tpi));
       for (int cc = cc_begin; cc < cc_end; cc += 32) {
         // cc walks all accumulator columns of the item; c0 is the column inside the current tap's tile
         const int tsub = cc / p.block_n;
@@ -511,6 +534,9 @@ static int pick_stages(int block_n, int tpi, int reserve) {
   const int stage = kStageABytes + block_n * 128 * tpi;
   int s = (224 * 1024 - reserve) / stage;
   if (s > kMaxStages) s = kMaxStages;
+  static int cap = -1;       // DDPX_MAX_STAGES: pipeline-depth experiments (latency- vs bandwidth-bound)
+  if (cap < 0) { const char* e = getenv("DDPX_MAX_STAGES"); cap = e ? atoi(e) : 0; }
+  if (cap >= 2 && s > cap) s = cap;
   if (s < 2) s = 2;
   return s;
 }
@@ -529,7 +555,7 @@ static int launch_tc_cg(const CUtensorMap& a, const CUtensorMap& b, TcParams& p,
     if (e != cudaSuccess) return DDPX_ERR_LAUNCH;
     attr_set = true;
   }
-  const int taps = (kMode == MODE_WGRAD) ? 9 / p.tpi : (kMode == MODE_GEMM ? p.batch1 * p.batch2 : 1);
+  const int taps = (kMode == MODE_WGRAD) ? (9 + p.tpi - 1) / p.tpi : (kMode == MODE_GEMM ? p.batch1 * p.batch2 : 1);
   const int items = p.m_blocks * p.n_blocks * taps * p.num_splits;
   const int max_clusters = num_sms() / kCG;
   int clusters = items < max_clusters ? items : max_clusters;
@@ -738,10 +764,12 @@ extern "C" int ddpx_conv3x3_wgrad(const float* dy, const float* x, float* dw, in
   static int tpi_cfg = -1;
   if (tpi_cfg < 0) {
     const char* e = getenv("DDPX_WGRAD_TPI");
-    tpi_cfg = (e && e[0] == '1') ? 1 : ((e && e[0] == '3') ? 3 : 0);
+    tpi_cfg = (e && e[0] >= '1' && e[0] <= '4') ? (e[0] - '0') : 0;
   }
-  p.tpi = tpi_cfg ? tpi_cfg : (Cin <= 64 ? 3 : 1);
-  const int max_bn = p.tpi == 3 ? 128 : 256;   // 3 accumulators of block_n columns must fit the 512 TMEM columns
+  // taps per item so that one MMA is as close to N = 256 as the layer allows: Cin <= 64 -> a filter row (3 taps,
+  // N = 192), Cin = 128 -> 2 taps (N = 256; groups 2,2,2,2,1), wider -> 1 tap with a 256-column tile
+  p.tpi = tpi_cfg ? tpi_cfg : (Cin <= 64 ? 3 : (Cin == 128 ? 2 : 1));
+  const int max_bn = 256 / p.tpi / 32 * 32;    // all taps of a group form ONE MMA: taps * block_n <= 256
   int bn = Cin >= max_bn ? max_bn : Cin;       // Cin is a multiple of 32
   while (Cin % bn) bn -= 32;
   if (bn < 32 || bn % 32) return DDPX_ERR_SHAPE;
@@ -750,7 +778,7 @@ extern "C" int ddpx_conv3x3_wgrad(const float* dy, const float* x, float* dw, in
   p.m_blocks = (Cout + kBlockM * cg - 1) / (kBlockM * cg);
   p.n_blocks = (Cin + bn - 1) / bn;
   p.k_steps_total = static_cast<int>(P / 32);
-  const int tiles = p.m_blocks * p.n_blocks * (9 / p.tpi);
+  const int tiles = p.m_blocks * p.n_blocks * ((9 + p.tpi - 1) / p.tpi);
   int splits = split_k;
   if (splits <= 0) {   // fill the machine about twice over
     splits = (2 * num_sms() + tiles - 1) / tiles;
