@@ -35,6 +35,27 @@ __global__ void pack_conv_w_kernel(const float* __restrict__ w, float* __restric
   }
 }
 
+// Tiled flavour for Cout, Cin multiples of 32: a block stages w[32 co][32 ci][9] (contiguous 1152-byte rows) in shared
+// memory and writes both packed layouts with 128-byte rows; the simple kernel above gathers with a 36-byte stride and
+// scatters the dgrad layout with a Cout-float stride (126 us per step for the 7 VGG layers, ~20 us of traffic).
+__global__ void __launch_bounds__(256)
+pack_conv_w_tiled_kernel(const float* __restrict__ w, float* __restrict__ wf, float* __restrict__ wd, int Cout, int Cin) {
+  __shared__ float tile[32][289];
+  const int ci0 = blockIdx.x * 32, co0 = blockIdx.y * 32;
+  for (int idx = threadIdx.x; idx < 32 * 288; idx += 256) {
+    const int co = idx / 288, j = idx - co * 288;
+    tile[co][j] = w[(static_cast<long long>(co0 + co) * Cin + ci0) * 9 + j];
+  }
+  __syncthreads();
+  for (int idx = threadIdx.x; idx < 9 * 1024; idx += 256) {
+    const int tap = idx >> 10, a = (idx >> 5) & 31, b = idx & 31;
+    if (wf != nullptr)      // a = co, b = ci
+      wf[(static_cast<long long>(tap) * Cout + co0 + a) * Cin + ci0 + b] = tile[a][b * 9 + tap];
+    if (wd != nullptr)      // a = ci, b = co; flipped tap, transposed
+      wd[(static_cast<long long>(8 - tap) * Cin + ci0 + a) * Cout + co0 + b] = tile[b][a * 9 + tap];
+  }
+}
+
 // ------------------------------------------------------------------------------------------------
 // direct conv for Cin == 3 (input NCHW, output NHWC).  One thread = one output pixel, all Cout channels.
 // ------------------------------------------------------------------------------------------------
@@ -253,6 +274,11 @@ __global__ void scale_copy_kernel(const float* __restrict__ src, float* __restri
 
 extern "C" int ddpx_pack_conv_weights(const float* w, float* w_fprop, float* w_dgrad, int Cout, int Cin, void* stream) {
   const long long total = static_cast<long long>(Cout) * Cin * 9;
+  if (Cout % 32 == 0 && Cin % 32 == 0 && Cout / 32 <= 65535) {
+    dim3 grid(Cin / 32, Cout / 32);
+    pack_conv_w_tiled_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(w, w_fprop, w_dgrad, Cout, Cin);
+    return LAUNCH_OK();
+  }
   pack_conv_w_kernel<<<nblocks(total, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(w, w_fprop, w_dgrad, Cout, Cin);
   return LAUNCH_OK();
 }
@@ -343,17 +369,22 @@ extern "C" int ddpx_zero(void* p, long long bytes, void* stream) {
 namespace {
 __global__ void gemm_small_kernel(const float* __restrict__ A, const float* __restrict__ B, float* __restrict__ C, int M, int N,
                                   int K, long long sam, long long sak, long long sbn, long long sbk, long long ldc,
-                                  const float* __restrict__ bias, int act, int accumulate) {
+                                  const float* __restrict__ bias, int act, int accumulate, int k_per_split) {
   __shared__ float As[32][33];
   __shared__ float Bs[32][33];
   const int tx = threadIdx.x, ty = threadIdx.y;           // 32 x 8
   const int m0 = blockIdx.y * 32, n0 = blockIdx.x * 32;
+  // split-K over blockIdx.z (few-tile problems such as the 512 -> 10 classifier would otherwise run 16 blocks through
+  // 16 dependent load-sync-compute rounds): partial sums are added atomically into a zeroed / accumulated C
+  const int kbeg = blockIdx.z * k_per_split;
+  const int kend = min(K, kbeg + k_per_split);
+  const bool split = gridDim.z > 1;
   float acc[4] = {0.f, 0.f, 0.f, 0.f};
-  for (int k0 = 0; k0 < K; k0 += 32) {
+  for (int k0 = kbeg; k0 < kend; k0 += 32) {
     for (int j = ty; j < 32; j += 8) {
       const int m = m0 + j, n = n0 + j, k = k0 + tx;
-      As[j][tx] = (m < M && k < K) ? A[m * sam + k * sak] : 0.f;
-      Bs[j][tx] = (n < N && k < K) ? B[n * sbn + k * sbk] : 0.f;
+      As[j][tx] = (m < M && k < kend) ? A[m * sam + k * sak] : 0.f;
+      Bs[j][tx] = (n < N && k < kend) ? B[n * sbn + k * sbk] : 0.f;
     }
     __syncthreads();
 #pragma unroll
@@ -370,10 +401,11 @@ __global__ void gemm_small_kernel(const float* __restrict__ A, const float* __re
     for (int i = 0; i < 4; ++i) {
       const int m = m0 + ty + 8 * i;
       if (m < M) {
-        float v = acc[i] + (bias != nullptr ? bias[n] : 0.f);
+        float v = acc[i] + ((bias != nullptr && blockIdx.z == 0) ? bias[n] : 0.f);
         if (act == 1) v = fmaxf(v, 0.f);
         float* c = C + m * ldc + n;
-        *c = accumulate ? *c + v : v;
+        if (split) atomicAdd(c, v);
+        else *c = accumulate ? *c + v : v;
       }
     }
   }
@@ -385,7 +417,22 @@ extern "C" int ddpx_gemm_small(const float* A, const float* B, float* C, int M, 
                                void* stream) {
   dim3 grid((N + 31) / 32, (M + 31) / 32), block(32, 8);
   if (grid.y > 65535) return DDPX_ERR_SHAPE;
+  int splits = 1;
+  const int tiles = static_cast<int>(grid.x * grid.y);
+  if (act == 0 && tiles < 148 && K >= 128) {
+    splits = (2 * 148) / tiles;
+    if (splits > K / 64) splits = K / 64;
+    if (splits < 1) splits = 1;
+  }
+  int k_per_split = ((K + splits - 1) / splits + 31) / 32 * 32;
+  splits = (K + k_per_split - 1) / k_per_split;
+  if (splits > 1 && !accumulate) {      // rows of C are ldc apart: clear exactly the M x N window
+    cudaError_t e = cudaMemset2DAsync(C, static_cast<size_t>(ldc) * sizeof(float), 0, static_cast<size_t>(N) * sizeof(float),
+                                      static_cast<size_t>(M), static_cast<cudaStream_t>(stream));
+    if (e != cudaSuccess) return DDPX_ERR_LAUNCH;
+  }
+  grid.z = splits;
   gemm_small_kernel<<<grid, block, 0, static_cast<cudaStream_t>(stream)>>>(A, B, C, M, N, K, sam, sak, sbn, sbk, ldc, bias, act,
-                                                                          accumulate);
+                                                                          accumulate, k_per_split);
   return LAUNCH_OK();
 }

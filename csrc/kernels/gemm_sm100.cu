@@ -780,8 +780,14 @@ extern "C" int ddpx_conv3x3_wgrad(const float* dy, const float* x, float* dw, in
   p.k_steps_total = static_cast<int>(P / 32);
   const int tiles = p.m_blocks * p.n_blocks * ((9 + p.tpi - 1) / p.tpi);
   int splits = split_k;
-  if (splits <= 0) {   // fill the machine about twice over
-    splits = (2 * num_sms() + tiles - 1) / tiles;
+  if (splits <= 0) {
+    // ONE wave of work items: every extra split re-adds a whole [Cout][Cin][9] tile with scattered fp32 atomics
+    // (512->512 @ 4x4 spent 3/4 of its time there with 9 splits), so split K only until every SM / CTA pair has an item.
+    // DDPX_WGRAD_WAVES=n asks for n waves instead.
+    static int waves = -1;
+    if (waves < 0) { const char* e = getenv("DDPX_WGRAD_WAVES"); waves = e ? atoi(e) : 1; if (waves < 1) waves = 1; }
+    const int units = num_sms() / cg;
+    splits = waves * units / tiles;
     if (splits < 1) splits = 1;
   }
   if (splits > p.k_steps_total) splits = p.k_steps_total;
