@@ -12,6 +12,7 @@
 //     the initial parameter sync and the per-forward BatchNorm-buffer sync.
 // Every spin is bounded: after ~20 s a rank writes an error code into its pad and traps instead of hanging the box.
 #include <cuda_runtime.h>
+#include <cstdlib>
 #include <cuda_bf16.h>
 #include <stdint.h>
 #include <string.h>
@@ -159,6 +160,153 @@ __device__ __forceinline__ void apply_update(const Hyper& h, const Slot& s, long
   }
 }
 
+// the same update on registers: g, p, s0 (momentum / exp_avg), s1 (exp_avg_sq) hold one 16-byte vector each
+template <int V>
+__device__ __forceinline__ void update_regs(const Hyper& h, const float* g, float* p, float* s0, float* s1) {
+#pragma unroll
+  for (int k = 0; k < V; ++k) {
+    if (h.opt == 1) {
+      float gv = g[k] + h.wd * p[k];
+      if (h.momentum != 0.f) {
+        const float bv = h.first_step ? gv : h.momentum * s0[k] + (1.f - h.dampening) * gv;
+        s0[k] = bv;
+        gv = h.nesterov ? gv + h.momentum * bv : bv;
+      }
+      p[k] -= h.lr * gv;
+    } else {
+      const float pv = p[k] * (1.f - h.lr * h.wd);
+      const float mv = h.beta1 * s0[k] + (1.f - h.beta1) * g[k];
+      const float vv = h.beta2 * s1[k] + (1.f - h.beta2) * g[k] * g[k];
+      s0[k] = mv;
+      s1[k] = vv;
+      p[k] = pv - (h.lr / h.bc1) * mv / (sqrtf(vv) / h.bc2_sqrt + h.eps);
+    }
+  }
+}
+
+// Optimizer update of one parameter slot.  kPeers = false: the gradient is the (already averaged) local bucket;
+// kPeers = true (one-shot): it is summed from every rank's bucket here.  16-byte vectors, kUU of them per thread per trip
+// with every load issued before the first use: the scalar one-element-per-trip loop this replaces was latency-bound (one
+// DRAM round trip per element per thread - a 27 MB VGG bucket took 685 us and slowed the conv kernels it overlapped).
+template <typename T, bool kPeers>
+__device__ __forceinline__ void update_slot(const Peers& P, const Hyper& h, const Slot& s) {
+  constexpr int V = Vec<T>::N;
+  constexpr int kUU = kPeers ? 1 : 4;
+  const long long tid = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  const long long nth = static_cast<long long>(gridDim.x) * blockDim.x;
+  const bool has0 = (h.opt == 2) || (h.opt == 1 && h.momentum != 0.f);
+  const bool has1 = (h.opt == 2);
+  const bool rd0 = has0 && !(h.opt == 1 && h.first_step);
+  const uintptr_t align = reinterpret_cast<uintptr_t>(s.param) | (has0 ? reinterpret_cast<uintptr_t>(s.state0) : 0) |
+                          (has1 ? reinterpret_cast<uintptr_t>(s.state1) : 0) | static_cast<uintptr_t>(s.offset * sizeof(T));
+  const long long nv = (align & 15) ? 0 : s.numel / V;
+  uint4* pp = reinterpret_cast<uint4*>(s.param);
+  uint4* q0 = reinterpret_cast<uint4*>(s.state0);
+  uint4* q1 = reinterpret_cast<uint4*>(s.state1);
+  for (long long j0 = tid; j0 < nv; j0 += nth * kUU) {
+    uint4 gq[kUU][kPeers ? kMaxRanks : 1], pq[kUU], aq[kUU], bq[kUU];
+#pragma unroll
+    for (int u = 0; u < kUU; ++u) {
+      const long long j = j0 + u * nth;
+      if (j < nv) {
+        if constexpr (kPeers) {
+#pragma unroll
+          for (int r = 0; r < kMaxRanks; ++r)
+            if (r < P.world) gq[u][r] = reinterpret_cast<const uint4*>(static_cast<const T*>(P.buf[r]) + s.offset)[j];
+        } else {
+          gq[u][0] = reinterpret_cast<const uint4*>(static_cast<const T*>(P.buf[P.rank]) + s.offset)[j];
+        }
+        pq[u] = pp[j];
+        if (rd0) aq[u] = q0[j];
+        if (has1) bq[u] = q1[j];
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < kUU; ++u) {
+      const long long j = j0 + u * nth;
+      if (j >= nv) break;
+      float g[V], pf[V], s0[V], s1[V];
+      if constexpr (kPeers) {
+#pragma unroll
+        for (int k = 0; k < V; ++k) g[k] = 0.f;
+#pragma unroll
+        for (int r = 0; r < kMaxRanks; ++r) {
+          if (r < P.world) {
+            float f[V];
+            unpack<T>(gq[u][r], f);
+#pragma unroll
+            for (int k = 0; k < V; ++k) g[k] += f[k];
+          }
+        }
+      } else {
+        unpack<T>(gq[u][0], g);
+      }
+      unpack<T>(pq[u], pf);
+      if (rd0) unpack<T>(aq[u], s0);
+      else {
+#pragma unroll
+        for (int k = 0; k < V; ++k) s0[k] = 0.f;
+      }
+      if (has1) unpack<T>(bq[u], s1);
+      update_regs<V>(h, g, pf, s0, s1);
+      pp[j] = pack<T>(pf);
+      if (has0) q0[j] = pack<T>(s0);
+      if (has1) q1[j] = pack<T>(s1);
+    }
+  }
+  // scalar tail (and unaligned slots)
+  for (long long j = nv * V + tid; j < s.numel; j += nth) {
+    float g = 0.f;
+    if constexpr (kPeers) {
+#pragma unroll 1
+      for (int r = 0; r < P.world; ++r) g += ldT(static_cast<const T*>(P.buf[r]) + s.offset + j);
+    } else {
+      g = ldT(static_cast<const T*>(P.buf[P.rank]) + s.offset + j);
+    }
+    apply_update<T>(h, s, j, g);
+  }
+}
+
+// two-shot step 2: reduce vectors [v0, v1) of every rank's bucket in fixed rank order and store the sum into every
+// rank's bucket.  kW = ranks the loops are unrolled for, kU = vectors per thread per trip: kW * kU = 16 sixteen-byte peer
+// loads are in flight per thread whatever the world size (NVLink load latency ~2-3 us).
+template <typename T, int kW, int kU>
+__device__ __forceinline__ void reduce_shard(const Peers& P, long long v0, long long v1) {
+  constexpr int V = Vec<T>::N;
+  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+  for (long long i0 = v0 + static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i0 < v1; i0 += stride * kU) {
+    uint4 in[kU][kW];
+#pragma unroll
+    for (int u = 0; u < kU; ++u) {
+      const long long i = i0 + u * stride;
+#pragma unroll
+      for (int r = 0; r < kW; ++r)
+        if (r < P.world && i < v1) in[u][r] = reinterpret_cast<const uint4*>(P.buf[r])[i];
+    }
+#pragma unroll
+    for (int u = 0; u < kU; ++u) {
+      const long long i = i0 + u * stride;
+      if (i >= v1) break;
+      float acc[V];
+#pragma unroll
+      for (int k = 0; k < V; ++k) acc[k] = 0.f;
+#pragma unroll
+      for (int r = 0; r < kW; ++r) {
+        if (r < P.world) {
+          float f[V];
+          unpack<T>(in[u][r], f);
+#pragma unroll
+          for (int k = 0; k < V; ++k) acc[k] += f[k];
+        }
+      }
+      const uint4 o = pack<T>(acc);
+#pragma unroll
+      for (int r = 0; r < kW; ++r)
+        if (r < P.world) reinterpret_cast<uint4*>(P.buf[r])[i] = o;
+    }
+  }
+}
+
 // ------------------------------------------------------------------------------------------------
 // fused all-reduce (+ optimizer).  n = bucket elements (multiple of the vector width).
 // mode 0 = two-shot, mode 1 = one-shot (requires opt != 0: the local bucket is not rewritten)
@@ -182,39 +330,9 @@ allreduce_fused_kernel(const Peers P, const uint32_t gen, const long long n, con
     const long long v0 = per * P.rank, v1 = min(v0 + per, nvec);
     // U vectors per thread per trip, all peer loads issued before the first add: the ~2 us NVLink load latency needs
     // tens of 16-byte requests in flight per thread to reach link bandwidth
-    constexpr int U = 2;
-    const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
-    for (long long i0 = v0 + static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i0 < v1; i0 += stride * U) {
-      uint4 in[U][kMaxRanks];
-#pragma unroll
-      for (int u = 0; u < U; ++u) {
-        const long long i = i0 + u * stride;
-#pragma unroll
-        for (int r = 0; r < kMaxRanks; ++r)
-          if (r < P.world && i < v1) in[u][r] = reinterpret_cast<const uint4*>(P.buf[r])[i];
-      }
-#pragma unroll
-      for (int u = 0; u < U; ++u) {
-        const long long i = i0 + u * stride;
-        if (i >= v1) break;
-        float acc[V];
-#pragma unroll
-        for (int k = 0; k < V; ++k) acc[k] = 0.f;
-#pragma unroll
-        for (int r = 0; r < kMaxRanks; ++r) {
-          if (r < P.world) {
-            float f[V];
-            unpack<T>(in[u][r], f);
-#pragma unroll
-            for (int k = 0; k < V; ++k) acc[k] += f[k];
-          }
-        }
-        const uint4 o = pack<T>(acc);
-#pragma unroll
-        for (int r = 0; r < kMaxRanks; ++r)
-          if (r < P.world) reinterpret_cast<uint4*>(P.buf[r])[i] = o;
-      }
-    }
+    if (P.world <= 2) reduce_shard<T, 2, 8>(P, v0, v1);
+    else if (P.world <= 4) reduce_shard<T, 4, 4>(P, v0, v1);
+    else reduce_shard<T, kMaxRanks, 2>(P, v0, v1);
     // ---- 3. when the whole grid is done with the shard, tell every peer
     last_cta_does(pad + PAD_COUNTER, [&] {
       for (int r = 0; r < P.world; ++r) st_release_sys(P.pad[r] + PAD_DONE + P.rank, gen);
@@ -224,26 +342,11 @@ allreduce_fused_kernel(const Peers P, const uint32_t gen, const long long n, con
     __syncthreads();
     // ---- 5. optimizer update of every parameter slot of the bucket from the (now averaged) local bucket
     if (h.opt != 0) {
-      const T* g = static_cast<const T*>(P.buf[P.rank]);
-      for (int si = 0; si < slots.n; ++si) {
-        const Slot& s = slots.s[si];
-        for (long long j = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; j < s.numel;
-             j += static_cast<long long>(gridDim.x) * blockDim.x)
-          apply_update<T>(h, s, j, ldT(g + s.offset + j));
-      }
+      for (int si = 0; si < slots.n; ++si) update_slot<T, false>(P, h, slots.s[si]);
     }
   } else {
     // ---- one-shot: every rank reduces the whole bucket from peer memory and updates its replica directly
-    for (int si = 0; si < slots.n; ++si) {
-      const Slot& s = slots.s[si];
-      for (long long j = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; j < s.numel;
-           j += static_cast<long long>(gridDim.x) * blockDim.x) {
-        float acc = 0.f;
-#pragma unroll 1
-        for (int r = 0; r < P.world; ++r) acc += ldT(static_cast<const T*>(P.buf[r]) + s.offset + j);
-        apply_update<T>(h, s, j, acc);
-      }
-    }
+    for (int si = 0; si < slots.n; ++si) update_slot<T, true>(P, h, slots.s[si]);
     // exit barrier: nobody may refill its bucket before every peer finished reading it
     last_cta_does(pad + PAD_COUNTER, [&] {
       for (int r = 0; r < P.world; ++r) st_release_sys(P.pad[r] + PAD_EXIT + P.rank, gen);
@@ -386,8 +489,17 @@ extern "C" int ddpx_p2p_allreduce_fused(int rank, int world, void* const* bufs, 
   if (ctas < 1) ctas = 1;
   if (ctas > 148) ctas = 148;
   cudaStream_t s = static_cast<cudaStream_t>(stream);
-  if (is_bf16) allreduce_fused_kernel<__nv_bfloat16><<<ctas, 512, 0, s>>>(P, gen, n, mode, h, tab);
-  else allreduce_fused_kernel<float><<<ctas, 512, 0, s>>>(P, gen, n, mode, h, tab);
+  // 256 threads x ~100 registers leave room for a communication CTA NEXT TO a resident conv CTA (384 threads x <= 96
+  // registers, ~226 KB of shared memory): the all-reduce then starts at once and shares the SM with the mostly idle
+  // warp-specialised compute CTA instead of waiting for, or displacing, a persistent kernel.  DDPX_COMM_THREADS overrides.
+  static int threads = 0;
+  if (threads == 0) {
+    const char* e = getenv("DDPX_COMM_THREADS");
+    threads = e ? atoi(e) : 256;
+    if (threads < 64 || threads > 512 || threads % 32) threads = 256;
+  }
+  if (is_bf16) allreduce_fused_kernel<__nv_bfloat16><<<ctas, threads, 0, s>>>(P, gen, n, mode, h, tab);
+  else allreduce_fused_kernel<float><<<ctas, threads, 0, s>>>(P, gen, n, mode, h, tab);
   return CUDA_OK(cudaGetLastError());
 }
 

@@ -28,6 +28,7 @@ class RuntimeConfig:
     first_bucket_mb: float = 1.0
     comm_ctas: int = 32                 # CTAs a communication kernel may occupy
     fuse_optimizer: bool = True
+    broadcast_buffers: bool = True      # DataParallel default (torch DDP default); DDPX_BROADCAST_BUFFERS=0 for diagnosis
     wait_timeout_s: float = 30.0        # device-side flag waits give up after this long
     checkpoint_path: str = "checkpoint.pt"   # multigpu.py:111
     metrics_jsonl: str = ""
@@ -42,6 +43,7 @@ class RuntimeConfig:
         c.bucket_cap_mb = float(_env_str("DDPX_BUCKET_CAP_MB", str(c.bucket_cap_mb)))
         c.comm_ctas = _env_int("DDPX_COMM_CTAS", c.comm_ctas)
         c.fuse_optimizer = _env_int("DDPX_FUSE_OPTIMIZER", 1) == 1
+        c.broadcast_buffers = _env_int("DDPX_BROADCAST_BUFFERS", 1) == 1
         c.wait_timeout_s = float(_env_str("DDPX_WAIT_TIMEOUT_S", str(c.wait_timeout_s)))
         c.checkpoint_path = _env_str("DDPX_CHECKPOINT_PATH", c.checkpoint_path)
         c.metrics_jsonl = _env_str("DDPX_METRICS_JSONL", c.metrics_jsonl)

