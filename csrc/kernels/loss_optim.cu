@@ -279,6 +279,32 @@ __global__ void sgd_multi_kernel(const __grid_constant__ TensorTable t, float lr
   }
 }
 
+// dst[i] = src[i] * scale for a table of tensors in ONE launch (gradient reducer: every gradient of a bucket goes into
+// its slot of the flat communication buffer, pre-divided by the world size).  t.p = destinations, t.g = sources.
+template <typename T>
+__global__ void scale_copy_multi_kernel(const __grid_constant__ TensorTable t, float scale) {
+  const int total_chunks = t.chunk_start[t.n];
+  for (int chunk = blockIdx.x; chunk < total_chunks; chunk += gridDim.x) {
+    const int ti = find_tensor(t, chunk);
+    const long long base = static_cast<long long>(chunk - t.chunk_start[ti]) * kChunk;
+    const long long end = min(base + kChunk, t.numel[ti]);
+    T* __restrict__ d = static_cast<T*>(t.p[ti]);
+    const T* __restrict__ g = static_cast<const T*>(t.g[ti]);
+    constexpr int V = ddpx::VecOf<T>::N;
+    const bool al = ((reinterpret_cast<uintptr_t>(d) | reinterpret_cast<uintptr_t>(g)) & 15) == 0;
+    const long long nvec = al ? (end - base) / V : 0;
+    for (long long vi = threadIdx.x; vi < nvec; vi += blockDim.x) {
+      const long long i = base + vi * V;
+      float v[V];
+      ddpx::vload(g + i, v);
+#pragma unroll
+      for (int k = 0; k < V; ++k) v[k] *= scale;
+      ddpx::vstore(d + i, v);
+    }
+    for (long long i = base + nvec * V + threadIdx.x; i < end; i += blockDim.x) d[i] = from_f<T>(to_f(g[i]) * scale);
+  }
+}
+
 // torch AdamW semantics: p *= 1 - lr*wd; m = b1*m + (1-b1)*g; v = b2*v + (1-b2)*g^2;
 // p -= lr/bc1 * m / (sqrt(v)/sqrt(bc2) + eps)
 template <typename T>
@@ -462,4 +488,19 @@ extern "C" int ddpx_adamw_multi(int n, void* const* params, void* const* grads, 
                                                                                    bc2_sqrt, grad_scale);
   }
   return LAUNCH_OK();
+}
+
+extern "C" int ddpx_scale_copy_multi(int n, void* const* dst, void* const* src, const long long* numel, float scale, int is_bf16,
+                                     void* stream) {
+  for (int off = 0; off < n; off += kMaxTensors) {
+    const int m = (n - off) < kMaxTensors ? (n - off) : kMaxTensors;
+    TensorTable t;
+    int rc = fill_table(t, m, dst + off, src + off, nullptr, nullptr, numel + off);
+    if (rc != DDPX_OK) return rc;
+    int grid = t.chunk_start[m] < 148 * 8 ? t.chunk_start[m] : 148 * 8;
+    if (grid < 1) continue;
+    if (is_bf16) scale_copy_multi_kernel<__nv_bfloat16><<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(t, scale);
+    else scale_copy_multi_kernel<float><<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(t, scale);
+  }
+  return cudaGetLastError() == cudaSuccess ? DDPX_OK : DDPX_ERR_LAUNCH;
 }

@@ -234,6 +234,14 @@ def sgd_multi(params, grads, bufs, lr, momentum, dampening, weight_decay, nester
           launches=(n + 95) // 96)
 
 
+def scale_copy_multi(dsts, srcs, scale):
+    """dsts[i] = srcs[i] * scale, one launch per 96 tensors (all the same dtype, contiguous)."""
+    n = len(dsts)
+    numel = (c_longlong * n)(*[d.numel() for d in dsts])
+    _call("ddpx_scale_copy_multi", c_int(n), _ptr_array(dsts), _ptr_array(srcs), numel, c_float(scale),
+          c_int(1 if dsts[0].dtype == torch.bfloat16 else 0), _st(), launches=(n + 95) // 96)
+
+
 def adamw_multi(params, grads, exp_avg, exp_avg_sq, lr, beta1, beta2, eps, weight_decay, step, grad_scale=1.0):
     n = len(params)
     numel = (c_longlong * n)(*[p.numel() for p in params])

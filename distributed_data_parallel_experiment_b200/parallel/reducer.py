@@ -69,6 +69,10 @@ class Reducer:
         self._hooks = []
         self._callback_queued = False
         self._scratch = (ctypes.c_int * max(1, len(self.params)))()
+        # CUDA: gradients are gathered into their bucket by ONE multi-tensor kernel when the bucket becomes launchable
+        # instead of one small kernel per parameter from the hook (34 launches per VGG step -> 3)
+        self._batch_copy = (self.device.type == "cuda" and
+                            all(p.dtype in (torch.float32, torch.bfloat16) for p in self.params))
         self.stats = {"rebuilt_bucket_sizes": [], "num_buckets": 0, "launched": 0}
         # first iteration: one bucket holding everything (distributed.py:1224-1225, find_unused_parameters=False)
         idx, _ = compute_bucket_assignment_by_size(self.params, [2 ** 62])
@@ -154,11 +158,12 @@ class Reducer:
         g = param.grad
         if g is None:
             raise RuntimeError("gradient hook fired without a gradient")
-        scale = 1.0 / self.world_size
-        if g.data_ptr() != view.data_ptr():
-            _scaled_copy(view, g, scale)
-        elif scale != 1.0:
-            _scaled_copy(view, view, scale)
+        if not self._batch_copy:
+            scale = 1.0 / self.world_size
+            if g.data_ptr() != view.data_ptr():
+                _scaled_copy(view, g, scale)
+            elif scale != 1.0:
+                _scaled_copy(view, view, scale)
         out = self._scratch
         k = self._lib.ddpx_reducer_mark_ready(ctypes.c_void_p(self._core), pid, out, len(self.params))
         if k == -1:
@@ -171,7 +176,28 @@ class Reducer:
             self._callback_queued = True
             torch.autograd.Variable._execution_engine.queue_callback(self.finalize_backward)
 
+    def _gather_bucket(self, bucket: Bucket):
+        """All gradients of the bucket -> their slots, pre-divided by the world size, in one launch."""
+        views = bucket.views[self.step_parity if self.double_buffer else 0]
+        scale = 1.0 / self.world_size
+        dsts, srcs = [], []
+        for pid, view in zip(bucket.param_ids, views):
+            g = self.params[pid].grad
+            if g.dtype == view.dtype and g.is_contiguous():
+                if g.data_ptr() == view.data_ptr() and scale == 1.0:
+                    continue
+                dsts.append(view); srcs.append(g)
+            else:
+                view.copy_(g)
+                if scale != 1.0:
+                    view.mul_(scale)
+        if dsts:
+            from ..ops import native
+            native.scale_copy_multi(dsts, srcs, scale)
+
     def _launch(self, bucket: Bucket):
+        if self._batch_copy:
+            self._gather_bucket(bucket)
         buf = bucket.buffers[self.step_parity if self.double_buffer else 0]
         self.stats["launched"] += 1
         if self.fused is not None:

@@ -130,6 +130,9 @@ int ddpx_ce_bwd(const void* logits, const long long* targets, const float* lse, 
 int ddpx_scale_by_device_scalar(void* p, long long n, const float* g, int bf16, void* stream);
 int ddpx_mse(const float* pred, const float* target, float* dpred, float* loss_sum, long long n, void* stream);
 /* one launch for all tensors; torch SGD / AdamW semantics (M:97, torch/optim/sgd.py:346-380) */
+/* dst[i][:] = src[i][:] * scale for n tensors in one launch per 96 tensors (gradient reducer: gradients -> bucket slots). */
+int ddpx_scale_copy_multi(int n, void* const* dst, void* const* src, const long long* numel, float scale, int is_bf16,
+                          void* stream);
 int ddpx_sgd_multi(int n, void* const* params, void* const* grads, void* const* momentum_bufs, const long long* numel,
                    float lr, float momentum, float dampening, float weight_decay, int nesterov, int first_step,
                    float grad_scale, int is_bf16, void* stream);

@@ -154,25 +154,30 @@ def test_vgg_fused_p2p_training_tracks_torch_ddp():
     for k, v in outs[0]["mine"].items():
         if "running" not in k and "num_batches" not in k:
             assert torch.equal(v, outs[1]["mine"][k]), k
-    # same framework, same kernels, but gradients through NCCL and the optimizer as a separate step: isolates the
-    # fused P2P all-reduce + SGD path.  fp32-atomic ordering differs between runs and a 4-step trajectory through
-    # BatchNorm / ReLU amplifies it, so weights are compared tightly and the small-norm bias vectors loosely.
+    # Same framework and kernels, but gradients through NCCL and the optimizer as a separate step: isolates the fused P2P
+    # all-reduce + SGD path.  What is compared is the UPDATE (final - initial weights) of every conv / linear weight: its
+    # norm must agree within 2 % (a missing 1/world, a wrong momentum or weight-decay term shows up here) and its
+    # direction within cos > 0.97.  Tighter is not meaningful: TF32 rounding and fp32-atomic ordering differ from run to
+    # run, and ReLU / max-pool decisions amplify that to ~0.2-0.7 % of direction noise over 4 steps - measured alike
+    # between any two of {this framework over P2P, over NCCL, torch DDP + cuDNN} (profiles/raw/p2p_parity_report*.json).
     base = _run(_w_vgg_parity, world, "nccl")
     assert not base[0]["fused"]
-    report = {}
-    for k, v in outs[0]["mine"].items():
-        if "num_batches" in k:
-            continue
-        ref = base[0]["mine"][k]
-        if k.endswith(".weight"):      # compare the UPDATE (final - initial): sensitive to a wrong average / optimizer step
-            i0 = outs[0]["init"][k]
-            report[k] = (((v - i0) - (ref - i0)).norm() / (ref - i0).norm().clamp_min(1e-12)).item()
-        else:
-            report[k] = ((v - ref).norm() / ref.norm().clamp_min(1e-6)).item()
-    report["losses_p2p"] = outs[0]["losses"]; report["losses_nccl"] = base[0]["losses"]; report["losses_torch"] = outs[0]["t_losses"]
-    for k in ("backbone.conv7.weight", "classifier.weight", "backbone.conv3.weight"):
-        o = outs[0]["oracle"][k]; i0 = outs[0]["init"][k]
-        report["vs_torch/" + k] = (((outs[0]["mine"][k] - i0) - (o - i0)).norm() / (o - i0).norm().clamp_min(1e-12)).item()
+
+    def _cmp(a, b, i0):
+        da, db = (a - i0).flatten().double(), (b - i0).flatten().double()
+        return {"norm_ratio": (da.norm() / db.norm()).item(), "cos": (da @ db / (da.norm() * db.norm())).item()}
+
+    report = {"losses_p2p": outs[0]["losses"], "losses_nccl": base[0]["losses"], "losses_torch": outs[0]["t_losses"]}
+    weights = [k for k in outs[0]["mine"] if k.endswith(".weight") and ".bn" not in k]
+    for k in weights:
+        i0 = outs[0]["init"][k]
+        report["p2p_vs_nccl/" + k] = _cmp(outs[0]["mine"][k], base[0]["mine"][k], i0)
+        report["p2p_vs_torch/" + k] = _cmp(outs[0]["mine"][k], outs[0]["oracle"][k], i0)
+        report["nccl_vs_torch/" + k] = _cmp(base[0]["mine"][k], base[0]["oracle"][k], i0)
+    for k in outs[0]["mine"]:
+        if "running" in k:
+            ref = base[0]["mine"][k]
+            report["p2p_vs_nccl/" + k] = ((outs[0]["mine"][k] - ref).norm() / ref.norm().clamp_min(1e-6)).item()
     try:
         import json
         os.makedirs(str(REPO / "gpurun_out"), exist_ok=True)
@@ -181,19 +186,10 @@ def test_vgg_fused_p2p_training_tracks_torch_ddp():
     except Exception:
         pass
     for k, r in report.items():
-        if k.startswith("vs_torch/") or k.startswith("losses"):
-            continue
-        if k.endswith(".weight") and ".bn" not in k:
-            assert r < 5e-2, (k, r)
+        if isinstance(r, dict):
+            assert abs(r["norm_ratio"] - 1.0) < 0.02 and r["cos"] > 0.97, (k, r)
         elif "running" in k:
             assert r < 5e-2, (k, r)
-        elif k.endswith(".bias") or ".bn" in k:
-            # BatchNorm shifts start at 0 and their gradient is a cancellation-dominated sum over N*H*W values: after
-            # 4 warm-up steps their norm is tiny and run-to-run noise (fp32 atomics order, TF32) is ~0.2-0.3 of it -
-            # measured between two runs of this framework regardless of the backend (profiles/raw/p2p_parity_report*.json)
-            assert r < 0.6, (k, r)
-    # and the whole thing tracks torch DDP + NCCL + cuDNN: loss curve and the large weight tensors
+    # and the loss curve tracks torch DDP + NCCL + cuDNN
     for a, b in zip(outs[0]["losses"], outs[0]["t_losses"]):
-        assert abs(a - b) < 0.05 * max(1.0, abs(b)), (outs[0]["losses"], outs[0]["t_losses"])
-    for k in ("backbone.conv7.weight", "classifier.weight", "backbone.conv3.weight"):
-        assert report["vs_torch/" + k] < 0.1, (k, report["vs_torch/" + k])
+        assert abs(a - b) < 0.02 * max(1.0, abs(b)), (outs[0]["losses"], outs[0]["t_losses"])
