@@ -78,9 +78,9 @@ __device__ __forceinline__ float gelu_tanh(float x) {
 // tcgen05 cta_group::2 - each CTA stages its own 128 rows of A and HALF of the B tile, so a k-step costs 32 KB instead
 // of 48 KB of L2->SM traffic per CTA and the same shared memory holds 6 stages instead of 4 (ncu on the 1-CTA kernel:
 // tensor pipe 58 % active, paced by operand delivery - profiles/ncu_conv_fprop.md).
-// Register budget: the convolution flavours are capped at 96 registers so that a 256-thread communication CTA (fused
-// all-reduce, csrc/runtime/p2p.cu) fits on the same SM next to this persistent kernel; the GEMM flavour keeps the
-// staged epilogue's working set in registers.
+// Register budget: the convolution flavours are capped at 96 registers (no spills) so that CTAs of other streams -
+// the fused all-reduce of csrc/runtime/p2p.cu above all - find room on the same SM next to this persistent kernel;
+// the GEMM flavour keeps the staged epilogue's working set in registers.
 template <int kMode, bool kBF16, int kCG>
 __global__ void __launch_bounds__(kNumThreads, 1) __maxnreg__(kMode == MODE_GEMM ? 168 : 96)
 tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const TcParams p) {

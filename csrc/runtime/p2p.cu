@@ -489,14 +489,14 @@ extern "C" int ddpx_p2p_allreduce_fused(int rank, int world, void* const* bufs, 
   if (ctas < 1) ctas = 1;
   if (ctas > 148) ctas = 148;
   cudaStream_t s = static_cast<cudaStream_t>(stream);
-  // 256 threads x ~100 registers leave room for a communication CTA NEXT TO a resident conv CTA (384 threads x <= 96
-  // registers, ~226 KB of shared memory): the all-reduce then starts at once and shares the SM with the mostly idle
-  // warp-specialised compute CTA instead of waiting for, or displacing, a persistent kernel.  DDPX_COMM_THREADS overrides.
+  // Block size: 512 threads measured best end to end (2 GPUs, VGG step: 512 x 64 CTAs 4.47 ms, 256 x 64 4.70 ms,
+  // 256 x 148 4.57 ms - bench/run_ddp_ab.sh); communication CTAs do run next to the persistent conv CTAs
+  // (bench/coresidency_probe.cu), so what matters is how quickly the kernel is gone again.  DDPX_COMM_THREADS overrides.
   static int threads = 0;
   if (threads == 0) {
     const char* e = getenv("DDPX_COMM_THREADS");
-    threads = e ? atoi(e) : 256;
-    if (threads < 64 || threads > 512 || threads % 32) threads = 256;
+    threads = e ? atoi(e) : 512;
+    if (threads < 64 || threads > 512 || threads % 32) threads = 512;
   }
   if (is_bf16) allreduce_fused_kernel<__nv_bfloat16><<<ctas, threads, 0, s>>>(P, gen, n, mode, h, tab);
   else allreduce_fused_kernel<float><<<ctas, threads, 0, s>>>(P, gen, n, mode, h, tab);

@@ -81,3 +81,39 @@ def gpt2_train_objs(size: str = "small", dtype=torch.bfloat16, lr: float = 3e-4,
     optimizer = torch.optim.AdamW(model.parameters(), lr=lr, betas=(0.9, 0.95), weight_decay=0.1)
     train_set = _data.SyntheticTokens(dataset_size, seq_len, cfg.vocab_size) if dataset_size else None
     return TrainObjs(train_set, model, optimizer, None, None)
+
+
+MODEL_CHOICES = ("vgg", "deepnn", "toy", "mlp", "gpt2", "gpt2-medium", "gpt2-large", "gpt2-xl")
+
+
+def make(name: str = "vgg", world_size: int = 1, synthetic: bool = False, synthetic_size: int = 50000,
+         dtype: Optional[str] = None, device: Optional[torch.device] = None, seq_len: int = 1024):
+    """``--model`` of the entrypoints -> (TrainObjs, loss_fn for ``Trainer``).  ``vgg`` is the reference workload
+    (multigpu.py:122-144); the others are the BASELINE.json configurations and the reference's dead-code DeepNN
+    (singlegpu.py:18-44).  ``dtype``: "fp32" | "bf16" (default: fp32 for the CNNs / toy, bf16 for MLP and GPT-2)."""
+    name = name.lower()
+    tdt = {None: None, "fp32": torch.float32, "bf16": torch.bfloat16}[dtype]
+    if name == "vgg":
+        return vgg_train_objs(world_size, synthetic, device, synthetic_size=synthetic_size), None
+    if name == "toy":
+        return toy_train_objs(device=device), "mse"
+    if name == "deepnn":
+        if device is None:
+            device = torch.device("cuda") if torch.cuda.is_available() else torch.device("cpu")
+        if synthetic:
+            train_set = _data.SyntheticImages(synthetic_size, seed=0) if synthetic_size else None
+            test_set = _data.SyntheticImages(min(10000, synthetic_size), seed=1) if synthetic_size else None
+        else:
+            train_set, test_set = _data.get_training_data("data/cifar10")
+        model = models.DeepNN().to(device)
+        optimizer = torch.optim.SGD(model.parameters(), lr=0.01, momentum=0.9)
+        return TrainObjs(train_set, model, optimizer, test_set, None), None
+    if name == "mlp":
+        return mlp_train_objs(dtype=tdt or torch.bfloat16, device=device, dataset_size=synthetic_size), None
+    if name.startswith("gpt2"):
+        size = {"gpt2": "small", "gpt2-medium": "medium", "gpt2-large": "large", "gpt2-xl": "xl"}[name]
+        o = gpt2_train_objs(size, dtype=tdt or torch.bfloat16, device=device, dataset_size=synthetic_size, seq_len=seq_len)
+        vocab = o.model.cfg.vocab_size
+        from .ops import functional as FX
+        return o, (lambda out, tgt: FX.cross_entropy_padded(out, tgt, vocab))
+    raise ValueError(f"unknown model {name!r}; choices: {MODEL_CHOICES}")

@@ -11,13 +11,14 @@ out).  Print lines, save cadence (``epoch % save_every == 0``, rank 0 only, ``ch
 """
 from __future__ import annotations
 
-from typing import Callable, Optional, Union
+from typing import Iterable, Callable, Optional, Union
 
 import torch
 import torch.distributed as dist
 
 from . import checkpoint, config, ops, optim as _optim
 from .parallel import DataParallel
+from .utils import debug as _debug, watchdog as _watchdog
 
 
 def _resolve_loss(loss_fn: Union[str, Callable, None]) -> Callable:
@@ -66,11 +67,32 @@ class Trainer:
             # multigpu.py:89 - wrap; the optimizer was built on the raw module's parameters and keeps working
             self.model = DataParallel(self.model, device_ids=[gpu_id] if self.device.type == "cuda" else None,
                                       optimizer=self.optimizer)
+        # failure detection / debug aids - all off unless their environment variable is set
+        self.global_step = 0
+        self._rank = dist.get_rank() if (dist.is_available() and dist.is_initialized()) else 0
+        self._fault = _watchdog.fault_plan_from_env()
+        self._watchdog = _watchdog.from_env(self._rank, self._describe_state)
+        self._checksum = _debug.checksum_enabled()
+
+    def _describe_state(self) -> str:
+        parts = [f"global step {self.global_step}"]
+        red = getattr(self.model, "reducer", None)
+        if red is not None:
+            parts.append(f"reducer iteration {red.iteration}, buckets launched {red.stats['launched']}, "
+                         f"parameters without gradient {red._unmarked() if red.expect_finalize else []}")
+        comm = getattr(self.model, "comm", None)
+        if comm is not None and hasattr(comm, "error_word"):
+            parts.append(f"device error word {comm.error_word():#x}")
+        return "; ".join(parts)
 
     # ------------------------------------------------------------------------------------------ one step
     def _run_batch(self, source, targets):
         """zero_grad -> forward -> loss -> backward -> optimizer.step -> scheduler.step (multigpu.py:92-98), with
         optional gradient accumulation over ``accum_steps`` micro-batches under ``no_sync``."""
+        if self._fault is not None:
+            self._fault.maybe_fire(self._rank, self.global_step)
+        if self._watchdog is not None:
+            self._watchdog.beat(f"step {self.global_step} begins")
         last = (self._micro + 1) % self.accum_steps == 0
         if self._micro % self.accum_steps == 0:
             self.optimizer.zero_grad()
@@ -81,19 +103,25 @@ class Trainer:
             loss = self._forward_backward(source, targets)
         self._micro += 1
         if last:
-            self.optimizer.step()
+            with _debug.nvtx_range("optimizer"):
+                self.optimizer.step()
             if self.scheduler is not None:
                 self.scheduler.step()
+            if self._checksum:
+                _debug.assert_replicas_in_sync(self.model.parameters(), getattr(self.model, "comm", None), self.global_step)
+        self.global_step += 1
         self.last_loss = loss
         return loss
 
     def _forward_backward(self, source, targets):
-        output = self.model(source)
-        loss = self.loss_fn(output, targets)
-        if self.accum_steps > 1:
-            (loss / self.accum_steps).backward()
-        else:
-            loss.backward()
+        with _debug.nvtx_range("forward"):
+            output = self.model(source)
+            loss = self.loss_fn(output, targets)
+        with _debug.nvtx_range("backward"):
+            if self.accum_steps > 1:
+                (loss / self.accum_steps).backward()
+            else:
+                loss.backward()
         return loss.detach()
 
     def train_step(self, source: torch.Tensor, targets: torch.Tensor) -> float:
@@ -102,6 +130,64 @@ class Trainer:
         targets = targets.to(self.device, non_blocking=True)
         loss = self._run_batch(source, targets)
         return float(loss.item())
+
+    def train_stream(self, batches: Iterable):
+        """Pipelined end-to-end loop over host batches ``(source, targets)``; yields one host-side loss per batch, in order.
+
+        While step *i* computes, batch *i+1* is uploaded on a copy stream (pinned memory makes that a true DMA) and the
+        loss of step *i-1* is read back, so neither the PCIe copy nor the read-back sits between two steps' kernels.
+        Every batch is still copied and every loss still read - only the order of the host's waits changes.
+        CPU runs degrade to the plain loop."""
+        if self.device.type != "cuda":
+            for source, targets in batches:
+                yield self.train_step(source, targets)
+            return
+        compute = torch.cuda.current_stream(self.device)
+        copy = getattr(self, "_copy_stream", None)
+        if copy is None:
+            copy = self._copy_stream = torch.cuda.Stream(self.device)
+
+        def upload(batch):
+            ev = torch.cuda.Event()
+            with torch.cuda.stream(copy):       # buffers are allocated on the copy stream; record_stream() below keeps
+                src = batch[0].to(self.device, non_blocking=True)   # the allocator from reusing them under the step
+                tgt = batch[1].to(self.device, non_blocking=True)
+                ev.record(copy)
+            return src, tgt, ev
+
+        it = iter(batches)
+        try:
+            nxt = upload(next(it))
+        except StopIteration:
+            return
+        # losses land in pinned host slots by async copies; the host waits on the slot's own event, i.e. for step i-1
+        # only, never for the step it has just enqueued
+        slots = getattr(self, "_loss_slots", None)
+        if slots is None:
+            slots = self._loss_slots = [torch.empty((), dtype=torch.float32).pin_memory() for _ in range(2)]
+        prev = None                                   # (slot, event) of the previous step
+        i = 0
+        while nxt is not None:
+            src, tgt, ready = nxt
+            compute.wait_event(ready)
+            src.record_stream(compute); tgt.record_stream(compute)
+            loss = self._run_batch(src, tgt)
+            slot = slots[i & 1]
+            slot.copy_(loss.detach().float().reshape(()), non_blocking=True)
+            ev = torch.cuda.Event()
+            ev.record(compute)
+            try:
+                nxt = upload(next(it))
+            except StopIteration:
+                nxt = None
+            if prev is not None:
+                prev[1].synchronize()
+                yield float(prev[0])
+            prev = (slot, ev)
+            i += 1
+        if prev is not None:
+            prev[1].synchronize()
+            yield float(prev[0])
 
     # ------------------------------------------------------------------------------------------ epochs
     def _run_epoch(self, epoch):
@@ -122,7 +208,11 @@ class Trainer:
 
     def train(self, max_epochs: int):
         for epoch in range(max_epochs):
+            if self._watchdog is not None:
+                self._watchdog.resume()
             self._run_epoch(epoch)
+            if self._watchdog is not None:
+                self._watchdog.pause()          # checkpoint writes and whatever the caller does next are not hangs
             # multigpu.py:118 gates on gpu_id == 0 (rank 0); singlegpu.py:127 saves unconditionally
             if (not self.distributed or self.gpu_id == 0) and epoch % self.save_every == 0:
                 self._save_checkpoint(epoch)

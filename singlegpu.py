@@ -15,11 +15,12 @@ from distributed_data_parallel_experiment_b200.models import VGG, DeepNN  # noqa
 
 def load_train_objs(opts=None):
     opts = opts or {}
-    if opts.get("model") == "toy":
-        o = ddpx.recipes.toy_train_objs(device=torch.device("cuda") if torch.cuda.is_available() else None)
-    else:
-        o = ddpx.recipes.vgg_train_objs(world_size=1, synthetic=bool(opts.get("synthetic", False)),
-                                        synthetic_size=int(opts.get("synthetic_size", 50000)))
+    name = opts.get("model", "vgg")
+    o, loss_fn = ddpx.recipes.make(name, world_size=1, synthetic=bool(opts.get("synthetic", False)),
+                                   synthetic_size=int(opts.get("synthetic_size", 50000)), dtype=opts.get("dtype"),
+                                   device=(torch.device("cuda") if torch.cuda.is_available() else None) if name == "toy" else None,
+                                   seq_len=int(opts.get("seq_len", 1024)))
+    opts["_loss_fn"] = loss_fn
     return o.train_set, o.model, o.optimizer, o.test_set, o.scheduler
 
 
@@ -28,7 +29,7 @@ def main(device, total_epochs, save_every, batch_size, opts=None):
     dataset, model, optimizer, testdata, scheduler = load_train_objs(opts)
     train_data = prepare_dataloader(dataset, batch_size, distributed=False)
     trainer = Trainer(model, train_data, optimizer, device, save_every, scheduler=scheduler, distributed=False,
-                      loss_fn="mse" if opts.get("model") == "toy" else None)
+                      loss_fn=opts.get("_loss_fn"), accum_steps=int(opts.get("accum_steps", 1)))
 
     start_time = time.time()
     trainer.train(total_epochs)
@@ -52,11 +53,15 @@ if __name__ == "__main__":
     parser.add_argument('total_epochs', type=int, help='Total epochs to train the model')
     parser.add_argument('save_every', type=int, help='How often to save a snapshot')
     parser.add_argument('--batch_size', default=512, type=int, help='Input batch size on each device (default: 32)')
-    parser.add_argument('--model', default='vgg', choices=['vgg', 'toy'], help='extra: model to train')
+    parser.add_argument('--model', default='vgg', choices=list(ddpx.recipes.MODEL_CHOICES), help='extra: model to train')
+    parser.add_argument('--dtype', default=None, choices=[None, 'fp32', 'bf16'], help='extra: parameter dtype (MLP / GPT-2)')
+    parser.add_argument('--seq-len', dest='seq_len', default=1024, type=int, help='extra: GPT-2 sequence length')
+    parser.add_argument('--accum-steps', dest='accum_steps', default=1, type=int, help='extra: micro-batches per optimizer step')
     parser.add_argument('--synthetic', action='store_true', help='extra: CIFAR-shaped random data (no download)')
     parser.add_argument('--synthetic_size', default=50000, type=int)
     args = parser.parse_args()
 
     device = 0  # shorthand for cuda:0
     main(device, args.total_epochs, args.save_every, args.batch_size,
-         {"model": args.model, "synthetic": args.synthetic, "synthetic_size": args.synthetic_size})
+         {"model": args.model, "synthetic": args.synthetic, "synthetic_size": args.synthetic_size, "dtype": args.dtype,
+          "seq_len": args.seq_len, "accum_steps": args.accum_steps})
