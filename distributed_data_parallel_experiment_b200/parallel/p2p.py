@@ -72,6 +72,7 @@ class P2PComm(CommBase):
         self._by_ptr = {}
         if self.world_size > 8:
             raise RuntimeError("P2PComm supports up to 8 ranks (one NVSwitch domain)")
+        self.store = self._open_store()
         self.pad = self._sym_alloc(4096)
         self.slot_bytes = staging_mb * 1024 * 1024
         self.staging = self._sym_alloc(2 * self.slot_bytes)
@@ -81,6 +82,43 @@ class P2PComm(CommBase):
         self.ctas = int(self.cfg.comm_ctas)
         self._pads_arr = _cvoidp_array(self.pad.ptrs)
         self.barrier()
+
+    # ------------------------------------------------------------------------------------------ control plane
+    def _open_store(self):
+        """Native TCP store (csrc/runtime/store.cpp) hosted by rank 0 for every host-side exchange of this backend:
+        CUDA-IPC handles, bucket orders, barriers.  torch's process group is used once, to tell the peers the port.
+        ``DDPX_NATIVE_STORE=0`` keeps everything on torch.distributed object collectives."""
+        import os
+        if self.world_size == 1 or os.environ.get("DDPX_NATIVE_STORE", "1") in ("0", ""):
+            return None
+        from .store import NativeStore
+        host = os.environ.get("MASTER_ADDR", "127.0.0.1")
+        if host == "localhost":
+            host = "127.0.0.1"
+        timeout = max(30.0, float(self.cfg.wait_timeout_s))
+        if self.rank == 0:
+            st = NativeStore(host, 0, 0, self.world_size, timeout_s=timeout, is_server=True)
+            super().broadcast_object(st.port, src=0)
+            return st
+        port = super().broadcast_object(None, src=0)
+        return NativeStore(host, int(port), self.rank, self.world_size, timeout_s=timeout, is_server=False)
+
+    def all_gather_object(self, obj):
+        if self.store is not None:
+            return self.store.all_gather_object(obj)
+        return super().all_gather_object(obj)
+
+    def broadcast_object(self, obj, src: int = 0):
+        if self.store is not None:
+            return self.store.broadcast_object(obj, src=src)
+        return super().broadcast_object(obj, src=src)
+
+    def barrier(self):
+        if self.store is not None:
+            torch.cuda.synchronize(self.device)          # a host barrier after the device work it is meant to fence
+            self.store.barrier()
+        else:
+            super().barrier()
 
     # ------------------------------------------------------------------------------------------ symmetric memory
     def _sym_alloc(self, nbytes: int) -> SymBuf:
@@ -230,6 +268,9 @@ class P2PComm(CommBase):
             self.lib.ddpx_p2p_free(ctypes.c_void_p(sb.local))
         self._bufs = []
         self._by_ptr = {}
+        if getattr(self, "store", None) is not None:
+            self.store.close()
+            self.store = None
 
 
 class FusedUpdate:

@@ -186,6 +186,19 @@ int ddpx_p2p_broadcast(int rank, int world, void* const* pads, int src, unsigned
 /* ---- reducer core (csrc/runtime/reducer_core.cpp): host-side bucket assignment + ready/launch state machine ----
  * Counterpart of c10d::compute_bucket_assignment_by_size and the bookkeeping of c10d::Reducer that torch DDP builds
  * for the reference at M:89. */
+/* ---- control-plane store (csrc/runtime/store.cpp): TCP key-value store hosted by rank 0; the bootstrap exchanges CUDA-IPC
+ * handles, bucket orders and barriers through it.  Status < 0: -1 missing key / timeout, -2 connection, <= -16 buffer too
+ * small (-16 - needed).  Stands where c10d::TCPStore stands for the reference (multigpu.py:30-32). */
+void* ddpx_store_server_start(int port, int* bound_port);       /* port 0 = pick one */
+void ddpx_store_server_stop(void* server);
+void* ddpx_store_connect(const char* host, int port, int timeout_ms);
+void ddpx_store_close(void* client);
+long long ddpx_store_set(void* client, const char* key, const void* data, long long len);
+long long ddpx_store_get(void* client, const char* key, void* buf, long long cap, int timeout_ms);
+long long ddpx_store_add(void* client, const char* key, long long delta);
+long long ddpx_store_delete(void* client, const char* key);
+long long ddpx_store_num_keys(void* client);
+
 int ddpx_bucket_assign(int n, const long long* nbytes, const int* keys, int nlimits, const long long* limits,
                        int sort_by_min_position, int* out_bucket_of_position, long long* out_bucket_limit,
                        int* out_num_buckets);
