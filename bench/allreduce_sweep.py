@@ -55,6 +55,29 @@ def worker(rank, world, port, args):
             algbw = size / ms / 1e6
             results.append({"impl": "p2p_twoshot", "ctas": ctas, "bytes": size, "us": ms * 1e3, "algbw_gbs": algbw,
                             "busbw_gbs": algbw * 2 * (world - 1) / world})
+        if args.fused and size <= (64 << 20):
+            # the product path: all-reduce + 1/world + SGD-momentum in ONE kernel (two-shot / one-shot) against the
+            # baseline pair NCCL all-reduce + torch's fused SGD step on a parameter of the same size
+            prm = torch.zeros(n, dtype=dtype, device="cuda"); mom = torch.zeros(n, dtype=dtype, device="cuda")
+            slots = ([prm.data_ptr()], [mom.data_ptr()], [0], [0], [n])
+            hyper = [1e-3, 0.9, 0.0, 5e-4, 0.0, 0.0, 0.0, 1.0, 1.0]
+            comm.ctas = args.ctas[-1]
+            for mode, label in ((0, "p2p_twoshot+sgd"), (1, "p2p_oneshot+sgd")):
+                if mode == 1 and size > (16 << 20):
+                    continue
+                ms = _time(lambda: comm.launch_allreduce(buf, mode=mode, opt=1, hyper=hyper, slots=slots).wait(), iters, world)
+                results.append({"impl": label, "ctas": comm.ctas, "bytes": size, "us": ms * 1e3, "algbw_gbs": size / ms / 1e6,
+                                "busbw_gbs": size / ms / 1e6 * 2 * (world - 1) / world})
+            tp = torch.nn.Parameter(torch.zeros(n, dtype=dtype, device="cuda")); tp.grad = ref
+            topt = torch.optim.SGD([tp], lr=1e-3, momentum=0.9, weight_decay=5e-4, fused=True)
+
+            def base_step():
+                dist.all_reduce(ref)
+                topt.step()
+            ms = _time(base_step, iters, world)
+            results.append({"impl": "nccl+torch_fused_sgd", "ctas": None, "bytes": size, "us": ms * 1e3,
+                            "algbw_gbs": size / ms / 1e6, "busbw_gbs": size / ms / 1e6 * 2 * (world - 1) / world})
+            del prm, mom, tp, topt
         ms = _time(lambda: dist.all_reduce(ref), iters, world)
         algbw = size / ms / 1e6
         results.append({"impl": "nccl", "ctas": None, "bytes": size, "us": ms * 1e3, "algbw_gbs": algbw,
@@ -72,7 +95,8 @@ def main():
     ap.add_argument("--gpus", type=int, default=2)
     ap.add_argument("--max-mb", type=int, default=1024)
     ap.add_argument("--dtype", default="fp32")
-    ap.add_argument("--ctas", default="32")
+    ap.add_argument("--ctas", default="64")
+    ap.add_argument("--fused", action="store_true", help="also time all-reduce+SGD in one kernel vs NCCL + torch fused SGD")
     args = ap.parse_args()
     args.ctas = [int(c) for c in args.ctas.split(",")]
     import socket

@@ -23,6 +23,15 @@ from .. import _lib, config
 from .comm import CommBase
 
 ONESHOT_MAX_BYTES = 256 * 1024
+# Algorithm selection ("auto"): largest bucket for which the one-shot kernel (every rank reduces the whole bucket from peer
+# memory and updates its replica; one barrier less) beats two-shot, per world size.  From the measured fused sweep
+# (bench/allreduce_sweep.py --fused, profiles/raw/sweep_*): 2 GPUs - one-shot+SGD 24.4 us vs two-shot+SGD 24.5 us at 1 MB,
+# 34.7 vs 26.6 us at 4 MB; one-shot traffic grows with the world size, so the threshold shrinks with it.
+ONESHOT_MAX_BYTES_BY_WORLD = {1: 1 << 20, 2: 1 << 20, 3: 512 << 10, 4: 512 << 10}
+
+
+def oneshot_max_bytes(world_size: int) -> int:
+    return ONESHOT_MAX_BYTES_BY_WORLD.get(world_size, ONESHOT_MAX_BYTES)
 _MAX_SLOTS = 128
 
 
@@ -364,7 +373,8 @@ class FusedUpdate:
             self._unfused = True
             return self.comm.launch_allreduce(buf, mode=0, opt=0)
         group = self.group_of[id(self.params[bucket.param_ids[0]])]
-        small = bucket.numel * buf.element_size() <= ONESHOT_MAX_BYTES and self.comm.cfg.allreduce_algo in ("auto", "oneshot")
+        small = (bucket.numel * buf.element_size() <= oneshot_max_bytes(self.comm.world_size)
+                 and self.comm.cfg.allreduce_algo in ("auto", "oneshot"))
         mode = 1 if (small or self.comm.cfg.allreduce_algo == "oneshot") else 0
         if self.comm.cfg.allreduce_algo == "twoshot":
             mode = 0
