@@ -59,6 +59,7 @@ struct TcParams {
   int out_bf16;
   int atomic;               // 1 = accumulate with red.global.add.f32 (split-K / wgrad)
   float alpha;              // GEMM: D = act(alpha * A*B + bias)
+  int a_big, b_big;         // GEMM: MN-major operand map carries the 128-byte chunk index as a 5th dimension (one TMA per tile)
   int big_box;              // WGRAD: operand maps have the 32-channel chunk as outermost dim (one TMA per tile)
   int st_vec;               // GEMM: output rows are 16-byte aligned -> epilogue stages 32x32 chunks through shared
                             // memory and stores whole 64/128-byte row segments (coalesced) instead of 16 B per lane
@@ -204,14 +205,23 @@ tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
           if (leader) mbar_arrive_expect_tx(&full_bar[stage], tx_bytes);
           if constexpr (kMode == MODE_GEMM) {
             const int k0 = (kbeg + i) * kBK;
+            // MN-major operands: the tile is kBlockM/kChunk (or bn_local/kChunk) swizzle tiles of [kBK rows][128 B].  With
+            // the chunk index as an extra tensor-map dimension ONE instruction fetches them all; every TMA instruction
+            // costs the single producer thread ~100 cycles (profiles/probe_findings.md)
             if (!p.a_mn) {
               ld4(sa, &tmA, &full_bar[stage], k0, m0, b1, b2);
+            } else if (p.a_big) {
+              if constexpr (kCG == 2) tma_load_5d_2sm(sa, &tmA, &full_bar[stage], 0, k0, m0 / kChunk, b1, b2);
+              else tma_load_5d(sa, &tmA, &full_bar[stage], 0, k0, m0 / kChunk, b1, b2);
             } else {
               for (int j = 0; j < kBlockM / kChunk; ++j)
                 ld4(sa + j * (kBK * 128), &tmA, &full_bar[stage], m0 + j * kChunk, k0, b1, b2);
             }
             if (!p.b_mn) {
               ld4(sb, &tmB, &full_bar[stage], k0, n0, b1, b2);
+            } else if (p.b_big) {
+              if constexpr (kCG == 2) tma_load_5d_2sm(sb, &tmB, &full_bar[stage], 0, k0, n0 / kChunk, b1, b2);
+              else tma_load_5d(sb, &tmB, &full_bar[stage], 0, k0, n0 / kChunk, b1, b2);
             } else {
               for (int j = 0; j < bn_local / kChunk; ++j)
                 ld4(sb + j * (kBK * 128), &tmB, &full_bar[stage], n0 + j * kChunk, k0, b1, b2);
@@ -651,18 +661,34 @@ extern "C" int ddpx_gemm_batched(const void* A, const void* B, void* D, int M, i
   {
     uint64_t dims[4], str[3]; uint32_t box[4];
     dims[2] = batch1; dims[3] = batch2; box[2] = 1; box[3] = 1;
+    static int gemm_big = -1;      // DDPX_GEMM_BIGBOX=0: one TMA per 128-byte chunk (the older path), for A/B runs
+    if (gemm_big < 0) { const char* e = getenv("DDPX_GEMM_BIGBOX"); gemm_big = (e && e[0] == '0') ? 0 : 1; }
+    // chunked 5-D view of an MN-major operand: (chunk elements, K rows, chunks, batch1, batch2); whole chunks only
+    auto big_map = [&](CUtensorMap* tm, const void* base, int MN, long long ld, long long bs1, long long bs2, int tile_rows) {
+      uint64_t d5[5] = {static_cast<uint64_t>(chunk), static_cast<uint64_t>(K), static_cast<uint64_t>(MN / chunk),
+                        static_cast<uint64_t>(batch1), static_cast<uint64_t>(batch2)};
+      uint64_t s5[4] = {static_cast<uint64_t>(ld) * elt, 128,
+                        batch1 > 1 ? static_cast<uint64_t>(bs1) * elt : static_cast<uint64_t>(ld) * elt * K,
+                        batch2 > 1 ? static_cast<uint64_t>(bs2) * elt : static_cast<uint64_t>(ld) * elt * K * batch1};
+      uint32_t b5[5] = {static_cast<uint32_t>(chunk), static_cast<uint32_t>(bk), static_cast<uint32_t>(tile_rows / chunk), 1, 1};
+      return make_tmap(tm, base, bf16, 5, d5, s5, b5, !bf16);
+    };
+    p.a_big = (gemm_big && a_mn && M % chunk == 0) ? 1 : 0;
+    p.b_big = (gemm_big && b_mn && N % chunk == 0 && (bn / cg) % chunk == 0) ? 1 : 0;
     if (!a_mn) { dims[0] = K; dims[1] = M; box[0] = bk; box[1] = kBlockM; }
     else       { dims[0] = M; dims[1] = K; box[0] = chunk; box[1] = bk; }
     str[0] = static_cast<uint64_t>(lda) * elt;
     str[1] = batch1 > 1 ? static_cast<uint64_t>(a_bs1) * elt : str[0] * dims[1];
     str[2] = batch2 > 1 ? static_cast<uint64_t>(a_bs2) * elt : str[1] * dims[2];
-    if ((rc = make_tmap(&ta, A, bf16, 4, dims, str, box, a_mn && !bf16)) != DDPX_OK) return rc;
+    if (p.a_big && big_map(&ta, A, M, lda, a_bs1, a_bs2, kBlockM) != DDPX_OK) p.a_big = 0;
+    if (!p.a_big && (rc = make_tmap(&ta, A, bf16, 4, dims, str, box, a_mn && !bf16)) != DDPX_OK) return rc;
     if (!b_mn) { dims[0] = K; dims[1] = N; box[0] = bk; box[1] = bn / cg; }
     else       { dims[0] = N; dims[1] = K; box[0] = chunk; box[1] = bk; }
     str[0] = static_cast<uint64_t>(ldb) * elt;
     str[1] = batch1 > 1 ? static_cast<uint64_t>(b_bs1) * elt : str[0] * dims[1];
     str[2] = batch2 > 1 ? static_cast<uint64_t>(b_bs2) * elt : str[1] * dims[2];
-    if ((rc = make_tmap(&tb, B, bf16, 4, dims, str, box, b_mn && !bf16)) != DDPX_OK) return rc;
+    if (p.b_big && big_map(&tb, B, N, ldb, b_bs1, b_bs2, bn / cg) != DDPX_OK) p.b_big = 0;
+    if (!p.b_big && (rc = make_tmap(&tb, B, bf16, 4, dims, str, box, b_mn && !bf16)) != DDPX_OK) return rc;
   }
   return bf16 ? launch_tc<MODE_GEMM, true>(ta, tb, p, stream, cg) : launch_tc<MODE_GEMM, false>(ta, tb, p, stream, cg);
 }
