@@ -53,7 +53,7 @@ def worker(rank, world, port, args):
             comm.ctas = ctas
             ms = _time(lambda: comm.all_reduce_sum_(buf, async_op=False), iters, world)
             algbw = size / ms / 1e6
-            results.append({"impl": "p2p_twoshot", "ctas": ctas, "bytes": size, "us": ms * 1e3, "algbw_gbs": algbw,
+            results.append({"impl": "p2p_nvls" if getattr(comm, "nvls", None) is not None else "p2p_twoshot", "ctas": ctas, "bytes": size, "us": ms * 1e3, "algbw_gbs": algbw,
                             "busbw_gbs": algbw * 2 * (world - 1) / world})
         if args.fused and size <= (64 << 20):
             # the product path: all-reduce + 1/world + SGD-momentum in ONE kernel (two-shot / one-shot) against the

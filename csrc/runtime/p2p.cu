@@ -63,6 +63,7 @@ struct Peers {
   void* buf[kMaxRanks];        // every rank's copy of the symmetric buffer, indexed by rank (buf[rank] is local)
   uint32_t* pad[kMaxRanks];    // every rank's signal pad
   int rank, world;
+  void* mc;                    // NVLS: multicast mapping of the same symmetric buffer (nullptr = none)
 };
 
 struct Slot {
@@ -307,6 +308,51 @@ __device__ __forceinline__ void reduce_shard(const Peers& P, long long v0, long 
   }
 }
 
+// NVLS flavour of step 2 (mode 2): the shard is reduced INSIDE the NVSwitch - one multimem.ld_reduce on the multicast
+// address returns the sum over all ranks' buckets - and one multimem.st writes the result into every rank's bucket.
+// Per-direction traffic is ~S/world in and S/world out per rank instead of (world-1)/world * S each way.
+template <typename T>
+__device__ __forceinline__ void reduce_shard_nvls(const Peers& P, long long v0, long long v1) {
+  constexpr int kU = 8;      // multimem.ld_reduce round trips go through the switch: keep 8 of them in flight per thread
+  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+  uint4* mc = reinterpret_cast<uint4*>(P.mc);
+  for (long long i0 = v0 + static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i0 < v1; i0 += stride * kU) {
+    uint4 v[kU];
+#pragma unroll
+    for (int u = 0; u < kU; ++u) {
+      const long long i = i0 + u * stride;
+      if (i < v1) {
+        if constexpr (sizeof(T) == 4) {
+          asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0,%1,%2,%3}, [%4];"
+                       : "=r"(v[u].x), "=r"(v[u].y), "=r"(v[u].z), "=r"(v[u].w)
+                       : "l"(mc + i)
+                       : "memory");
+        } else {
+          asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v4.bf16x2 {%0,%1,%2,%3}, [%4];"
+                       : "=r"(v[u].x), "=r"(v[u].y), "=r"(v[u].z), "=r"(v[u].w)
+                       : "l"(mc + i)
+                       : "memory");
+        }
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < kU; ++u) {
+      const long long i = i0 + u * stride;
+      if (i < v1) {
+        if constexpr (sizeof(T) == 4) {
+          asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(mc + i), "r"(v[u].x), "r"(v[u].y),
+                       "r"(v[u].z), "r"(v[u].w)
+                       : "memory");
+        } else {
+          asm volatile("multimem.st.relaxed.sys.global.v4.bf16x2 [%0], {%1,%2,%3,%4};" ::"l"(mc + i), "r"(v[u].x),
+                       "r"(v[u].y), "r"(v[u].z), "r"(v[u].w)
+                       : "memory");
+        }
+      }
+    }
+  }
+}
+
 // ------------------------------------------------------------------------------------------------
 // fused all-reduce (+ optimizer).  n = bucket elements (multiple of the vector width).
 // mode 0 = two-shot, mode 1 = one-shot (requires opt != 0: the local bucket is not rewritten)
@@ -323,14 +369,15 @@ allreduce_fused_kernel(const Peers P, const uint32_t gen, const long long n, con
   if (threadIdx.x < P.world) wait_flag(pad + PAD_ARRIVE + threadIdx.x, gen, pad, 0xA1000000u | threadIdx.x);
   __syncthreads();
 
-  if (mode == 0) {
+  if (mode == 0 || mode == 2) {
     // ---- 2. reduce my shard from every rank's bucket (fixed rank order => identical bits everywhere),
     //         store it into every rank's bucket
     const long long per = (nvec + P.world - 1) / P.world;
     const long long v0 = per * P.rank, v1 = min(v0 + per, nvec);
     // U vectors per thread per trip, all peer loads issued before the first add: the ~2 us NVLink load latency needs
     // tens of 16-byte requests in flight per thread to reach link bandwidth
-    if (P.world <= 2) reduce_shard<T, 2, 8>(P, v0, v1);
+    if (mode == 2) reduce_shard_nvls<T>(P, v0, v1);
+    else if (P.world <= 2) reduce_shard<T, 2, 8>(P, v0, v1);
     else if (P.world <= 4) reduce_shard<T, 4, 4>(P, v0, v1);
     else reduce_shard<T, kMaxRanks, 2>(P, v0, v1);
     // ---- 3. when the whole grid is done with the shard, tell every peer
@@ -456,16 +503,17 @@ extern "C" unsigned int ddpx_p2p_read_error(void* pad) {
 // ---- collectives -----------------------------------------------------------------------------------
 // slots: arrays of length nslots (param / state0 / state1 pointers, element offsets, element counts); may be 0 slots
 // when opt == 0.  hyper: [lr, momentum, dampening, wd, beta1, beta2, eps, bc1, bc2_sqrt].
-extern "C" int ddpx_p2p_allreduce_fused(int rank, int world, void* const* bufs, void* const* pads, unsigned int gen,
-                                        long long n, int is_bf16, int mode, int opt, const float* hyper, int nesterov,
-                                        int first_step, int nslots, void* const* params, void* const* state0,
-                                        void* const* state1, const long long* offsets, const long long* numels, int ctas,
-                                        void* stream) {
+static int allreduce_impl(int rank, int world, void* const* bufs, void* const* pads, unsigned int gen, long long n,
+                          int is_bf16, int mode, int opt, const float* hyper, int nesterov, int first_step, int nslots,
+                          void* const* params, void* const* state0, void* const* state1, const long long* offsets,
+                          const long long* numels, int ctas, void* stream, void* mc) {
   Peers P;
   int rc = fill_peers(P, rank, world, bufs, pads);
   if (rc != DDPX_OK) return rc;
+  P.mc = mc;
   if (nslots > kMaxSlots) return DDPX_ERR_LIMIT;
   if (mode == 1 && opt == 0) return DDPX_ERR_ARG;
+  if (mode == 2 && mc == nullptr) return DDPX_ERR_ARG;
   const int vec = is_bf16 ? 8 : 4;
   if (n % vec) return DDPX_ERR_ALIGN;
   static SlotTable tab;   // filled per call; passed by value
@@ -501,6 +549,27 @@ extern "C" int ddpx_p2p_allreduce_fused(int rank, int world, void* const* bufs, 
   if (is_bf16) allreduce_fused_kernel<__nv_bfloat16><<<ctas, threads, 0, s>>>(P, gen, n, mode, h, tab);
   else allreduce_fused_kernel<float><<<ctas, threads, 0, s>>>(P, gen, n, mode, h, tab);
   return CUDA_OK(cudaGetLastError());
+}
+
+extern "C" int ddpx_p2p_allreduce_fused(int rank, int world, void* const* bufs, void* const* pads, unsigned int gen,
+                                        long long n, int is_bf16, int mode, int opt, const float* hyper, int nesterov,
+                                        int first_step, int nslots, void* const* params, void* const* state0,
+                                        void* const* state1, const long long* offsets, const long long* numels, int ctas,
+                                        void* stream) {
+  if (mode == 2) return DDPX_ERR_ARG;      // NVLS needs the multicast mapping: ddpx_p2p_allreduce_nvls
+  return allreduce_impl(rank, world, bufs, pads, gen, n, is_bf16, mode, opt, hyper, nesterov, first_step, nslots, params,
+                        state0, state1, offsets, numels, ctas, stream, nullptr);
+}
+
+// NVLS all-reduce (+ optimizer): as two-shot, but the shard is reduced in the NVSwitch through `mc_buf`, the multicast
+// mapping of the same symmetric buffer (parallel/nvls.py builds it with cuMulticastCreate / cuMulticastBindMem).
+extern "C" int ddpx_p2p_allreduce_nvls(int rank, int world, void* const* bufs, void* mc_buf, void* const* pads,
+                                       unsigned int gen, long long n, int is_bf16, int opt, const float* hyper, int nesterov,
+                                       int first_step, int nslots, void* const* params, void* const* state0,
+                                       void* const* state1, const long long* offsets, const long long* numels, int ctas,
+                                       void* stream) {
+  return allreduce_impl(rank, world, bufs, pads, gen, n, is_bf16, 2, opt, hyper, nesterov, first_step, nslots, params,
+                        state0, state1, offsets, numels, ctas, stream, mc_buf);
 }
 
 // broadcast one chunk: `ptrs[i]` (bytes[i] long) <-> staging offset offs[i].  is_src selects the role.

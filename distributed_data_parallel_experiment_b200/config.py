@@ -23,7 +23,7 @@ class RuntimeConfig:
     master_addr: str = "localhost"      # multigpu.py:30
     master_port: int = 12355            # multigpu.py:31
     backend: str = "auto"               # auto | p2p | nccl | gloo
-    allreduce_algo: str = "auto"        # auto | oneshot | twoshot | nccl
+    allreduce_algo: str = "auto"        # auto | oneshot | twoshot | nvls | nccl
     bucket_cap_mb: float = 25.0         # torch DDP default (distributed.py:831-833)
     first_bucket_mb: float = 1.0
     comm_ctas: int = 64                 # CTAs of a communication kernel (64 x 512 threads measured best, 2 and 8 GPUs)

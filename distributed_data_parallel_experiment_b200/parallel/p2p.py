@@ -44,10 +44,11 @@ class _RawCuda:
 
 
 class SymBuf:
-    __slots__ = ("local", "ptrs", "nbytes", "tensor")
+    __slots__ = ("local", "ptrs", "nbytes", "tensor", "mc_ptr")
 
     def __init__(self, local, ptrs, nbytes, tensor):
         self.local, self.ptrs, self.nbytes, self.tensor = local, ptrs, nbytes, tensor
+        self.mc_ptr = 0          # NVLS: multicast mapping of the same buffer (parallel/nvls.py), 0 = none
 
 
 class _EventHandle:
@@ -82,6 +83,7 @@ class P2PComm(CommBase):
         if self.world_size > 8:
             raise RuntimeError("P2PComm supports up to 8 ranks (one NVSwitch domain)")
         self.store = self._open_store()
+        self.nvls = self._open_nvls()
         self.pad = self._sym_alloc(4096)
         self.slot_bytes = staging_mb * 1024 * 1024
         self.staging = self._sym_alloc(2 * self.slot_bytes)
@@ -111,6 +113,21 @@ class P2PComm(CommBase):
             return st
         port = super().broadcast_object(None, src=0)
         return NativeStore(host, int(port), self.rank, self.world_size, timeout_s=timeout, is_server=False)
+
+    def _open_nvls(self):
+        """``allreduce_algo = nvls``: gradient buckets come from the VMM / multicast allocator (parallel/nvls.py) and the
+        shard reduction of the all-reduce kernel runs in the NVSwitch.  Needs multicast support on every rank; otherwise
+        the backend says so once and stays on the two-shot path."""
+        if self.cfg.allreduce_algo != "nvls" or self.world_size == 1 or self.store is None:
+            return None
+        from . import nvls
+        ok = nvls.supported(self.device.index)
+        if not all(self.all_gather_object(bool(ok))):
+            if self.rank == 0:
+                print("[ddpx] NVLS multicast is not available on every rank: using the two-shot all-reduce")
+            return None
+        torch.zeros(1, device=self.device)                  # the primary context must exist before driver-API calls
+        return nvls.NvlsAllocator(self.rank, self.world_size, self.device.index, self)
 
     def all_gather_object(self, obj):
         if self.store is not None:
@@ -156,6 +173,13 @@ class P2PComm(CommBase):
     def alloc(self, numel: int, dtype: torch.dtype, device=None) -> torch.Tensor:
         """Collective: every rank must call with the same sizes in the same order."""
         es = torch.empty((), dtype=dtype).element_size()
+        if self.nvls is not None:
+            nb = self.nvls.alloc(numel * es)
+            sb = SymBuf(nb.local, nb.ptrs, nb.nbytes, nb.tensor)
+            sb.mc_ptr = nb.mc_ptr
+            self._nvls_bufs = getattr(self, "_nvls_bufs", []) + [sb]
+            self._by_ptr[nb.local] = sb
+            return sb.tensor[: numel * es].view(dtype)
         sb = self._sym_alloc(numel * es)
         return sb.tensor[: numel * es].view(dtype)
 
@@ -188,13 +212,22 @@ class P2PComm(CommBase):
         else:
             params = s0 = s1 = offs = nums = None
             ns = 0
-        rc = self.lib.ddpx_p2p_allreduce_fused(
-            self.rank, self.world_size, _cvoidp_array(sb.ptrs), self._pads_arr, ctypes.c_uint(gen), ctypes.c_longlong(n),
-            is_bf16, mode, opt, hy, int(nesterov), int(first_step), ns,
-            _cvoidp_array(params) if ns else None, _cvoidp_array(s0) if ns and s0 else None,
-            _cvoidp_array(s1) if ns and s1 else None,
-            (ctypes.c_longlong * max(1, ns))(*(offs or [0])), (ctypes.c_longlong * max(1, ns))(*(nums or [0])),
-            self.ctas, ctypes.c_void_p(self.stream.cuda_stream))
+        tail = (is_bf16, opt, hy, int(nesterov), int(first_step), ns,
+                _cvoidp_array(params) if ns else None, _cvoidp_array(s0) if ns and s0 else None,
+                _cvoidp_array(s1) if ns and s1 else None,
+                (ctypes.c_longlong * max(1, ns))(*(offs or [0])), (ctypes.c_longlong * max(1, ns))(*(nums or [0])),
+                self.ctas, ctypes.c_void_p(self.stream.cuda_stream))
+        mc_ptr = getattr(sb, "mc_ptr", 0)
+        if mode == 2 and not mc_ptr:
+            mode = 0                                        # not a multicast-bound buffer: plain two-shot
+        if mode == 2:
+            rc = self.lib.ddpx_p2p_allreduce_nvls(
+                self.rank, self.world_size, _cvoidp_array(sb.ptrs), ctypes.c_void_p(mc_ptr), self._pads_arr,
+                ctypes.c_uint(gen), ctypes.c_longlong(n), *tail)
+        else:
+            rc = self.lib.ddpx_p2p_allreduce_fused(
+                self.rank, self.world_size, _cvoidp_array(sb.ptrs), self._pads_arr, ctypes.c_uint(gen), ctypes.c_longlong(n),
+                tail[0], mode, *tail[1:])
         _lib.count_launch(1)
         _lib.check(rc, "ddpx_p2p_allreduce_fused")
         done = torch.cuda.Event()
@@ -202,7 +235,7 @@ class P2PComm(CommBase):
         return _EventHandle(done)
 
     def all_reduce_sum_(self, flat: torch.Tensor, async_op: bool = True):
-        h = self.launch_allreduce(flat, mode=0, opt=0)
+        h = self.launch_allreduce(flat, mode=2 if self.nvls is not None else 0, opt=0)
         if not async_op:
             h.wait()
         return h
@@ -378,6 +411,8 @@ class FusedUpdate:
         mode = 1 if (small or self.comm.cfg.allreduce_algo == "oneshot") else 0
         if self.comm.cfg.allreduce_algo == "twoshot":
             mode = 0
+        if mode == 0 and self.comm.nvls is not None:
+            mode = 2                                        # shard reduction in the NVSwitch
         self.modes[bucket.index] = mode
         return self.comm.launch_allreduce(buf, mode=mode, opt=1 if self.kind == "sgd" else 2, hyper=self._hyper(group),
                                           nesterov=bool(group.get("nesterov", False)),

@@ -180,6 +180,12 @@ int ddpx_p2p_allreduce_fused(int rank, int world, void* const* bufs, void* const
                              int is_bf16, int mode, int opt, const float* hyper, int nesterov, int first_step, int nslots,
                              void* const* params, void* const* state0, void* const* state1, const long long* offsets,
                              const long long* numels, int ctas, void* stream);
+/* NVLS flavour: the shard reduction runs in the NVSwitch (multimem.ld_reduce / multimem.st on mc_buf, the multicast
+ * mapping of the same symmetric buffer); everything else as the two-shot mode of ddpx_p2p_allreduce_fused. */
+int ddpx_p2p_allreduce_nvls(int rank, int world, void* const* bufs, void* mc_buf, void* const* pads, unsigned int gen,
+                            long long n, int is_bf16, int opt, const float* hyper, int nesterov, int first_step, int nslots,
+                            void* const* params, void* const* state0, void* const* state1, const long long* offsets,
+                            const long long* numels, int ctas, void* stream);
 int ddpx_p2p_broadcast(int rank, int world, void* const* pads, int src, unsigned int gen, void* staging_of_src, int n,
                        void* const* ptrs, const long long* offs, const long long* bytes, int ctas, void* stream);
 

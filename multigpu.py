@@ -78,7 +78,7 @@ if __name__ == "__main__":
     parser.add_argument('--seq-len', dest='seq_len', default=1024, type=int, help='extra: GPT-2 sequence length')
     parser.add_argument('--bucket-cap-mb', dest='bucket_cap_mb', default=None, type=float, help='extra: gradient bucket cap')
     parser.add_argument('--allreduce-algo', dest='allreduce_algo', default=None,
-                        choices=[None, 'auto', 'oneshot', 'twoshot', 'nccl'], help='extra: all-reduce algorithm')
+                        choices=[None, 'auto', 'oneshot', 'twoshot', 'nvls', 'nccl'], help='extra: all-reduce algorithm')
     parser.add_argument('--accum-steps', dest='accum_steps', default=1, type=int, help='extra: micro-batches per optimizer step (no_sync)')
     parser.add_argument('--synthetic', action='store_true', help='extra: CIFAR-shaped random data (no download)')
     parser.add_argument('--synthetic_size', default=50000, type=int)

@@ -141,6 +141,58 @@ def test_p2p_collectives_match_nccl():
         assert not bad, bad
 
 
+def _w_nvls(rank, world, port, outdir):
+    os.environ["DDPX_ALLREDUCE_ALGO"] = "nvls"
+    _setup(rank, world, port)
+    import torch.distributed as dist
+    comm = ddpx.launch.get_comm()
+    res = {"supported": comm.nvls is not None}
+    if comm.nvls is not None:
+        for dtype in (torch.float32, torch.bfloat16):
+            for n in (8, 4096, 3_000_000):
+                buf = comm.alloc(n, dtype, None)
+                sb = comm.symbuf_of(buf)
+                res[("mc", str(dtype), n)] = bool(sb.mc_ptr)
+                torch.manual_seed(rank * 11 + n)
+                src = (torch.randn(n, device="cuda") * 0.5).to(dtype)
+                for rep in range(2):                  # twice: generations advance, the buffer is reused
+                    buf.copy_(src)
+                    ref = src.clone().float()
+                    dist.all_reduce(ref)
+                    comm.all_reduce_sum_(buf, async_op=False)
+                    torch.cuda.synchronize()
+                    tol = 1e-5 if dtype == torch.float32 else 3e-2
+                    res[(str(dtype), n, rep)] = ((buf.float() - ref).abs().max() / ref.abs().max().clamp_min(1e-6)).item() < tol
+        # fused SGD through the NVLS mode: every rank ends with the same parameter = p - lr * mean(g)
+        n = 1_000_000
+        buf = comm.alloc(n, torch.float32, None)
+        g = torch.full((n,), float(rank + 1), device="cuda")
+        buf.copy_(g / world)
+        prm = torch.ones(n, device="cuda"); mom = torch.zeros(n, device="cuda")
+        h = comm.launch_allreduce(buf, mode=2, opt=1, hyper=[0.1, 0.0, 0.0, 0.0, 0, 0, 0, 1.0, 1.0],
+                                  slots=([prm.data_ptr()], [0], [0], [0], [n]))
+        h.wait(); torch.cuda.synchronize()
+        mean_g = sum(range(1, world + 1)) / world
+        res["fused_sgd"] = bool(torch.allclose(prm, torch.full_like(prm, 1.0 - 0.1 * mean_g), atol=1e-6))
+    res["err"] = comm.error_word()
+    torch.save(res, os.path.join(outdir, f"rank{rank}.pt"))
+    ddpx.teardown()
+
+
+@pytest.mark.multigpu
+def test_nvls_allreduce_matches_nccl():
+    """multimem.ld_reduce / multimem.st through a multicast-bound bucket; skipped where the driver has no multicast."""
+    world = min(torch.cuda.device_count(), 8)
+    outs = _run(_w_nvls, world)
+    os.environ.pop("DDPX_ALLREDUCE_ALGO", None)
+    if not all(o["supported"] for o in outs):
+        pytest.skip("NVLS multicast not supported on this box")
+    for o in outs:
+        assert o["err"] == 0
+        bad = [k for k, v in o.items() if k not in ("err", "supported") and not v]
+        assert not bad, bad
+
+
 @pytest.mark.multigpu
 def test_vgg_fused_p2p_training_tracks_torch_ddp():
     world = min(torch.cuda.device_count(), 8)
