@@ -18,9 +18,18 @@ torch.cuda.set_device(local_rank)
 if world > 1:
     ddpx.launch.setup_from_env()
 torch.manual_seed(local_rank)
-objs = ddpx.recipes.vgg_train_objs(world_size=world, synthetic=True, synthetic_size=0)
-tr = ddpx.Trainer(objs.model, [], objs.optimizer, local_rank, 1, scheduler=objs.scheduler)
-x = torch.rand(512, 3, 32, 32, device="cuda"); y = torch.randint(0, 10, (512,), device="cuda")
+model_name = sys.argv[1] if len(sys.argv) > 1 else "vgg"
+if model_name == "vgg":
+    objs = ddpx.recipes.vgg_train_objs(world_size=world, synthetic=True, synthetic_size=0)
+    tr = ddpx.Trainer(objs.model, [], objs.optimizer, local_rank, 1, scheduler=objs.scheduler)
+    x = torch.rand(512, 3, 32, 32, device="cuda"); y = torch.randint(0, 10, (512,), device="cuda")
+    first_kernel = "im2col"
+else:                                   # gpt2 | gpt2-medium | ... : batch 8 x seq 1024, bf16, AdamW
+    objs, loss_fn = ddpx.recipes.make(model_name, world_size=world, synthetic=True, synthetic_size=0)
+    tr = ddpx.Trainer(objs.model, [], objs.optimizer, local_rank, 1, loss_fn=loss_fn)
+    V = objs.model.cfg.vocab_size
+    x = torch.randint(0, V, (8, 1024), device="cuda"); y = torch.randint(0, V, (8, 1024), device="cuda")
+    first_kernel = "embedding"
 for _ in range(6):
     tr._run_batch(x, y)
 torch.cuda.synchronize()
@@ -36,7 +45,7 @@ if local_rank == 0:
     ev = [e for e in json.load(open(path))["traceEvents"] if e.get("cat") in ("kernel", "gpu_memcpy", "gpu_memset")]
     ev.sort(key=lambda e: e["ts"])
     # split into steps at the stem im2col kernel (first kernel of a forward)
-    starts = [i for i, e in enumerate(ev) if "im2col" in e["name"]]
+    starts = [i for i, e in enumerate(ev) if first_kernel in e["name"] and "bwd" not in e["name"]]
     if len(starts) >= 2:
         a, b = starts[-2], starts[-1]
         step = ev[a:b]
@@ -46,8 +55,15 @@ if local_rank == 0:
         for e in step:
             s = e["args"].get("stream", "?")
             busy[s] = busy.get(s, 0.0) + e["dur"]
-            nm = e["name"].split("(")[0][-60:]
+            nm = e["name"].replace("(anonymous namespace)::", "").replace("void ", "").split("(")[0][:60]
             print(f"{e['ts'] - t0:9.1f} {e['dur']:8.1f}  s{s}  {nm}")
+        agg = {}
+        for e in step:
+            nm = e["name"].replace("(anonymous namespace)::", "").replace("void ", "").split("(")[0][:60]
+            a = agg.setdefault(nm, [0, 0.0]); a[0] += 1; a[1] += e["dur"]
+        print("# per kernel (calls, total us):")
+        for nm, (c, d) in sorted(agg.items(), key=lambda kv: -kv[1][1]):
+            print(f"#   {d:9.1f} us  {c:4d}  {nm}")
         print("# busy us per stream:", {k: round(v, 1) for k, v in busy.items()})
 if world > 1:
     ddpx.launch.teardown()

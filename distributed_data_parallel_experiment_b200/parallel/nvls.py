@@ -76,9 +76,9 @@ class NvlsBuf:
     """One symmetric buffer: ``ptrs[r]`` = rank r's copy mapped here, ``mc_ptr`` = the multicast mapping, ``tensor`` = a
     uint8 view of the local copy."""
 
-    def __init__(self, local, ptrs, mc_ptr, nbytes, tensor, handles):
+    def __init__(self, local, ptrs, mc_ptr, nbytes, tensor, handles, mc_handle, rank):
         self.local, self.ptrs, self.mc_ptr, self.nbytes, self.tensor = local, ptrs, mc_ptr, nbytes, tensor
-        self._handles = handles
+        self._handles, self._mc_handle, self._rank = handles, mc_handle, rank
 
 
 class NvlsAllocator:
@@ -166,6 +166,26 @@ class NvlsAllocator:
         t = torch.as_tensor(_RawCuda(ptrs[self.rank], size), device=torch.device("cuda", self.device))
         t.zero_()
         torch.cuda.synchronize(self.device)
-        buf = NvlsBuf(ptrs[self.rank], ptrs, mc_ptr, size, t, handles + [h_mc])
+        buf = NvlsBuf(ptrs[self.rank], ptrs, mc_ptr, size, t, handles, h_mc, self.rank)
         self.bufs.append(buf)
         return buf
+
+    def close(self) -> None:
+        """Collective teardown: unmap everything, unbind from the multicast objects, release the physical memory."""
+        drv = self.drv
+        torch.cuda.synchronize(self.device)
+        self.x.barrier()                                   # nobody is still reading a peer's copy
+        for b in self.bufs:
+            b.tensor = None
+            for va in list(b.ptrs) + [b.mc_ptr]:
+                if va:
+                    drv.cuMemUnmap(va, b.nbytes)
+                    drv.cuMemAddressFree(va, b.nbytes)
+            drv.cuMulticastUnbind(b._mc_handle, self.dev, 0, b.nbytes)
+        self.x.barrier()
+        for b in self.bufs:
+            for h in b._handles:
+                if h is not None:
+                    drv.cuMemRelease(h)
+            drv.cuMemRelease(b._mc_handle)
+        self.bufs = []

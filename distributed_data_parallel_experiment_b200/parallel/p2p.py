@@ -310,6 +310,15 @@ class P2PComm(CommBase):
             self.lib.ddpx_p2p_free(ctypes.c_void_p(sb.local))
         self._bufs = []
         self._by_ptr = {}
+        if getattr(self, "nvls", None) is not None:
+            try:
+                for sb in getattr(self, "_nvls_bufs", []):
+                    sb.tensor = None
+                self._nvls_bufs = []
+                self.nvls.close()
+            except Exception as e:                      # teardown must not mask the caller's own exception
+                print(f"[ddpx] NVLS teardown: {e!r}")
+            self.nvls = None
         if getattr(self, "store", None) is not None:
             self.store.close()
             self.store = None

@@ -65,3 +65,34 @@ def test_barrier_and_all_gather_across_processes():
     expect = [f"handle-of-{r}".encode() * (r + 1) for r in range(world)]
     for got, order, final in outs:
         assert got == expect and order == [3, 1, 2] and final == 6
+
+
+def _fd_child(conn):
+    r, w = os.pipe()
+    os.write(w, b"through-pidfd")
+    conn.send((os.getpid(), r))
+    conn.recv()                      # stay alive until the parent has duplicated the descriptor
+
+
+def test_fd_passing_by_pidfd():
+    """The NVLS allocator hands cuMem file descriptors to peers with pidfd_getfd (parallel/nvls.py)."""
+    import multiprocessing as pmp
+    from distributed_data_parallel_experiment_b200.parallel import nvls
+    assert nvls.supported(0) in (True, False)           # never raises, with or without a GPU
+    r, w = os.pipe()
+    os.write(w, b"self")
+    d = nvls._dup_fd_from(os.getpid(), r)
+    assert os.read(d, 4) == b"self"
+    ctx = pmp.get_context("spawn")
+    parent, child = ctx.Pipe()
+    p = ctx.Process(target=_fd_child, args=(child,))
+    p.start()
+    pid, fd = parent.recv()
+    try:
+        got = nvls._dup_fd_from(pid, fd)
+    except OSError as e:                                 # ptrace-restricted sandboxes refuse pidfd_getfd
+        parent.send(1); p.join()
+        pytest.skip(f"pidfd_getfd not permitted here: {e}")
+    assert os.read(got, 13) == b"through-pidfd"
+    parent.send(1)
+    p.join()
