@@ -56,6 +56,22 @@ pack_conv_w_tiled_kernel(const float* __restrict__ w, float* __restrict__ wf, fl
   }
 }
 
+// inverse direction for the weight gradient: staging layout [9][Cout][Cin] -> torch layout [Cout][Cin][3][3]
+__global__ void __launch_bounds__(256)
+unpack_conv_wgrad_kernel(const float* __restrict__ wp, float* __restrict__ w, int Cout, int Cin) {
+  __shared__ float tile[32][289];
+  const int ci0 = blockIdx.x * 32, co0 = blockIdx.y * 32;
+  for (int idx = threadIdx.x; idx < 9 * 1024; idx += 256) {
+    const int tap = idx >> 10, co = (idx >> 5) & 31, ci = idx & 31;
+    tile[co][ci * 9 + tap] = wp[(static_cast<long long>(tap) * Cout + co0 + co) * Cin + ci0 + ci];
+  }
+  __syncthreads();
+  for (int idx = threadIdx.x; idx < 32 * 288; idx += 256) {
+    const int co = idx / 288, j = idx - co * 288;
+    w[(static_cast<long long>(co0 + co) * Cin + ci0) * 9 + j] = tile[co][j];
+  }
+}
+
 // ------------------------------------------------------------------------------------------------
 // direct conv for Cin == 3 (input NCHW, output NHWC).  One thread = one output pixel, all Cout channels.
 // ------------------------------------------------------------------------------------------------
@@ -280,6 +296,13 @@ extern "C" int ddpx_pack_conv_weights(const float* w, float* w_fprop, float* w_d
     return LAUNCH_OK();
   }
   pack_conv_w_kernel<<<nblocks(total, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(w, w_fprop, w_dgrad, Cout, Cin);
+  return LAUNCH_OK();
+}
+
+extern "C" int ddpx_unpack_conv_wgrad(const float* dw_packed, float* dw, int Cout, int Cin, void* stream) {
+  if (Cout % 32 || Cin % 32 || Cout / 32 > 65535) return DDPX_ERR_SHAPE;
+  dim3 grid(Cin / 32, Cout / 32);
+  unpack_conv_wgrad_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(dw_packed, dw, Cout, Cin);
   return LAUNCH_OK();
 }
 

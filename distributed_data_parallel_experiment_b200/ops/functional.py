@@ -59,6 +59,8 @@ def _check_f32(*ts):
 
 
 # ------------------------------------------------------------------------------------------------ conv (+BN+ReLU+pool)
+import os as _os
+_WGRAD_PACKED = _os.environ.get("DDPX_WGRAD_PACKED", "1") not in ("0", "")   # A/B switch for the staging-layout epilogue
 _STEM_SPLIT_K = 296   # two K-slices per SM for the pixels-long reduction of the stem weight gradient
 
 
@@ -86,12 +88,20 @@ def _conv_forward(x, w, y, N, H, W_, Cin, Cout, stem, bias, act, ssum, ssq, need
 
 
 def _conv_backward(ctx_stem, dconv, xin, w, wd, N, H, W_, Cin, Cout, need_dx):
-    dw = _zeros(w.shape, w.device)
     if ctx_stem:
+        dw = _zeros(w.shape, w.device)
         # dw[Cout][27] += dconv^T[Cout][P] @ patches[P][0:27]  (both operands MN-major, split-K, fp32 atomics)
         native.gemm(dconv, xin, dw, Cout, 27, N * H * W_, Cout, 32, 27, 1, 1, None, 0, _STEM_SPLIT_K, 1)
         return None, dw
-    native.conv3x3_wgrad(dconv, xin, dw, N, H, W_, Cin, Cout)
+    if _WGRAD_PACKED:
+        # accumulate into the tap-major staging layout with 16-byte vector reductions, then transpose once
+        staging = _zeros((9 * Cout * Cin,), w.device)
+        native.conv3x3_wgrad_packed(dconv, xin, staging, N, H, W_, Cin, Cout)
+        dw = torch.empty(w.shape, device=w.device, dtype=torch.float32)
+        native.unpack_conv_wgrad(staging, dw, Cout, Cin)
+    else:
+        dw = _zeros(w.shape, w.device)
+        native.conv3x3_wgrad(dconv, xin, dw, N, H, W_, Cin, Cout)
     dx = None
     if need_dx:
         dx = torch.empty((N, H, W_, Cin), device=w.device, dtype=torch.float32)

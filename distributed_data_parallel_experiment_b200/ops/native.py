@@ -76,6 +76,15 @@ def conv3x3_wgrad(dy_nhwc, x_nhwc, dw, N, H, W, Cin, Cout, split_k=0):
           c_int(split_k), _st(), tag=f"[{Cin}->{Cout}@{H}]")
 
 
+def conv3x3_wgrad_packed(dy_nhwc, x_nhwc, dw_packed, N, H, W, Cin, Cout, split_k=0):
+    _call("ddpx_conv3x3_wgrad_packed", _P(dy_nhwc), _P(x_nhwc), _P(dw_packed), c_int(N), c_int(H), c_int(W), c_int(Cin),
+          c_int(Cout), c_int(split_k), _st(), tag=f"[{Cin}->{Cout}@{H}]")
+
+
+def unpack_conv_wgrad(dw_packed, dw, Cout, Cin):
+    _call("ddpx_unpack_conv_wgrad", _P(dw_packed), _P(dw), c_int(Cout), c_int(Cin), _st())
+
+
 def im2col_stem(x_nchw, patches, N, H, W):
     _call("ddpx_im2col_stem", _P(x_nchw), _P(patches), c_int(N), c_int(H), c_int(W), _st())
 

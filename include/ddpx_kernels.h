@@ -55,6 +55,11 @@ int ddpx_conv3x3_fprop(const float* x, const float* wpacked, float* y, int Nimg,
                        const float* bias, int act, float* stat_sum, float* stat_sq, void* stream);
 int ddpx_conv3x3_wgrad(const float* dy, const float* x, float* dw, int Nimg, int H, int W, int Cin, int Cout,
                        int split_k, void* stream);
+/* Weight gradient into the tap-major staging layout dw_packed[9][Cout][Cin] (caller zeroes it; 16-byte vector reductions),
+ * and the transposition of that layout into torch's [Cout][Cin][3][3]. */
+int ddpx_conv3x3_wgrad_packed(const float* dy, const float* x, float* dw_packed, int Nimg, int H, int W, int Cin, int Cout,
+                              int split_k, void* stream);
+int ddpx_unpack_conv_wgrad(const float* dw_packed, float* dw, int Cout, int Cin, void* stream);
 /* RGB stem on tensor cores (M:53 conv0, K = 27 padded to 32): patches[P][32] = im2col(x_nchw); forward =
  * ddpx_conv1x1_fprop(patches, wp[Cout][32]) with the same epilogue as the 3x3 kernel; weight gradient =
  * ddpx_gemm(dy^T, patches) with split-K. */

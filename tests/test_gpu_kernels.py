@@ -315,3 +315,22 @@ def test_deepnn_runs_natively():
     import copy
     cpu = copy.deepcopy(m).cpu()
     assert rel_err(m(x), cpu(x.cpu()).cuda()) < 2e-2
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("N,H,W,Cin,Cout", [(8, 8, 8, 64, 128), (4, 16, 16, 128, 256), (16, 4, 4, 256, 256)])
+def test_conv_wgrad_staging_layout_matches_direct(N, H, W, Cin, Cout):
+    """ddpx_conv3x3_wgrad_packed + ddpx_unpack_conv_wgrad == ddpx_conv3x3_wgrad (same MMAs, different reduction layout)."""
+    from distributed_data_parallel_experiment_b200.ops import native
+    torch.manual_seed(3)
+    x = torch.randn(N, H, W, Cin, device="cuda")
+    dy = torch.randn(N, H, W, Cout, device="cuda")
+    direct = torch.zeros(Cout, Cin, 3, 3, device="cuda")
+    native.conv3x3_wgrad(dy, x, direct, N, H, W, Cin, Cout)
+    staging = torch.zeros(9 * Cout * Cin, device="cuda")
+    native.conv3x3_wgrad_packed(dy, x, staging, N, H, W, Cin, Cout)
+    out = torch.empty(Cout, Cin, 3, 3, device="cuda")
+    native.unpack_conv_wgrad(staging, out, Cout, Cin)
+    assert rel_err(out, direct) < 1e-5
+    ref = torch.nn.grad.conv2d_weight(x.permute(0, 3, 1, 2).double(), (Cout, Cin, 3, 3), dy.permute(0, 3, 1, 2).double(), padding=1)
+    assert rel_err(out, ref) < TF32_RTOL
