@@ -59,6 +59,7 @@ class VGG(nn.Module):
             conv = getattr(bb, f"conv{idx}")
             bn = getattr(bb, f"bn{idx}")
             x = ops.conv_bn_act(x, conv.weight, bn.weight, bn.bias, bn.running_mean, bn.running_var,
-                                bn.num_batches_tracked, bn.training, bn.momentum, bn.eps, relu=True, pool=pooled)
+                                bn.num_batches_tracked, bn.training, bn.momentum, bn.eps, relu=True, pool=pooled,
+                                sync=getattr(bn, "stat_sync", None))
         x = ops.spatial_mean(x)
         return self.classifier(x)

@@ -39,6 +39,52 @@ class BatchNorm2d(nn.BatchNorm2d):
         return super().forward(x)
 
 
+class SyncBatchNorm(BatchNorm2d):
+    """BatchNorm2d whose batch statistics span all ranks (the option the reference leaves commented out at
+    multigpu.py:127).  Same parameters, buffers and state_dict keys as BatchNorm2d; with one process it IS BatchNorm2d.
+    ``sync_key`` names the layer's statistic buffers on the P2P backend (set by ``convert_sync_batchnorm``)."""
+
+    sync_key = "bn"
+
+    @property
+    def stat_sync(self):
+        """(StatSync, key) while training in a multi-rank job, else None."""
+        import torch.distributed as dist
+        if not (self.training and dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1):
+            return None
+        from ..parallel.syncbn import default_sync
+        return (default_sync(), self.sync_key)
+
+    def forward(self, x: torch.Tensor) -> torch.Tensor:
+        sync = self.stat_sync
+        if sync is None:
+            return super().forward(x)
+        if not (self.affine and self.track_running_stats and self.momentum is not None):
+            raise NotImplementedError("SyncBatchNorm needs affine=True, track_running_stats=True, fixed momentum")
+        return ops.batch_norm(x, self.weight, self.bias, self.running_mean, self.running_var, self.num_batches_tracked,
+                              self.training, self.momentum, self.eps, sync=sync)
+
+
+def convert_sync_batchnorm(module: nn.Module, _prefix: str = "") -> nn.Module:
+    """Replace every BatchNorm2d in ``module`` by a SyncBatchNorm sharing its parameters and buffers (counterpart of
+    ``torch.nn.SyncBatchNorm.convert_sync_batchnorm``).  Call before wrapping in DataParallel, on every rank."""
+    for name, child in list(module.named_children()):
+        full = f"{_prefix}.{name}" if _prefix else name
+        if isinstance(child, nn.BatchNorm2d) and not isinstance(child, SyncBatchNorm):
+            new = SyncBatchNorm(child.num_features, child.eps, child.momentum, child.affine, child.track_running_stats)
+            if child.affine:
+                new.weight, new.bias = child.weight, child.bias
+            if child.track_running_stats:
+                new.running_mean, new.running_var = child.running_mean, child.running_var
+                new.num_batches_tracked = child.num_batches_tracked
+            new.training = child.training
+            new.sync_key = full
+            setattr(module, name, new)
+        else:
+            convert_sync_batchnorm(child, full)
+    return module
+
+
 class ReLU(nn.ReLU):
     def forward(self, x: torch.Tensor) -> torch.Tensor:
         return ops.relu(x)

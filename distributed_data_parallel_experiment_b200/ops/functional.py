@@ -119,7 +119,7 @@ class _ConvBNAct(Function):
     """conv3x3(pad 1, no bias) -> BatchNorm2d -> [ReLU] -> [MaxPool2d(2)] as one differentiable op (VGG block)."""
 
     @staticmethod
-    def forward(ctx, x, w, gamma, beta, running_mean, running_var, nbt, training, momentum, eps, relu, pool):
+    def forward(ctx, x, w, gamma, beta, running_mean, running_var, nbt, training, momentum, eps, relu, pool, sync=None):
         _check_f32(x, w, gamma, beta)
         N, Cin, H, W_ = x.shape
         Cout = w.shape[0]
@@ -133,9 +133,14 @@ class _ConvBNAct(Function):
         xin, wd = _conv_forward(x, w.detach(), y, N, H, W_, Cin, Cout, stem, None, 0,
                                 stats[0] if training else None, stats[1] if training else None, need_dx)
         mr = torch.empty((2, Cout), device=dev, dtype=torch.float32)
+        sync_key, sync_world = None, 1
+        if training and sync is not None and sync[0].world_size > 1:
+            # SyncBatchNorm: batch statistics over the GLOBAL batch - sum the (sum x, sum x^2) blocks over the ranks
+            sync_key, sync_world = sync[1], sync[0].world_size
+            stats = sync[0].reduce(stats, sync_key + "/fwd")
         if training:
-            native.bn_finalize(stats[0], stats[1], float(N * H * W_), mr[0], mr[1], running_mean, running_var, nbt,
-                               momentum, eps, Cout)
+            native.bn_finalize(stats[0], stats[1], float(N * H * W_ * sync_world), mr[0], mr[1], running_mean, running_var,
+                               nbt, momentum, eps, Cout)
         else:
             native.bn_eval_stats(running_mean, running_var, eps, mr[0], mr[1], Cout)
         Ho, Wo = (H // 2, W_ // 2) if pool else (H, W_)
@@ -143,6 +148,7 @@ class _ConvBNAct(Function):
         native.bn_apply(y, out, mr[0], mr[1], gamma, beta, N, H, W_, Cout, int(relu), int(pool))
         ctx.save_for_backward(xin, y, mr, gamma, beta, w, wd)
         ctx.cfg = (N, H, W_, Cin, Cout, stem, bool(training), bool(relu), bool(pool), need_dx)
+        ctx.sync = (sync[0], sync_key) if sync_key is not None else None
         return from_nhwc(out)
 
     @staticmethod
@@ -154,11 +160,17 @@ class _ConvBNAct(Function):
         sums = _zeros((2, Cout), dev)
         native.bn_bwd_reduce(y, d, mr[0], mr[1], gamma, beta, N, H, W_, Cout, int(relu), int(pool), sums[0], sums[1])
         dconv = torch.empty_like(y)
-        native.bn_bwd_apply(y, d, mr[0], mr[1], gamma, beta, sums[0], sums[1], N, H, W_, Cout, int(relu), int(pool),
+        tot = sums
+        if ctx.sync is not None:
+            # the input gradient needs the global (sum dy, sum dy*xhat); bn_bwd_apply divides by the LOCAL pixel count,
+            # so hand it the global sums divided by the world size.  gamma / beta keep their local sums (DDP averages)
+            tot = ctx.sync[0].reduce(sums, ctx.sync[1] + "/bwd")
+            native.scale_copy(tot, tot, tot.numel(), 1.0 / ctx.sync[0].world_size)
+        native.bn_bwd_apply(y, d, mr[0], mr[1], gamma, beta, tot[0], tot[1], N, H, W_, Cout, int(relu), int(pool),
                             int(training), dconv)
         dx, dw = _conv_backward(stem, dconv, xin, w, wd, N, H, W_, Cin, Cout, need_dx)
         dxo = from_nhwc(dx) if dx is not None else None
-        return dxo, dw, sums[1], sums[0], None, None, None, None, None, None, None, None
+        return dxo, dw, sums[1], sums[0], None, None, None, None, None, None, None, None, None
 
 
 class _ConvAct(Function):
@@ -199,15 +211,14 @@ class _ConvAct(Function):
 
 
 def conv_bn_act(x, w, gamma, beta, running_mean, running_var, num_batches_tracked, training: bool, momentum: float = 0.1,
-                eps: float = 1e-5, relu: bool = True, pool: bool = False):
-    """Fused VGG block (multigpu.py:53-59).  CPU tensors use the torch composition with the same semantics."""
+                eps: float = 1e-5, relu: bool = True, pool: bool = False, sync=None):
+    """Fused VGG block (multigpu.py:53-59).  CPU tensors use the torch composition with the same semantics.
+    ``sync = (StatSync, key)`` turns the BatchNorm into a SyncBatchNorm (statistics over all ranks)."""
     if x.is_cuda:
         return _ConvBNAct.apply(x, w, gamma, beta, running_mean, running_var, num_batches_tracked, training, momentum, eps,
-                                relu, pool)
+                                relu, pool, sync)
     y = F.conv2d(x, w, None, padding=1)
-    if training and num_batches_tracked is not None:
-        num_batches_tracked.add_(1)
-    y = F.batch_norm(y, running_mean, running_var, gamma, beta, training, momentum, eps)
+    y = batch_norm(y, gamma, beta, running_mean, running_var, num_batches_tracked, training, momentum, eps, sync=sync)
     if relu:
         y = F.relu(y)
     if pool:
@@ -225,14 +236,24 @@ def conv3x3(x, w, bias=None, relu: bool = False):
 # ------------------------------------------------------------------------------------------------ stand-alone BN / ReLU / pool
 class _BatchNorm(Function):
     @staticmethod
-    def forward(ctx, x, gamma, beta, running_mean, running_var, nbt, training, momentum, eps):
+    def forward(ctx, x, gamma, beta, running_mean, running_var, nbt, training, momentum, eps, sync=None):
         _check_f32(x, gamma, beta)
         N, C, H, W_ = x.shape
         xin = to_nhwc(x)
         dev = x.device
         mr = torch.empty((2, C), device=dev, dtype=torch.float32)
         out = torch.empty_like(xin)
-        if training:
+        ctx.sync = None
+        if training and sync is not None and sync[0].world_size > 1:
+            # SyncBatchNorm: local (sum, sum^2) -> summed over the ranks -> finalize with the global count -> apply
+            stats = _zeros((2, C), dev)
+            native.bn_stats(xin, N * H * W_, C, stats[0], stats[1])
+            stats = sync[0].reduce(stats, sync[1] + "/fwd")
+            native.bn_finalize(stats[0], stats[1], float(N * H * W_ * sync[0].world_size), mr[0], mr[1], running_mean,
+                               running_var, nbt, momentum, eps, C)
+            native.bn_apply(xin, out, mr[0], mr[1], gamma, beta, N, H, W_, C, 0, 0)
+            ctx.sync = sync
+        elif training:
             work = torch.empty((2, C), device=dev, dtype=torch.float32)      # scratch: cleared inside the call
             native.bn_train_fwd(xin, out, gamma, beta, running_mean, running_var, nbt, momentum, eps, N, H, W_, C, 0, 0,
                                 mr, work)
@@ -251,15 +272,67 @@ class _BatchNorm(Function):
         sums = _zeros((2, C), xin.device)
         native.bn_bwd_reduce(xin, d, mr[0], mr[1], gamma, beta, N, H, W_, C, 0, 0, sums[0], sums[1])
         dx = torch.empty_like(xin)
-        native.bn_bwd_apply(xin, d, mr[0], mr[1], gamma, beta, sums[0], sums[1], N, H, W_, C, 0, 0, int(training), dx)
-        return from_nhwc(dx), sums[1], sums[0], None, None, None, None, None, None
+        tot = sums
+        if ctx.sync is not None:
+            tot = ctx.sync[0].reduce(sums, ctx.sync[1] + "/bwd")
+            native.scale_copy(tot, tot, tot.numel(), 1.0 / ctx.sync[0].world_size)
+        native.bn_bwd_apply(xin, d, mr[0], mr[1], gamma, beta, tot[0], tot[1], N, H, W_, C, 0, 0, int(training), dx)
+        return from_nhwc(dx), sums[1], sums[0], None, None, None, None, None, None, None
 
 
-def batch_norm(x, gamma, beta, running_mean, running_var, num_batches_tracked, training, momentum=0.1, eps=1e-5):
+class _SyncBatchNormRef(Function):
+    """SyncBatchNorm in plain torch math (CPU / gloo): the same formulas as the native path, statistics summed over the
+    ranks through ``StatSync`` (torch's own SyncBatchNorm refuses CPU tensors)."""
+
+    @staticmethod
+    def forward(ctx, x, gamma, beta, running_mean, running_var, momentum, eps, sync):
+        C = x.shape[1]
+        red = [0, 2, 3]
+        n_local = x.numel() // C
+        xf = x.float()
+        stats = torch.stack([xf.sum(red), (xf * xf).sum(red)])
+        stats = sync[0].reduce(_pad8(stats), sync[1] + "/fwd")[:, :C]
+        n = n_local * sync[0].world_size
+        mean = stats[0] / n
+        var = (stats[1] / n - mean * mean).clamp_min(0)
+        rstd = torch.rsqrt(var + eps)
+        if running_mean is not None:
+            with torch.no_grad():
+                running_mean.mul_(1 - momentum).add_(momentum * mean)
+                running_var.mul_(1 - momentum).add_(momentum * var * (n / max(n - 1, 1)))
+        xhat = (xf - mean[None, :, None, None]) * rstd[None, :, None, None]
+        ctx.save_for_backward(xhat, rstd, gamma)
+        ctx.sync, ctx.n_local = sync, n_local
+        return (xhat * gamma[None, :, None, None] + beta[None, :, None, None]).to(x.dtype)
+
+    @staticmethod
+    def backward(ctx, dy):
+        xhat, rstd, gamma = ctx.saved_tensors
+        C = xhat.shape[1]
+        red = [0, 2, 3]
+        dyf = dy.float()
+        sums = torch.stack([dyf.sum(red), (dyf * xhat).sum(red)])
+        tot = ctx.sync[0].reduce(_pad8(sums), ctx.sync[1] + "/bwd")[:, :C] / (ctx.n_local * ctx.sync[0].world_size)
+        dx = (gamma * rstd)[None, :, None, None] * (dyf - tot[0][None, :, None, None] - xhat * tot[1][None, :, None, None])
+        return dx.to(dy.dtype), sums[1], sums[0], None, None, None, None, None
+
+
+def _pad8(t2c):
+    """[2, C] -> [2, C'] with C' a multiple of 4, so that the flattened block is a multiple of 8 elements."""
+    C = t2c.shape[1]
+    if C % 4 == 0:
+        return t2c.contiguous()
+    return F.pad(t2c, (0, 4 - C % 4)).contiguous()
+
+
+def batch_norm(x, gamma, beta, running_mean, running_var, num_batches_tracked, training, momentum=0.1, eps=1e-5, sync=None):
+    """``sync = (StatSync, key)`` computes the batch statistics over all ranks (SyncBatchNorm)."""
     if x.is_cuda:
-        return _BatchNorm.apply(x, gamma, beta, running_mean, running_var, num_batches_tracked, training, momentum, eps)
+        return _BatchNorm.apply(x, gamma, beta, running_mean, running_var, num_batches_tracked, training, momentum, eps, sync)
     if training and num_batches_tracked is not None:
         num_batches_tracked.add_(1)
+    if training and sync is not None and sync[0].world_size > 1:
+        return _SyncBatchNormRef.apply(x, gamma, beta, running_mean, running_var, momentum, eps, sync)
     return F.batch_norm(x, running_mean, running_var, gamma, beta, training, momentum, eps)
 
 

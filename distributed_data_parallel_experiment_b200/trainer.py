@@ -196,6 +196,12 @@ class Trainer:
         sampler = getattr(self.train_data, "sampler", None)
         if self.distributed and hasattr(sampler, "set_epoch"):
             sampler.set_epoch(epoch)                     # multigpu.py:103
+        if self.device.type == "cuda":
+            # same steps as the reference's loop (multigpu.py:104-107), with the upload of batch i+1 overlapping step i
+            # (the reference copies blockingly between steps - SURVEY.md K16)
+            for _ in self.train_stream(self.train_data):
+                pass
+            return
         for source, targets in self.train_data:
             source = source.to(self.device, non_blocking=True)
             targets = targets.to(self.device, non_blocking=True)

@@ -37,6 +37,8 @@ def load_train_objs(opts=None):
                                    synthetic_size=int(opts.get("synthetic_size", 50000)), dtype=opts.get("dtype"),
                                    device=None if model_name == "toy" else device, seq_len=int(opts.get("seq_len", 1024)))
     opts["_loss_fn"] = loss_fn
+    if opts.get("sync_bn"):
+        ddpx.nn.convert_sync_batchnorm(o.model)      # the option the reference keeps commented out (multigpu.py:127)
     return o.train_set, o.model, o.optimizer, o.test_set, o.scheduler
 
 
@@ -79,6 +81,7 @@ if __name__ == "__main__":
     parser.add_argument('--bucket-cap-mb', dest='bucket_cap_mb', default=None, type=float, help='extra: gradient bucket cap')
     parser.add_argument('--allreduce-algo', dest='allreduce_algo', default=None,
                         choices=[None, 'auto', 'oneshot', 'twoshot', 'nvls', 'nccl'], help='extra: all-reduce algorithm')
+    parser.add_argument('--sync-bn', dest='sync_bn', action='store_true', help='extra: SyncBatchNorm (statistics over all ranks)')
     parser.add_argument('--accum-steps', dest='accum_steps', default=1, type=int, help='extra: micro-batches per optimizer step (no_sync)')
     parser.add_argument('--synthetic', action='store_true', help='extra: CIFAR-shaped random data (no download)')
     parser.add_argument('--synthetic_size', default=50000, type=int)
@@ -89,5 +92,5 @@ if __name__ == "__main__":
     world_size = args.nprocs or (torch.cuda.device_count() if torch.cuda.is_available() else 2)
     opts = {"model": args.model, "synthetic": args.synthetic, "synthetic_size": args.synthetic_size, "backend": args.backend,
             "dtype": args.dtype, "seq_len": args.seq_len, "bucket_cap_mb": args.bucket_cap_mb,
-            "allreduce_algo": args.allreduce_algo, "accum_steps": args.accum_steps}
+            "allreduce_algo": args.allreduce_algo, "accum_steps": args.accum_steps, "sync_bn": args.sync_bn}
     ddpx.spawn(main, args=(world_size, args.save_every, args.total_epochs, args.batch_size, opts), nprocs=world_size)

@@ -179,6 +179,51 @@ def _w_nvls(rank, world, port, outdir):
     ddpx.teardown()
 
 
+def _w_syncbn(rank, world, port, outdir):
+    _setup(rank, world, port)
+    torch.manual_seed(7)
+    net = ddpx.models.VGG().cuda()
+    ref = ddpx.models.VGG().cuda(); ref.load_state_dict(net.state_dict())
+    ddpx.nn.convert_sync_batchnorm(net)
+    w = ddpx.DataParallel(net)
+
+    def data(r):
+        g = torch.Generator().manual_seed(500 + r)
+        return torch.rand(32, 3, 32, 32, generator=g).cuda(), torch.randint(0, 10, (32,), generator=g).cuda()
+    x, y = data(rank)
+    loss = ddpx.ops.cross_entropy(w(x), y)
+    loss.backward()
+    xs, ys = zip(*[data(r) for r in range(world)])
+    full = ddpx.ops.cross_entropy(ref(torch.cat(xs)), torch.cat(ys))       # ordinary BN over the global batch
+    full.backward()
+    gl = torch.tensor([float(loss.detach())], device="cuda")
+    import torch.distributed as dist
+    dist.all_reduce(gl)
+    out = {"loss_mean": float(gl) / world, "full": float(full.detach()), "rm": net.backbone.bn3.running_mean.cpu(),
+           "ref_rm": ref.backbone.bn3.running_mean.cpu(), "cos": {}}
+    for k in ("backbone.conv0.weight", "backbone.conv5.weight", "backbone.bn2.weight", "classifier.weight"):
+        a = dict(net.named_parameters())[k].grad.flatten().double(); b = dict(ref.named_parameters())[k].grad.flatten().double()
+        out["cos"][k] = (float(a @ b / (a.norm() * b.norm())), float(a.norm() / b.norm()))
+    comm = ddpx.launch.get_comm()
+    out["err"] = comm.error_word()
+    torch.save(out, os.path.join(outdir, f"rank{rank}.pt"))
+    ddpx.teardown()
+
+
+@pytest.mark.multigpu
+def test_syncbn_native_equals_full_batch():
+    """SyncBatchNorm through the fused conv-BN kernels + P2P statistic all-reduce == plain BN over the global batch."""
+    world = min(torch.cuda.device_count(), 8)
+    outs = _run(_w_syncbn, world)
+    for o in outs:
+        assert o["err"] == 0
+        assert abs(o["loss_mean"] - o["full"]) < 2e-3 * max(1.0, abs(o["full"])), (o["loss_mean"], o["full"])
+        assert torch.allclose(o["rm"], o["ref_rm"], rtol=2e-2, atol=2e-3)
+        for k, (cos, ratio) in o["cos"].items():
+            assert cos > 0.98 and abs(ratio - 1) < 0.05, (k, cos, ratio)
+    assert torch.equal(outs[0]["rm"], outs[1]["rm"])
+
+
 @pytest.mark.multigpu
 def test_nvls_allreduce_matches_nccl():
     """multimem.ld_reduce / multimem.st through a multicast-bound bucket; skipped where the driver has no multicast."""
