@@ -74,6 +74,34 @@ def _w_collectives(rank, world, port, outdir):
             torch.cuda.synchronize()
             tol = 1e-5 if dtype == torch.float32 else 3e-2
             res[(str(dtype), n)] = ((buf.float() - ref).abs().max() / ref.abs().max().clamp_min(1e-6)).item() < tol
+    # fused all-reduce + AdamW / SGD-momentum in one kernel (two-shot and one-shot) against torch's optimizers on the mean
+    # gradient; two steps, so the second one exercises the state (exp_avg / momentum buffer) that the first one wrote
+    import math
+    for kind in ("adamw", "sgd"):
+        for mode, n in ((0, 1_000_000), (1, 40_000)):
+            buf = comm.alloc(n, torch.float32, None)
+            torch.manual_seed(1234)
+            p0 = torch.randn(n, device="cuda")
+            prm = p0.clone(); s0 = torch.zeros(n, device="cuda"); s1 = torch.zeros(n, device="cuda")
+            tp = torch.nn.Parameter(p0.clone())
+            topt = (torch.optim.AdamW([tp], lr=1e-2, betas=(0.9, 0.95), eps=1e-8, weight_decay=0.1) if kind == "adamw"
+                    else torch.optim.SGD([tp], lr=1e-2, momentum=0.9, weight_decay=5e-4))
+            for step in range(1, 3):
+                gs = []
+                for r in range(world):
+                    torch.manual_seed(100 * step + r)
+                    gs.append(torch.randn(n, device="cuda"))
+                buf.copy_(gs[rank] / world)
+                tp.grad = torch.stack(gs).mean(0)
+                topt.step()
+                if kind == "adamw":
+                    hyper = [1e-2, 0.0, 0.0, 0.1, 0.9, 0.95, 1e-8, 1.0 - 0.9 ** step, math.sqrt(1.0 - 0.95 ** step)]
+                else:
+                    hyper = [1e-2, 0.9, 0.0, 5e-4, 0.0, 0.0, 0.0, 1.0, 1.0]
+                h = comm.launch_allreduce(buf, mode=mode, opt=2 if kind == "adamw" else 1, hyper=hyper, first_step=(step == 1),
+                                          slots=([prm.data_ptr()], [s0.data_ptr()], [s1.data_ptr()], [0], [n]))
+                h.wait(); torch.cuda.synchronize()
+            res[("fused", kind, mode)] = ((prm - tp.detach()).abs().max() / tp.detach().abs().max()).item() < 2e-5
     # broadcast: tensors of mixed dtypes, one larger than a staging slot piece
     ts = [torch.full((1000,), float(rank + 1), device="cuda"), torch.full((7,), rank + 1, device="cuda", dtype=torch.int64),
           torch.full((5_000_000,), float(rank + 1), device="cuda", dtype=torch.bfloat16)]
