@@ -79,7 +79,8 @@ __device__ __forceinline__ float gelu_tanh(float x) {
 // kCG = 1: one CTA per tile (128 rows).  kCG = 2: a CTA pair (cluster of 2 on one TPC) per 256-row tile with
 // tcgen05 cta_group::2 - each CTA stages its own 128 rows of A and HALF of the B tile, so a k-step costs 32 KB instead
 // of 48 KB of L2->SM traffic per CTA and the same shared memory holds 6 stages instead of 4 (ncu on the 1-CTA kernel:
-// tensor pipe 58 % active, paced by operand delivery - profiles/ncu_conv_fprop.md).
+// tensor pipe 58 % active - profiles/ncu_findings.md section 1; the larger limiter turned out to be the producer thread,
+// profiles/probe_findings.md section 3).
 // Register budget: the convolution flavours are capped at 96 registers (no spills) so that CTAs of other streams -
 // the fused all-reduce of csrc/runtime/p2p.cu above all - find room on the same SM next to this persistent kernel;
 // the GEMM flavour keeps the staged epilogue's working set in registers.
