@@ -189,6 +189,17 @@ def emit(args, world, impl, total_ms, e2e_ms, h2d, d2h, launches, clocks, extra_
 # ------------------------------------------------------------------------------------------------
 def run_reference(args):
     ref_dir = REPO / "baseline" / "_ref"
+    if not (ref_dir / "multigpu.py").exists() and Path("/root/reference/multigpu.py").exists():
+        # not installed yet (fresh checkout): local rank 0 runs the one-off offline install, the others wait for it
+        import time
+        if int(os.environ.get("LOCAL_RANK", "0")) == 0:
+            subprocess.call(["bash", str(REPO / "baseline" / "install_ref.sh")], stdout=subprocess.DEVNULL,
+                            stderr=subprocess.DEVNULL)
+        else:
+            for _ in range(240):
+                if (ref_dir / "multigpu.py").exists():
+                    break
+                time.sleep(0.5)
     if not (ref_dir / "multigpu.py").exists():
         print(json.dumps({"impl": "reference", "unavailable": "baseline/_ref is missing (run baseline/install_ref.sh)"}))
         return
