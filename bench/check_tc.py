@@ -163,6 +163,11 @@ CASES = {
     "conv_f_vgg3": lambda: run_conv(512, 16, 16, 256, 256, timing=True),
     "conv_f_vgg5": lambda: run_conv(512, 8, 8, 512, 512, timing=True),
     "conv_f_vgg7": lambda: run_conv(512, 4, 4, 512, 512, timing=True),
+    "conv_x_vgg2": lambda: run_conv(512, 16, 16, 128, 256, timing=True),        # the narrower / transition layers
+    "conv_x_vgg4": lambda: run_conv(512, 8, 8, 256, 512, timing=True),
+    "conv_x_dgrad1": lambda: run_conv(512, 32, 32, 128, 64, timing=True),
+    "conv_x_dgrad2": lambda: run_conv(512, 16, 16, 256, 128, timing=True),
+    "conv_x_dgrad4": lambda: run_conv(512, 8, 8, 512, 256, timing=True),
     "conv_w_vgg1": lambda: run_conv(512, 32, 32, 64, 128, wgrad=True, timing=True),
     "conv_w_vgg3": lambda: run_conv(512, 16, 16, 256, 256, wgrad=True, timing=True),
     "conv_w_vgg5": lambda: run_conv(512, 8, 8, 512, 512, wgrad=True, timing=True),
