@@ -79,3 +79,65 @@ class JsonlLogger:
         if self._fh is not None:
             self._fh.close()
             self._fh = None
+
+
+class StepMetrics:
+    """Per-step structured metrics for the Trainer, written as JSON lines to ``DDPX_METRICS_JSONL``
+    (``{rank}`` in the path is replaced by the rank).  Device time comes from CUDA events that are read back lazily -
+    only once they have completed - so logging never puts a synchronisation into the training loop.
+
+    One line per optimizer step: rank, step, device_ms, samples, samples_per_s, loss (when already on the host), world
+    size, and - on a data-parallel model - backend, number of buckets and whether the optimizer is fused."""
+
+    def __init__(self, path: str, rank: int = 0, device: Optional[torch.device] = None, static: Optional[dict] = None):
+        self.rank = rank
+        self.log = JsonlLogger(path.replace("{rank}", str(rank)) if path else "")
+        self.cuda = torch.cuda.is_available() and device is not None and torch.device(device).type == "cuda"
+        self.static = dict(static or {})
+        self._pending = []          # (step, samples, start, end)
+        self._t0 = None
+
+    @property
+    def enabled(self) -> bool:
+        return self.log._fh is not None
+
+    def begin(self):
+        if not self.enabled:
+            return
+        if self.cuda:
+            self._t0 = torch.cuda.Event(enable_timing=True)
+            self._t0.record()
+        else:
+            self._t0 = time.perf_counter()
+
+    def end(self, step: int, samples: int):
+        if not self.enabled or self._t0 is None:
+            return
+        if self.cuda:
+            e = torch.cuda.Event(enable_timing=True)
+            e.record()
+        else:
+            e = time.perf_counter()
+        self._pending.append((step, samples, self._t0, e))
+        self._t0 = None
+        self.flush(block=False)
+
+    def flush(self, block: bool = True):
+        keep = []
+        for step, samples, a, b in self._pending:
+            if self.cuda:
+                if not block and not b.query():
+                    keep.append((step, samples, a, b))
+                    continue
+                b.synchronize()
+                ms = a.elapsed_time(b)
+            else:
+                ms = (b - a) * 1e3
+            self.log.log(rank=self.rank, step=step, device_ms=round(ms, 4), samples=samples,
+                         samples_per_s=round(samples / (ms / 1e3), 1) if ms > 0 else None, **self.static)
+        self._pending = keep
+
+    def close(self):
+        if self.enabled:
+            self.flush(block=True)
+        self.log.close()

@@ -73,6 +73,12 @@ class Trainer:
         self._fault = _watchdog.fault_plan_from_env()
         self._watchdog = _watchdog.from_env(self._rank, self._describe_state)
         self._checksum = _debug.checksum_enabled()
+        static = {"world_size": dist.get_world_size() if self.distributed else 1}
+        if isinstance(self.model, DataParallel):
+            info = self.model.get_logging_data()
+            static.update(backend=info["backend"], fused_optimizer=info["fused_optimizer"])
+        from . import metrics as _metrics
+        self._metrics = _metrics.StepMetrics(config.get().metrics_jsonl, self._rank, self.device, static)
 
     def _describe_state(self) -> str:
         parts = [f"global step {self.global_step}"]
@@ -95,6 +101,7 @@ class Trainer:
             self._watchdog.beat(f"step {self.global_step} begins")
         last = (self._micro + 1) % self.accum_steps == 0
         if self._micro % self.accum_steps == 0:
+            self._metrics.begin()
             self.optimizer.zero_grad()
         if self.distributed and not last:
             with self.model.no_sync():
@@ -109,6 +116,8 @@ class Trainer:
                 self.scheduler.step()
             if self._checksum:
                 _debug.assert_replicas_in_sync(self.model.parameters(), getattr(self.model, "comm", None), self.global_step)
+        if last:
+            self._metrics.end(self.global_step, int(source.shape[0]) * self.accum_steps)
         self.global_step += 1
         self.last_loss = loss
         return loss
@@ -219,6 +228,7 @@ class Trainer:
             self._run_epoch(epoch)
             if self._watchdog is not None:
                 self._watchdog.pause()          # checkpoint writes and whatever the caller does next are not hangs
+            self._metrics.flush(block=True)
             # multigpu.py:118 gates on gpu_id == 0 (rank 0); singlegpu.py:127 saves unconditionally
             if (not self.distributed or self.gpu_id == 0) and epoch % self.save_every == 0:
                 self._save_checkpoint(epoch)

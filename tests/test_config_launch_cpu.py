@@ -91,3 +91,21 @@ def test_gpt2_and_mlp_cpu_forward_backward():
     assert ddpx.models.GPT2(ddpx.models.GPT2Config.small(), dtype=None).num_params() == 124475904
     mlp = ddpx.models.MLP(64, 64, 3, 16, dtype=torch.float32)
     assert mlp(torch.randn(4, 64)).shape == (4, 16)
+
+
+def test_trainer_writes_step_metrics_jsonl(tmp_path, monkeypatch):
+    import json
+    path = tmp_path / "m_{rank}.jsonl"
+    monkeypatch.setenv("DDPX_METRICS_JSONL", str(path))
+    config.reset()
+    torch.manual_seed(0)
+    m = ddpx.models.ToyLinear()
+    opt = torch.optim.SGD(m.parameters(), lr=0.01)
+    data = [(torch.randn(8, 20), torch.randn(8, 1)) for _ in range(4)]
+    tr = ddpx.Trainer(m, data, opt, 0, 1, loss_fn="mse", accum_steps=2, checkpoint_path=str(tmp_path / "c.pt"))
+    tr.train(1)
+    rows = [json.loads(l) for l in (tmp_path / "m_0.jsonl").read_text().splitlines()]
+    assert len(rows) == 2                                   # 4 micro-batches, 2 per optimizer step
+    assert all(r["rank"] == 0 and r["samples"] == 16 and r["device_ms"] >= 0 and r["world_size"] == 1 for r in rows)
+    monkeypatch.delenv("DDPX_METRICS_JSONL")
+    config.reset()
