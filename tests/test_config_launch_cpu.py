@@ -109,3 +109,36 @@ def test_trainer_writes_step_metrics_jsonl(tmp_path, monkeypatch):
     assert all(r["rank"] == 0 and r["samples"] == 16 and r["device_ms"] >= 0 and r["world_size"] == 1 for r in rows)
     monkeypatch.delenv("DDPX_METRICS_JSONL")
     config.reset()
+
+
+def test_recipes_make_covers_every_cli_model():
+    from distributed_data_parallel_experiment_b200 import recipes
+    cpu = torch.device("cpu")
+    o, loss = recipes.make("toy")
+    assert loss == "mse" and len(o.train_set) == 2048
+    o, loss = recipes.make("vgg", world_size=2, synthetic=True, synthetic_size=16, device=cpu)
+    assert loss is None and sum(p.numel() for p in o.model.parameters()) == 9228362 and o.scheduler is not None
+    o, loss = recipes.make("deepnn", synthetic=True, synthetic_size=16, device=cpu)
+    assert sum(p.numel() for p in o.model.parameters()) == 1186986            # singlegpu.py:18-44
+    o, loss = recipes.make("gpt2", synthetic=True, synthetic_size=4, device=cpu, dtype="fp32", seq_len=16)
+    x, y = o.train_set[0]
+    out = o.model(x[None])
+    assert callable(loss) and torch.isfinite(loss(out, y[None]))
+    import pytest
+    with pytest.raises(ValueError):
+        recipes.make("resnet")
+    assert set(recipes.MODEL_CHOICES) >= {"vgg", "deepnn", "toy", "mlp", "gpt2", "gpt2-xl"}
+
+
+def test_entrypoint_flags_parse(monkeypatch):
+    """The extra flags exist on both scripts and default to the reference's behaviour."""
+    import subprocess, sys
+    from pathlib import Path
+    repo = Path(__file__).resolve().parent.parent
+    for script, extra in (("multigpu.py", ["--bucket-cap-mb", "--allreduce-algo", "--sync-bn", "--backend", "--nprocs"]),
+                          ("singlegpu.py", [])):
+        out = subprocess.run([sys.executable, str(repo / script), "--help"], capture_output=True, text=True, timeout=120)
+        assert out.returncode == 0
+        for flag in ["total_epochs", "save_every", "--batch_size", "--model", "--dtype", "--seq-len", "--accum-steps",
+                     "--synthetic"] + extra:
+            assert flag in out.stdout, (script, flag)
