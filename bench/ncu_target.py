@@ -11,7 +11,8 @@ from distributed_data_parallel_experiment_b200.ops import native
 
 which = sys.argv[1] if len(sys.argv) > 1 else "all"
 torch.manual_seed(0)
-N, H, W, Cin, Cout = 512, 16, 16, 256, 256
+import os
+N, H, W, Cin, Cout = (int(v) for v in os.environ.get("NCU_SHAPE", "512,16,16,256,256").split(","))   # N,H,W,Cin,Cout
 x = torch.randn(N, H, W, Cin, device="cuda")
 w = torch.randn(Cout, Cin, 3, 3, device="cuda") * 0.05
 wp = torch.empty(9 * Cout * Cin, device="cuda"); wd = torch.empty_like(wp)
