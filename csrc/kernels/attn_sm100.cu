@@ -1,0 +1,272 @@
+// Fused causal attention (flash style) on tcgen05 / TMEM / TMA for sm_100a, bf16, head dimension 64.
+//
+// No [B,H,T,T] tensor exists in either direction:
+//   forward   one CTA per (batch, head, 128-query tile):  S = Q K^T lands in tensor memory, 128 threads (one per query
+//             row = TMEM lane) run the online softmax, P goes back into tensor memory as bf16 and is the A operand of
+//             O += P V (TS-mode tcgen05.mma: no shared-memory round trip for P); output + per-row log-sum-exp.
+//   backward  probabilities are recomputed from the saved log-sum-exp.  Kernel "dkv" (one CTA per 128-key tile, K and V
+//             resident in tensor memory) walks the query tiles and accumulates dK, dV; kernel "dq" (one CTA per
+//             128-query tile, Q and dO resident in tensor memory) walks the key tiles and accumulates dQ.  Every
+//             contraction whose left operand lives in tensor memory is a TS-mode MMA.
+//
+// The reference is a CNN (/root/reference/multigpu.py:36-71) and has no attention; this serves the GPT-2 configurations
+// of BASELINE.json, where torch's SDPA/flash kernels are the bar.
+#include "attn_common.cuh"
+
+#include <stdio.h>
+
+namespace ddpx {
+
+// =====================================================================================================================
+// forward
+// =====================================================================================================================
+// 192 threads: warp 0 = TMA producer, warp 1 = MMA issuer + TMEM owner, warps 2-5 = softmax (row = 32 * (warp % 4) + lane).
+// Tensor memory (256 columns, so two CTAs share an SM and one CTA's softmax overlaps the other's MMAs):
+//   [0,128) S fp32   [128,192) P bf16 (two per column)   [192,256) O fp32
+constexpr int kFwdThreads = 192;
+constexpr uint32_t kColS = 0, kColP = 128, kColO = 192;
+
+__global__ void __launch_bounds__(kFwdThreads, 2)
+attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const AttnParams p) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* sQ = smem;
+  uint8_t* sK = smem + kTileBytes;           // 2 stages
+  uint8_t* sV = smem + 3 * kTileBytes;       // 2 stages
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + 5 * kTileBytes);
+  uint64_t* q_full = bars;
+  uint64_t* k_full = bars + 1;     // [2]
+  uint64_t* k_empty = bars + 3;    // [2]
+  uint64_t* v_full = bars + 5;     // [2]
+  uint64_t* v_empty = bars + 7;    // [2]
+  uint64_t* s_full = bars + 9;
+  uint64_t* p_full = bars + 10;
+  uint64_t* o_done = bars + 11;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 12);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  // heaviest query tiles (most key blocks under the causal mask) first
+  const int bh_count = p.B * p.H;
+  const int qt = p.nq - 1 - static_cast<int>(blockIdx.x) / bh_count;
+  const int bh = static_cast<int>(blockIdx.x) % bh_count;
+  const int b = bh / p.H, h = bh - b * p.H;
+  const int nkv = qt + 1;
+
+  if (warp == 0 && lane == 0) tma_prefetch_desc(&tmQKV);
+  if (warp == 1) {
+    if (lane == 0) {
+      mbar_init(q_full, 1);
+      for (int s = 0; s < 2; ++s) {
+        mbar_init(&k_full[s], 1); mbar_init(&k_empty[s], 1);
+        mbar_init(&v_full[s], 1); mbar_init(&v_empty[s], 1);
+      }
+      mbar_init(s_full, 1);
+      mbar_init(p_full, 4);          // one arrival per softmax warp
+      mbar_init(o_done, 1);
+      fence_barrier_init();
+    }
+    __syncwarp();
+    tmem_alloc(tmem_slot, 256);
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = *tmem_slot;
+
+  if (warp == 0) {
+    // ================================================ TMA producer ================================================
+    if (lane == 0) {
+      mbar_arrive_expect_tx(q_full, kTileBytes);
+      tma_load_3d(sQ, &tmQKV, q_full, h * kHD, qt * kTile, b);
+      for (int j = 0; j < nkv; ++j) {
+        const int s = j & 1;
+        const uint32_t ph = (j >> 1) & 1;
+        mbar_wait(&k_empty[s], ph ^ 1u, 0x500u + s);
+        mbar_arrive_expect_tx(&k_full[s], kTileBytes);
+        tma_load_3d(sK + s * kTileBytes, &tmQKV, &k_full[s], p.C + h * kHD, j * kTile, b);
+        mbar_wait(&v_empty[s], ph ^ 1u, 0x510u + s);
+        mbar_arrive_expect_tx(&v_full[s], kTileBytes);
+        tma_load_3d(sV + s * kTileBytes, &tmQKV, &v_full[s], 2 * p.C + h * kHD, j * kTile, b);
+      }
+    }
+  } else if (warp == 1) {
+    // ================================================ MMA issuer ==================================================
+    if (lane == 0) {
+      const uint32_t idesc_qk = make_idesc(true, false, false, kTile, kTile);   // S[128 q][128 kv]
+      const uint32_t idesc_pv = make_idesc(true, false, true, kTile, kHD);      // O[128 q][64], V is MN-major
+      const uint32_t aQ = smem_u32(sQ);
+      mbar_wait(q_full, 0, 0x520u);
+      for (int j = 0; j <= nkv; ++j) {
+        if (j < nkv) mbar_wait(&k_full[j & 1], (j >> 1) & 1, 0x530u + (j & 1));
+        if (j > 0) {
+          // O += P(j-1) V(j-1): the softmax warps have finished reading S and writing P
+          const int jp = j - 1;
+          mbar_wait(p_full, jp & 1, 0x540u);
+          mbar_wait(&v_full[jp & 1], (jp >> 1) & 1, 0x550u + (jp & 1));
+          tc_fence_after();
+          const uint32_t aV = smem_u32(sV + (jp & 1) * kTileBytes);
+#pragma unroll
+          for (int kk = 0; kk < kTile / 16; ++kk)
+            tc_mma_ts_bf16(tmem + kColO, tmem + kColP + kk * 8, desc_mnmajor(aV, kk), idesc_pv, (jp > 0 || kk > 0) ? 1u : 0u);
+          tc_commit(&v_empty[jp & 1]);
+        }
+        if (j < nkv) {
+          tc_fence_after();
+          const uint32_t aK = smem_u32(sK + (j & 1) * kTileBytes);
+#pragma unroll
+          for (int kk = 0; kk < kHD / 16; ++kk)
+            tc_mma<true>(tmem + kColS, desc_kmajor(aQ, kk), desc_kmajor(aK, kk), idesc_qk, kk > 0 ? 1u : 0u);
+          tc_commit(&k_empty[j & 1]);
+          tc_commit(s_full);            // also covers the P V MMAs issued just before: O is stable when S is ready
+        } else {
+          tc_commit(o_done);
+        }
+      }
+    }
+  } else {
+    // ================================================ softmax =====================================================
+    const int quarter = warp & 3;
+    const int r = quarter * 32 + lane;                  // row inside the tile == TMEM lane
+    const uint32_t lane_base = static_cast<uint32_t>(quarter * 32) << 16;
+    const uint32_t tS = tmem + lane_base + kColS, tP = tmem + lane_base + kColP, tO = tmem + lane_base + kColO;
+    const float sl2 = p.scale_log2;
+    float m = -INFINITY, l = 0.f;                       // running maximum (raw scores) and sum
+    for (int j = 0; j < nkv; ++j) {
+      mbar_wait(s_full, j & 1, 0x560u);
+      tc_fence_after();
+      const bool diag = (j == qt);                      // only the last block crosses the diagonal
+      float mx = -INFINITY;
+#pragma unroll 1
+      for (int c = 0; c < 4; ++c) {
+        uint32_t v[32];
+        tmem_ld_32x32(tS + c * 32, v);
+        tmem_ld_wait();
+        if (diag) {
+#pragma unroll
+          for (int i = 0; i < 32; ++i) if (c * 32 + i <= r) mx = fmaxf(mx, __uint_as_float(v[i]));
+        } else {
+#pragma unroll
+          for (int i = 0; i < 32; ++i) mx = fmaxf(mx, __uint_as_float(v[i]));
+        }
+      }
+      const float m_new = fmaxf(m, mx);
+      if (j > 0) {
+        // the previous blocks were accumulated relative to the old maximum: rescale the sum and (only if some row of
+        // this warp moved) the output accumulator
+        const float alpha = ex2((m - m_new) * sl2);
+        l *= alpha;
+        if (__any_sync(0xffffffffu, m_new > m)) {
+#pragma unroll 1
+          for (int c = 0; c < 2; ++c) {
+            uint32_t o[32];
+            tmem_ld_32x32(tO + c * 32, o);
+            tmem_ld_wait();
+#pragma unroll
+            for (int i = 0; i < 32; ++i) o[i] = __float_as_uint(__uint_as_float(o[i]) * alpha);
+            tmem_st_32x32(tO + c * 32, o);
+          }
+        }
+      }
+      m = m_new;
+      const float moff = m * sl2;
+#pragma unroll 1
+      for (int c = 0; c < 4; ++c) {
+        uint32_t v[32];
+        tmem_ld_32x32(tS + c * 32, v);
+        tmem_ld_wait();
+        uint32_t pk[16];
+#pragma unroll
+        for (int i = 0; i < 32; i += 2) {
+          float p0 = ex2(fmaf(__uint_as_float(v[i]), sl2, -moff));
+          float p1 = ex2(fmaf(__uint_as_float(v[i + 1]), sl2, -moff));
+          if (diag) {
+            if (c * 32 + i > r) p0 = 0.f;
+            if (c * 32 + i + 1 > r) p1 = 0.f;
+          }
+          l += p0 + p1;
+          pk[i >> 1] = pack_bf16(p0, p1);
+        }
+        tmem_st_32x16(tP + c * 16, pk);
+      }
+      tmem_st_wait();
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(p_full);
+    }
+    // ---- epilogue: O / l -> bf16, log-sum-exp
+    mbar_wait(o_done, 0, 0x570u);
+    tc_fence_after();
+    const int q = qt * kTile + r;
+    const float inv = 1.f / l;
+    uint4 ov[8];
+#pragma unroll
+    for (int c = 0; c < 2; ++c) {
+      uint32_t o[32];
+      tmem_ld_32x32(tO + c * 32, o);
+      tmem_ld_wait();
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        ov[c * 4 + i].x = pack_bf16(__uint_as_float(o[8 * i]) * inv, __uint_as_float(o[8 * i + 1]) * inv);
+        ov[c * 4 + i].y = pack_bf16(__uint_as_float(o[8 * i + 2]) * inv, __uint_as_float(o[8 * i + 3]) * inv);
+        ov[c * 4 + i].z = pack_bf16(__uint_as_float(o[8 * i + 4]) * inv, __uint_as_float(o[8 * i + 5]) * inv);
+        ov[c * 4 + i].w = pack_bf16(__uint_as_float(o[8 * i + 6]) * inv, __uint_as_float(o[8 * i + 7]) * inv);
+      }
+    }
+    if (q < p.T) {
+      uint4* dst = reinterpret_cast<uint4*>(p.out + (static_cast<long long>(b) * p.T + q) * p.C + h * kHD);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) dst[i] = ov[i];
+      p.lse2[(static_cast<long long>(b) * p.H + h) * p.Tp + q] = m * sl2 + log2f(l);
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  if (warp == 1) tmem_dealloc(tmem, 256);
+}
+
+}  // namespace ddpx
+
+// =====================================================================================================================
+// host side
+// =====================================================================================================================
+using namespace ddpx;
+
+static int attn_check(const void* qkv, int B, int T, int H) {
+  if (B < 1 || T < 1 || H < 1) return DDPX_ERR_ARG;
+  if (reinterpret_cast<uintptr_t>(qkv) & 15) return DDPX_ERR_ALIGN;
+  return DDPX_OK;
+}
+
+extern "C" int ddpx_attn_fwd(const void* qkv, void* out, float* lse2, int B, int T, int H, float scale, void* stream_) {
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  int rc = attn_check(qkv, B, T, H);
+  if (rc != DDPX_OK) return rc;
+  if (reinterpret_cast<uintptr_t>(out) & 15) return DDPX_ERR_ALIGN;
+  AttnParams p{};
+  p.B = B; p.T = T; p.H = H; p.C = H * kHD; p.nq = (T + kTile - 1) / kTile; p.Tp = p.nq * kTile;
+  p.scale = scale; p.scale_log2 = scale * 1.4426950408889634f;
+  p.out = static_cast<__nv_bfloat16*>(out); p.lse2 = lse2; p.qkv = static_cast<const __nv_bfloat16*>(qkv);
+  CUtensorMap tm;
+  if ((rc = attn_map(&tm, qkv, B, T, 3 * p.C)) != DDPX_OK) return rc;
+  const size_t smem = 5 * kTileBytes + 1024 + 128;
+  static bool attr_set = false;
+  if (!attr_set) {
+    if (cudaFuncSetAttribute(attn_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)) != cudaSuccess)
+      return DDPX_ERR_LAUNCH;
+    attr_set = true;
+  }
+  const long long grid = static_cast<long long>(p.nq) * B * H;
+  if (grid > 0x7fffffffLL) return DDPX_ERR_SHAPE;
+  attn_fwd_kernel<<<static_cast<unsigned>(grid), kFwdThreads, smem, stream>>>(tm, p);
+  return cudaGetLastError() == cudaSuccess ? DDPX_OK : DDPX_ERR_LAUNCH;
+}
+
+// bounded waits of this translation unit report here (the error word is per translation unit)
+extern "C" unsigned int ddpx_attn_read_error_word(void) {
+  unsigned int v = 0;
+  cudaMemcpyFromSymbol(&v, g_ddpx_error_word, sizeof(v));
+  return v;
+}

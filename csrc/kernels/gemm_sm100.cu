@@ -21,6 +21,8 @@
 #include <stdio.h>
 #include <stdlib.h>
 #include <mutex>
+#include <string.h>
+#include "tmap.hpp"
 
 namespace ddpx {
 
@@ -523,9 +525,37 @@ static PFN_cuTensorMapEncodeTiled_v12000 get_encode_fn() {
   return fn;
 }
 
-// rank-N tiled map with 128B swizzle; dims/strides innermost first; strides in bytes for dims 1..rank-1
-static int make_tmap(CUtensorMap* out, const void* base, bool bf16, int rank, const uint64_t* dims,
-                     const uint64_t* strides_bytes, const uint32_t* box, bool atom32 = false) {
+// rank-N tiled map with 128B swizzle; dims/strides innermost first; strides in bytes for dims 1..rank-1.
+// Encoded maps are cached (key: base pointer, type, rank, extents, strides, box, swizzle flavour): a training step asks
+// for the same few hundred maps every iteration, and cuTensorMapEncodeTiled was a visible part of the per-call host time
+// (profiles/probe_findings.md section 9).  A map depends only on its key, so a stale entry cannot exist.
+struct TmapKey {
+  uint64_t base; uint64_t dims[5]; uint64_t strides[4]; uint32_t box[5]; int rank; int flags;
+  bool operator==(const TmapKey& o) const { return memcmp(this, &o, sizeof(TmapKey)) == 0; }
+};
+struct TmapEntry { TmapKey key; CUtensorMap map; bool valid; };
+constexpr int kTmapCacheSize = 8192;     // direct-mapped
+static TmapEntry* g_tmap_cache = nullptr;
+static std::mutex g_tmap_mutex;
+static unsigned long long g_tmap_hits = 0, g_tmap_misses = 0;
+
+int make_tmap(CUtensorMap* out, const void* base, bool bf16, int rank, const uint64_t* dims,
+              const uint64_t* strides_bytes, const uint32_t* box, bool atom32) {
+  TmapKey key;
+  memset(&key, 0, sizeof(key));
+  key.base = reinterpret_cast<uint64_t>(base); key.rank = rank; key.flags = (bf16 ? 1 : 0) | (atom32 ? 2 : 0);
+  for (int i = 0; i < rank; ++i) { key.dims[i] = dims[i]; key.box[i] = box[i]; }
+  for (int i = 0; i < rank - 1; ++i) key.strides[i] = strides_bytes[i];
+  uint64_t h = 1469598103934665603ull;
+  const uint64_t* w = reinterpret_cast<const uint64_t*>(&key);
+  for (size_t i = 0; i < sizeof(TmapKey) / 8; ++i) { h ^= w[i]; h *= 1099511628211ull; h ^= h >> 29; }
+  const int slot = static_cast<int>(h % kTmapCacheSize);
+  {
+    std::lock_guard<std::mutex> g(g_tmap_mutex);
+    if (!g_tmap_cache) g_tmap_cache = static_cast<TmapEntry*>(calloc(kTmapCacheSize, sizeof(TmapEntry)));
+    TmapEntry& e = g_tmap_cache[slot];
+    if (e.valid && e.key == key) { *out = e.map; ++g_tmap_hits; return DDPX_OK; }
+  }
   auto fn = get_encode_fn();
   if (!fn) return DDPX_ERR_DRIVER;
   cuuint64_t gdim[5];
@@ -541,11 +571,16 @@ static int make_tmap(CUtensorMap* out, const void* base, bool bf16, int rank, co
     fprintf(stderr, "[ddpx] cuTensorMapEncodeTiled failed: %d (rank %d)\n", static_cast<int>(r), rank);
     return DDPX_ERR_TMAP;
   }
+  {
+    std::lock_guard<std::mutex> g(g_tmap_mutex);
+    TmapEntry& e = g_tmap_cache[slot];
+    e.key = key; e.map = *out; e.valid = true; ++g_tmap_misses;
+  }
   return DDPX_OK;
 }
 
 static int g_num_sms = 0;
-static int num_sms() {
+int num_sms() {
   if (g_num_sms == 0) {
     int dev = 0;
     cudaGetDevice(&dev);

@@ -368,3 +368,21 @@ def causal_softmax_fwd(s, rows, T):
 
 def causal_softmax_bwd(p, dp, rows, T, scale):
     _call("ddpx_causal_softmax_bwd", _P(p), _P(dp), c_longlong(rows), c_int(T), c_float(scale), c_int(_bf(p)), _st())
+
+
+# ------------------------------------------------------------------------------------------------ fused causal attention
+def attn_fwd(qkv, out, lse2, B, T, H, scale):
+    """Flash-style causal attention forward: qkv [B,T,3*H*64] bf16 -> out [B,T,H*64] bf16, lse2 [B,H,T] fp32."""
+    _call("ddpx_attn_fwd", _P(qkv), _P(out), _P(lse2), c_int(B), c_int(T), c_int(H), c_float(scale), _st())
+
+
+def attn_bwd(qkv, out, dout, lse2, delta, dqkv, B, T, H, scale):
+    """Backward of attn_fwd: writes dqkv [B,T,3C] (dq | dk | dv); delta [B,H,T] fp32 is scratch."""
+    _call("ddpx_attn_bwd", _P(qkv), _P(out), _P(dout), _P(lse2), _P(delta), _P(dqkv), c_int(B), c_int(T), c_int(H),
+          c_float(scale), _st(), launches=3)
+
+
+def attn_error_word() -> int:
+    fn = _lib.lib().ddpx_attn_read_error_word
+    fn.restype = ctypes.c_uint
+    return int(fn())
