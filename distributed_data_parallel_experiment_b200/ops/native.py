@@ -383,6 +383,9 @@ def attn_bwd(qkv, out, dout, lse2, delta, dqkv, B, T, H, scale):
 
 
 def attn_error_word() -> int:
-    fn = _lib.lib().ddpx_attn_read_error_word
-    fn.restype = ctypes.c_uint
-    return int(fn())
+    v = 0
+    for name in ("ddpx_attn_read_error_word", "ddpx_attn_bwd_read_error_word"):
+        fn = getattr(_lib.lib(), name)
+        fn.restype = ctypes.c_uint
+        v |= int(fn())
+    return v

@@ -9,7 +9,11 @@ import math
 import torch
 from torch.autograd import Function
 
+import os
+
 from . import native
+
+_FLASH = os.environ.get("DDPX_FLASH_ATTN", "1") not in ("0", "")     # A/B switch: 0 = materialised-score path
 
 
 def _zeros(shape, device, dtype=torch.float32):
@@ -88,9 +92,11 @@ class EmbeddingSumFn(Function):
 class CausalAttentionFn(Function):
     """softmax(causal(Q K^T / sqrt(d))) V from a packed qkv [B,T,3C] tensor.
 
-    Three stages, all on the framework's kernels: batched tcgen05 GEMM for the scores (tiles above the diagonal are
-    never computed), a causal softmax in place, batched tcgen05 GEMM for P V (K loop cut at the diagonal).  The
-    probabilities are kept for the backward, which is four more batched GEMMs around the softmax backward.
+    bf16 with 64-wide heads (every GPT-2 size): ONE fused tcgen05 kernel forward (scores and probabilities never leave
+    tensor memory; output + per-row log-sum-exp) and two fused kernels backward that recompute the probabilities
+    (csrc/kernels/attn_sm100.cu, attn_bwd_sm100.cu) - no [B,H,T,T] tensor exists.
+    Other head sizes / fp32: batched tcgen05 GEMM for the scores (tiles above the diagonal are never computed), a causal
+    softmax in place, batched GEMM for P V; the probabilities are kept for a backward of four more batched GEMMs.
     """
 
     @staticmethod
@@ -100,6 +106,16 @@ class CausalAttentionFn(Function):
         hd = C // n_head
         q3 = qkv if qkv.is_contiguous() else qkv.contiguous()
         scale = 1.0 / math.sqrt(hd)
+        if hd == 64 and qkv.dtype == torch.bfloat16 and _FLASH:
+            Tp = (T + 127) // 128 * 128
+            out = torch.empty((B, T, C), device=qkv.device, dtype=qkv.dtype)
+            lse2 = torch.empty((B, n_head, Tp), device=qkv.device, dtype=torch.float32)
+            native.attn_fwd(q3, out, lse2, B, T, n_head, scale)
+            ctx.save_for_backward(q3, out, lse2)
+            ctx.cfg = (B, T, C, n_head, hd, scale)
+            ctx.flash = True
+            return out
+        ctx.flash = False
         BH = B * n_head
         P = torch.empty((B, n_head, T, T), device=qkv.device, dtype=qkv.dtype)
         q = q3.view(-1)
@@ -120,10 +136,16 @@ class CausalAttentionFn(Function):
 
     @staticmethod
     def backward(ctx, dout):
-        q3, P = ctx.saved_tensors
         B, T, C, n_head, hd, scale = ctx.cfg
-        C3 = 3 * C
         do = dout if dout.is_contiguous() else dout.contiguous()
+        if ctx.flash:
+            q3, out, lse2 = ctx.saved_tensors
+            dqkv = torch.empty_like(q3)
+            delta = torch.empty_like(lse2)
+            native.attn_bwd(q3, out, do, lse2, delta, dqkv, B, T, n_head, scale)
+            return dqkv, None
+        q3, P = ctx.saved_tensors
+        C3 = 3 * C
         flat = q3.view(-1)
         q, k, v = flat, flat[C:], flat[2 * C:]
         dqkv = torch.empty_like(q3)

@@ -24,6 +24,7 @@ def _dev():
     yield
     torch.cuda.synchronize()
     assert native.read_error_word() == 0
+    assert native.attn_error_word() == 0
 
 
 @pytest.mark.parametrize("dtype,tol", [(torch.float32, 1e-5), (torch.bfloat16, 2e-2)])
@@ -56,7 +57,7 @@ def test_linear_gelu(dtype, tol):
 
 
 @pytest.mark.parametrize("dtype,tol", [(torch.float32, 5e-3), (torch.bfloat16, 3e-2)])
-@pytest.mark.parametrize("B,T,H,hd", [(2, 128, 2, 64), (2, 256, 4, 64), (1, 1024, 2, 64)])
+@pytest.mark.parametrize("B,T,H,hd", [(2, 128, 2, 64), (2, 256, 4, 64), (1, 1024, 2, 64), (2, 200, 3, 64), (1, 128, 2, 32)])
 def test_causal_attention(dtype, tol, B, T, H, hd):
     torch.manual_seed(2)
     C = H * hd
@@ -71,6 +72,26 @@ def test_causal_attention(dtype, tol, B, T, H, hd):
     yr.backward(g.double())
     assert rel_l2(y, yr) < tol
     assert rel_l2(qkv.grad, qr.grad) < tol
+    C1 = H * hd          # each of dq / dk / dv on its own (a wrong third would hide inside the norm of the whole)
+    for part in range(3):
+        assert rel_l2(qkv.grad[..., part * C1:(part + 1) * C1], qr.grad[..., part * C1:(part + 1) * C1]) < tol
+
+
+def test_flash_attention_matches_materialised_path(monkeypatch):
+    """The fused kernels against the older batched-GEMM + softmax path on the same bf16 inputs."""
+    from distributed_data_parallel_experiment_b200.ops import transformer as TR
+    torch.manual_seed(5)
+    B, T, H = 2, 384, 4
+    qkv = torch.randn(B, T, 3 * H * 64, device="cuda").bfloat16()
+    g = torch.randn(B, T, H * 64, device="cuda").bfloat16()
+    res = []
+    for flash in (True, False):
+        monkeypatch.setattr(TR, "_FLASH", flash)
+        x = qkv.clone().requires_grad_()
+        y = FX.causal_attention(x, H)
+        y.backward(g)
+        res.append((y.detach(), x.grad))
+    assert rel_l2(res[0][0], res[1][0]) < 2e-2 and rel_l2(res[0][1], res[1][1]) < 3e-2
 
 
 def test_embedding_sum_and_padded_ce():
