@@ -83,28 +83,30 @@ class TorchGPT2(nn.Module):
         return F.linear(self.ln_f(x), self.wte.weight)
 
 
-# ---------------------------------------------------------------------------------------------- worker
-def worker(rank, world, port, args):
-    os.environ["MASTER_ADDR"] = "127.0.0.1"; os.environ["MASTER_PORT"] = str(port)
+# ---------------------------------------------------------------------------------------------- one arm
+def _pin(t):
+    return t.pin_memory() if torch.cuda.is_available() else t
+
+
+def run_arm(config: str, impl: str, rank: int, world: int, steps: int, warmup: int, e2e: bool = False) -> dict:
+    """Time `steps` optimizer steps of `config` on the calling rank's GPU (process group already set up by the caller:
+    ddpx.ddp_setup / setup_from_env for impl='ours', any NCCL group for impl='torch').  Device-timed, max over ranks.
+    With e2e=True the same steps are timed again with every micro-batch copied from pinned host memory and the loss
+    read back to the host (ours: Trainer.train_stream; torch: .to(device) / .item())."""
     import distributed_data_parallel_experiment_b200 as ddpx
     from distributed_data_parallel_experiment_b200 import _lib
     from distributed_data_parallel_experiment_b200.ops import functional as FX
-    cfg = CONFIGS[args.config]
-    torch.cuda.set_device(rank)
-    if world > 1:
-        if args.impl == "ours":
-            ddpx.ddp_setup(rank, world, backend="p2p")
-        else:
-            dist.init_process_group("nccl", rank=rank, world_size=world)
+    cfg = CONFIGS[config]
     torch.manual_seed(1 + rank)
     dtype = torch.bfloat16
     accum = cfg.get("accum", 1)
+    g = torch.Generator().manual_seed(100 + rank)
     if cfg["kind"] == "mlp":
         W, B = cfg["width"], cfg["batch"]
-        xs = [torch.randn(B, W, device="cuda").to(dtype) for _ in range(4)]
-        ys = [torch.randint(0, W, (B,), device="cuda") for _ in range(4)]
+        hxs = [_pin(torch.randn(B, W, generator=g).to(dtype)) for _ in range(4)]
+        hys = [_pin(torch.randint(0, W, (B,), generator=g)) for _ in range(4)]
         unit, per_step = "samples/s", B * world
-        if args.impl == "ours":
+        if impl == "ours":
             model = ddpx.models.MLP(W, W, cfg["depth"], W, dtype=dtype).cuda()
             loss_fn = ddpx.ops.cross_entropy
         else:
@@ -114,57 +116,118 @@ def worker(rank, world, port, args):
     else:
         gcfg = getattr(ddpx.models.GPT2Config, cfg["size"])()
         B, T = cfg["batch"], min(cfg["seq"], gcfg.n_positions)
-        xs = [torch.randint(0, gcfg.vocab_size, (B, T), device="cuda") for _ in range(4)]
-        ys = [torch.randint(0, gcfg.vocab_size, (B, T), device="cuda") for _ in range(4)]
+        hxs = [_pin(torch.randint(0, gcfg.vocab_size, (B, T), generator=g)) for _ in range(4)]
+        hys = [_pin(torch.randint(0, gcfg.vocab_size, (B, T), generator=g)) for _ in range(4)]
         unit, per_step = "tokens/s", B * T * world * accum
-        if args.impl == "ours":
+        if impl == "ours":
             model = ddpx.models.GPT2(gcfg, dtype=dtype).cuda()
             loss_fn = lambda o, t: FX.cross_entropy_padded(o, t, gcfg.vocab_size)
         else:
             model = TorchGPT2(gcfg).cuda().to(dtype)
             loss_fn = lambda o, t: F.cross_entropy(o[..., :gcfg.vocab_size].reshape(-1, gcfg.vocab_size).float(), t.reshape(-1))
         opt = torch.optim.AdamW(model.parameters(), lr=3e-4, betas=(0.9, 0.95), weight_decay=0.1,
-                                fused=True if args.impl == "torch" else None)
+                                fused=True if impl == "torch" else None)
+    xs = [x.cuda() for x in hxs]; ys = [y.cuda() for y in hys]
     nparams = sum(p.numel() for p in model.parameters())
-    if args.impl == "ours":
-        trainer = ddpx.Trainer(model, [], opt, rank, 1, loss_fn=loss_fn, distributed=world > 1, accum_steps=accum)
+    trainer = None
+    if impl == "ours":
+        trainer = ddpx.Trainer(model, [], opt, torch.cuda.current_device(), 1, loss_fn=loss_fn, distributed=world > 1,
+                               accum_steps=accum)
         step = lambda i: trainer._run_batch(xs[i % 4], ys[i % 4])
     else:
-        net = nn.parallel.DistributedDataParallel(model, device_ids=[rank]) if world > 1 else model
+        net = nn.parallel.DistributedDataParallel(model, device_ids=[torch.cuda.current_device()]) if world > 1 else model
         micro = {"i": 0}
+        import contextlib
 
-        def step(i):
+        def step(i, x=None, y=None):
             last = (micro["i"] + 1) % accum == 0
             if micro["i"] % accum == 0:
                 opt.zero_grad()
-            import contextlib
             ctx = net.no_sync() if (world > 1 and not last) else contextlib.nullcontext()
             with ctx:
-                (loss_fn(net(xs[i % 4]), ys[i % 4]) / accum).backward()
+                loss = loss_fn(net(xs[i % 4] if x is None else x), ys[i % 4] if y is None else y)
+                (loss / accum).backward()
             micro["i"] += 1
             if last:
                 opt.step()
-    n_calls = args.steps * accum
-    for i in range(args.warmup * accum):
+            return loss
+
+    def bracket(fn):
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize()
+        e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
+        e0.record()
+        fn()
+        e1.record(); torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1)
+        if world > 1:
+            t = torch.tensor([ms], device="cuda", dtype=torch.float64); dist.all_reduce(t, op=dist.ReduceOp.MAX); ms = float(t.item())
+        return ms
+
+    n_calls = steps * accum
+    for i in range(warmup * accum):
         step(i)
-    torch.cuda.synchronize()
-    if world > 1:
-        dist.barrier()
     l0 = _lib.launches()
-    e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
-    e0.record()
-    for i in range(n_calls):
-        step(i)
-    e1.record(); torch.cuda.synchronize()
-    ms = e0.elapsed_time(e1)
+    ms = bracket(lambda: [step(i) for i in range(n_calls)])
+    launches = _lib.launches() - l0
+    out = {"config": config, "impl": impl, "n_gpus": world, "value": per_step * steps / (ms / 1e3), "unit": unit,
+           "ms_per_step": ms / steps, "params": nparams, "dtype": "bf16", "gpu_launches": launches,
+           "global_batch": cfg["batch"] * world, "seq_len": cfg.get("seq"), "accum": accum,
+           "approx_model_tflops_per_gpu": 6.0 * nparams * per_step * steps / (ms / 1e3) / world / 1e12,
+           "max_mem_gb": torch.cuda.max_memory_allocated() / 2 ** 30}
+    if e2e:
+        if impl == "ours":
+            def e2e_run(n):
+                losses = list(trainer.train_stream((hxs[i % 4], hys[i % 4]) for i in range(n)))
+                assert len(losses) == n and all(l == l for l in losses)
+                return losses
+            e2e_run(accum)
+            holder = {}
+            ems = bracket(lambda: holder.setdefault("l", e2e_run(n_calls)))
+            out["loss"] = holder["l"][-1]
+        else:
+            def e2e_run(n):
+                last = None
+                for i in range(n):
+                    x = hxs[i % 4].to("cuda", non_blocking=True); y = hys[i % 4].to("cuda", non_blocking=True)
+                    last = float(step(i, x, y).item())
+                return last
+            e2e_run(accum)
+            holder = {}
+            ems = bracket(lambda: holder.setdefault("l", e2e_run(n_calls)))
+            out["loss"] = holder["l"]
+        out["e2e_value"] = per_step * steps / (ems / 1e3)
+        out["e2e_ms_per_step"] = ems / steps
+        out["h2d_bytes_per_step"] = (hxs[0].numel() * hxs[0].element_size() + hys[0].numel() * hys[0].element_size()) * accum
+        out["d2h_bytes_per_step"] = 4 * accum
+    if impl == "ours" and world > 1:
+        from distributed_data_parallel_experiment_b200.utils import debug as _debug
+        out["replicas_in_sync"] = bool(_debug.replicas_in_sync(model.parameters()))
+    # drop the arm's memory before the next one runs in this process
+    del model, opt, xs, ys
+    if trainer is not None:
+        if hasattr(trainer.model, "close"):
+            trainer.model.close()
+        del trainer
+    import gc
+    gc.collect(); torch.cuda.empty_cache()
+    return out
+
+
+def worker(rank, world, port, args):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"; os.environ["MASTER_PORT"] = str(port)
+    import distributed_data_parallel_experiment_b200 as ddpx
+    torch.cuda.set_device(rank)
     if world > 1:
-        t = torch.tensor([ms], device="cuda", dtype=torch.float64); dist.all_reduce(t, op=dist.ReduceOp.MAX); ms = float(t.item())
+        if args.impl == "ours":
+            ddpx.ddp_setup(rank, world, backend="p2p")
+        else:
+            dist.init_process_group("nccl", rank=rank, world_size=world)
+    out = run_arm(args.config, args.impl, rank, world, args.steps, args.warmup, e2e=args.e2e)
     if rank == 0:
-        flops = 6.0 * nparams * (per_step if cfg["kind"] == "gpt2" else per_step) * args.steps / (ms / 1e3) / world
-        print(json.dumps({"config": args.config, "impl": args.impl, "n_gpus": world, "value": per_step * args.steps / (ms / 1e3),
-                          "unit": unit, "ms_per_step": ms / args.steps, "params": nparams, "dtype": "bf16",
-                          "approx_model_tflops_per_gpu": flops / 1e12, "gpu_launches": _lib.launches() - l0,
-                          "max_mem_gb": torch.cuda.max_memory_allocated() / 2 ** 30}), flush=True)
+        print(json.dumps(out), flush=True)
     if world > 1:
         if args.impl == "ours":
             ddpx.teardown()
@@ -179,6 +242,7 @@ def main():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--e2e", action="store_true", help="also time the steps end to end (pinned H2D every micro-batch, loss read back)")
     args = ap.parse_args()
     s = socket.socket(); s.bind(("127.0.0.1", 0)); port = s.getsockname()[1]; s.close()
     if args.gpus == 1:

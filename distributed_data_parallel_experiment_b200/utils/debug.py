@@ -58,3 +58,21 @@ def assert_replicas_in_sync(params: Iterable[torch.Tensor], comm, step: int) -> 
         if other != everyone[0]:
             raise RuntimeError(f"replica divergence at step {step}: rank {r} checksums {other} != rank 0 {everyone[0]}")
     return mine
+
+
+def replicas_in_sync(params: Iterable[torch.Tensor], tol: float = 0.0) -> bool:
+    """True when every rank's fp64 parameter checksums agree (collective over torch.distributed's default group; a
+    single process is trivially in sync).  The P2P backend reduces every element exactly once in one order on one rank,
+    so its replicas are bit-identical and ``tol`` stays 0; NCCL-style reductions may need a relative tolerance."""
+    import torch.distributed as dist
+    mine = replica_checksums(params)
+    if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size() == 1:
+        return True
+    everyone = [None] * dist.get_world_size()
+    dist.all_gather_object(everyone, mine)
+    ref = everyone[0]
+    for other in everyone:
+        for a, b in zip(other, ref):
+            if a != b and not (abs(a - b) <= tol * max(abs(a), abs(b), 1e-300)):
+                return False
+    return True
