@@ -36,21 +36,60 @@ NUM_CLASSES = 10
 # clocks sampler (B200_PROFILING.md "clocks DURING the timed region")
 # ------------------------------------------------------------------------------------------------
 class ClockSampler:
+    """SM clock / power / throttle reasons DURING the timed region.  NVML is polled from a thread every ~4 ms (a 20-step
+    timed region is ~0.1 s: `nvidia-smi -lms` gave it one or two samples); nvidia-smi is the fallback."""
     FIELDS = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
               "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
               "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+    # nvmlClocksEventReason* bit masks
+    R_SW_POWER_CAP, R_HW_SLOWDOWN, R_SW_THERMAL, R_HW_THERMAL = 0x4, 0x8, 0x20, 0x40
 
     def __init__(self, gpu_index: int = 0):
         self.gpu_index = gpu_index
         self.proc = None
         self.lines: list[str] = []
         self.thread = None
+        self.samples = []          # (sm_mhz, power_w, reasons_mask)
+        self.smax = None
+        self._stop = False
+        self.mode = None
+
+    def _nvml_loop(self, nv, h):
+        get_reasons = getattr(nv, "nvmlDeviceGetCurrentClocksEventReasons", None) or nv.nvmlDeviceGetCurrentClocksThrottleReasons
+        while not self._stop:
+            try:
+                sm = nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM)
+                pw = nv.nvmlDeviceGetPowerUsage(h) / 1000.0
+                rs = int(get_reasons(h))
+                self.samples.append((float(sm), pw, rs))
+            except Exception:
+                pass
+            time.sleep(0.004)
 
     def start(self):
         try:
+            import pynvml as nv
+            nv.nvmlInit()
+            # NVML enumerates physical devices: honour CUDA_VISIBLE_DEVICES when it is a plain index list
+            idx = self.gpu_index
+            vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+            if vis:
+                parts = [x.strip() for x in vis.split(",") if x.strip()]
+                if idx < len(parts) and parts[idx].isdigit():
+                    idx = int(parts[idx])
+            h = nv.nvmlDeviceGetHandleByIndex(idx)
+            self.smax = float(nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM))
+            self.mode = "nvml"
+            self.thread = threading.Thread(target=self._nvml_loop, args=(nv, h), daemon=True)
+            self.thread.start()
+            return
+        except Exception:
+            self.mode = None
+        try:
             self.proc = subprocess.Popen(
                 ["nvidia-smi", f"--id={self.gpu_index}", f"--query-gpu={self.FIELDS}", "--format=csv,noheader,nounits",
-                 "-lms", "50"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+                 "-lms", "20"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.mode = "smi"
         except Exception:
             self.proc = None
             return
@@ -61,6 +100,20 @@ class ClockSampler:
         self.thread.start()
 
     def stop(self) -> dict:
+        if self.mode == "nvml":
+            self._stop = True
+            self.thread.join(timeout=1)
+            if not self.samples:
+                return {"sm_mhz": None, "sm_max_mhz": self.smax, "reasons": ["no samples"]}
+            sm = sorted(x[0] for x in self.samples)
+            mask = 0
+            for x in self.samples:
+                mask |= x[2]
+            reasons = [n for n, bit in (("hw_slowdown", self.R_HW_SLOWDOWN), ("hw_thermal_slowdown", self.R_HW_THERMAL),
+                                        ("sw_thermal_slowdown", self.R_SW_THERMAL), ("sw_power_cap", self.R_SW_POWER_CAP))
+                       if mask & bit]
+            return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": self.smax, "power_w_max": max(x[1] for x in self.samples),
+                    "samples": len(sm), "source": "nvml", "reasons": sorted(reasons)}
         if self.proc is None:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
         self.proc.terminate()
@@ -84,7 +137,7 @@ class ClockSampler:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no samples"]}
         sm.sort()
         return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": max(smax), "power_w_max": max(power), "samples": len(sm),
-                "reasons": sorted(reasons)}
+                "source": "nvidia-smi", "reasons": sorted(reasons)}
 
 
 # ------------------------------------------------------------------------------------------------
@@ -109,6 +162,15 @@ def make_host_batches(n: int, batch: int, seed: int):
             x = x.pin_memory(); y = y.pin_memory()
         xs.append(x); ys.append(y)
     return xs, ys
+
+
+def sync_report(params, loss_value, world: int) -> dict:
+    """Driver-visible correctness at N > 1: every rank's fp64 parameter checksums must agree after the timed steps.
+    Returns the keys to merge into the JSON line; the caller exits non-zero when replicas diverged."""
+    from distributed_data_parallel_experiment_b200.utils import debug as _debug
+    ok = bool(_debug.replicas_in_sync(list(params)))
+    cs = _debug.replica_checksums(list(params))
+    return {"replicas_in_sync": ok if world > 1 else None, "param_checksum": cs[0], "loss": loss_value}
 
 
 def max_over_ranks(ms: float, world: int) -> float:
@@ -158,7 +220,7 @@ def timed_block(fn, world: int) -> float:
     return max_over_ranks(ms, world)
 
 
-def emit(args, world, impl, total_ms, e2e_ms, h2d, d2h, launches, clocks, extra_cfg):
+def emit(args, world, impl, total_ms, e2e_ms, h2d, d2h, launches, clocks, detail, top=None):
     global_batch = BATCH_PER_GPU * world
     value = global_batch * args.steps / (total_ms / 1e3)
     e2e_value = global_batch * args.steps / (e2e_ms / 1e3) if e2e_ms else None
@@ -173,14 +235,15 @@ def emit(args, world, impl, total_ms, e2e_ms, h2d, d2h, launches, clocks, extra_
         "config": {"model": "VGG (reference multigpu.py:36-71, 9.23M params)", "global_batch": global_batch,
                    "batch_per_gpu": BATCH_PER_GPU, "seq_len": None, "image": "3x32x32",
                    "parallelism": f"dp{world}", "optimizer": "SGD lr0.4 m0.9 wd5e-4 + LambdaLR per step",
-                   "l2": "per-step working set (~2.5 GB of activations) exceeds the 126 MB L2; 4 distinct input batches rotate",
-                   **extra_cfg},
+                   "l2": "per-step working set (~2.5 GB of activations) exceeds the 126 MB L2; 4 distinct input batches rotate"},
+        "detail": detail,
         "clocks": clocks,
         "e2e": {"value": round(e2e_value, 1) if e2e_value else None, "unit": "samples/s",
                 "ms_per_step": round(e2e_ms / args.steps, 4) if e2e_ms else None,
                 "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
         "gpu_launches": launches,
     }
+    out.update(top or {})
     print(json.dumps(out), flush=True)
 
 
@@ -260,10 +323,14 @@ def run_reference(args):
     for i in range(2):
         e2e_step(i)
     e2e_ms = timed_loop(e2e_step, args.steps, world)
+    with torch.no_grad():
+        ref_model = trainer.model.module if world > 1 else trainer.model
+        ref_loss = float(torch.nn.functional.cross_entropy(trainer.model(dxs[0]), dys[0]).item())
+    rep = sync_report(ref_model.parameters(), ref_loss, world)
     if rank == 0:
         h2d = xs[0].numel() * 4 + ys[0].numel() * 8
         emit(args, world, "reference", total_ms, e2e_ms, h2d, 4, 0, clocks,
-             {"stack": "torch DDP + NCCL + cuDNN/cuBLAS" if world > 1 else "torch eager + cuDNN/cuBLAS"})
+             {"stack": "torch DDP + NCCL + cuDNN/cuBLAS" if world > 1 else "torch eager + cuDNN/cuBLAS"}, top=rep)
     if world > 1:
         ref.destroy_process_group()
 
@@ -339,9 +406,161 @@ def run_ours(args):
             dist.all_reduce(ex_t, op=dist.ReduceOp.MAX)
             extra["exposed_comm_ms_per_step"] = round(float(ex_t.item()), 4)
             extra["exposed_comm_frac_of_step"] = round(float(ex_t.item()) / (total_ms / args.steps), 4)
+    last_loss = float(trainer.last_loss.item()) if trainer.last_loss is not None else None
+    inner = trainer.model.module if hasattr(trainer.model, "module") else trainer.model
+    rep = sync_report(inner.parameters(), last_loss, world)
     if rank == 0:
         h2d = xs[0].numel() * 4 + ys[0].numel() * 8
-        emit(args, world, "ddpx_b200", total_ms, e2e_ms, h2d, 4, launches, clocks, extra)
+        emit(args, world, "ddpx_b200", total_ms, e2e_ms, h2d, 4, launches, clocks, extra, top=rep)
+    if world > 1:
+        ddpx.launch.teardown()
+    if world > 1 and rep["replicas_in_sync"] is False:
+        raise SystemExit("replicas diverged: parameter checksums differ between ranks")
+    if last_loss is None or last_loss != last_loss:
+        raise SystemExit("training loss is NaN")
+
+
+# ------------------------------------------------------------------------------------------------
+# the other BASELINE.json configurations (the reference, a CNN script, cannot run them: the bar is its *stack* -
+# torch modules + torch DDP + NCCL + cuBLAS / SDPA - measured in the same process tree)
+# ------------------------------------------------------------------------------------------------
+LM_CONFIGS = {"mlp": "mlp", "gpt2": "gpt2-small", "gpt2-xl": "gpt2-xl", "gpt2-tiny": "gpt2-tiny", "mlp-small": "mlp-small"}
+
+
+def run_lm(args):
+    import torch
+    sys.path.insert(0, str(REPO / "bench"))
+    import lm_bench
+    import distributed_data_parallel_experiment_b200 as ddpx
+    rank, local_rank, world = dist_env()
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device (CPU runs are covered by tests/)")
+    torch.cuda.set_device(local_rank)
+    name = LM_CONFIGS[args.config]
+    cfg = lm_bench.CONFIGS[name]
+    if world > 1:
+        ddpx.launch.setup_from_env()          # P2P backend + a torch process group (gloo / NCCL) for the torch-stack arm
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    ours = lm_bench.run_arm(name, "ours", rank, world, args.steps, args.warmup, e2e=True)
+    clocks = sampler.stop() if rank == 0 else {}
+    torch_arm = None
+    if not args.no_torch_stack:
+        try:
+            torch_arm = lm_bench.run_arm(name, "torch", rank, world, args.steps, args.warmup, e2e=True)
+        except Exception as e:      # the baseline arm must not take the product's number down with it
+            torch_arm = {"error": f"{type(e).__name__}: {e}"}
+    if rank == 0:
+        kind = cfg["kind"]
+        model = {"mlp": f"MLP {cfg.get('depth')}x{cfg.get('width')} bf16", "gpt2": f"GPT-2 {cfg.get('size')}"}[kind]
+        out = {
+            "metric": f"training throughput, {ours['unit']} ({model}, data-parallel)",
+            "value": round(ours["value"], 1), "unit": ours["unit"], "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": round(ours["ms_per_step"], 4), "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "impl": "ddpx_b200",
+            "data": "synthetic (random tokens / features, random-init weights)",
+            "config": {"model": model, "global_batch": ours["global_batch"], "seq_len": ours["seq_len"],
+                       "parallelism": f"dp{world}", "accum_steps": ours["accum"],
+                       "optimizer": "SGD momentum 0.9" if kind == "mlp" else "AdamW lr3e-4 wd0.1",
+                       "l2": "weights + activations of a step exceed the 126 MB L2; 4 distinct input batches rotate"},
+            "clocks": clocks,
+            "e2e": {"value": round(ours["e2e_value"], 1), "unit": ours["unit"], "ms_per_step": round(ours["e2e_ms_per_step"], 4),
+                    "h2d_bytes_per_step": ours["h2d_bytes_per_step"], "d2h_bytes_per_step": ours["d2h_bytes_per_step"]},
+            "gpu_launches": ours["gpu_launches"],
+            "replicas_in_sync": ours.get("replicas_in_sync"), "loss": ours.get("loss"),
+            "torch_stack_value": round(torch_arm["value"], 1) if torch_arm and "value" in torch_arm else None,
+            "torch_stack_e2e_value": round(torch_arm["e2e_value"], 1) if torch_arm and "e2e_value" in torch_arm else None,
+            "detail": {"params": ours["params"], "approx_model_tflops_per_gpu": round(ours["approx_model_tflops_per_gpu"], 1),
+                       "max_mem_gb": round(ours["max_mem_gb"], 2), "torch_stack": torch_arm,
+                       "torch_stack_is": "torch.nn modules + torch DDP + NCCL + cuBLAS / SDPA / fused AdamW, same dtype and shapes"},
+        }
+        print(json.dumps(out), flush=True)
+    if world > 1:
+        ddpx.launch.teardown()
+    if ours.get("replicas_in_sync") is False:
+        raise SystemExit("replicas diverged: parameter checksums differ between ranks")
+
+
+def run_sweep_config(args):
+    import torch
+    sys.path.insert(0, str(REPO / "bench"))
+    import allreduce_sweep
+    import distributed_data_parallel_experiment_b200 as ddpx
+    rank, local_rank, world = dist_env()
+    if world < 2:
+        print(json.dumps({"metric": "gradient all-reduce bus bandwidth", "unavailable": "needs >= 2 GPUs (--gpus 2|4|8)"}))
+        return
+    torch.cuda.set_device(local_rank)
+    ddpx.launch.setup_from_env()
+    sa = argparse.Namespace(max_mb=args.sweep_max_mb, dtype="fp32", ctas=[64], fused=True)
+    rows = allreduce_sweep.run_sweep(rank, world, sa)
+    if rank == 0:
+        top = max(r["bytes"] for r in rows)
+        best = max((r for r in rows if r["bytes"] == top and r["impl"].startswith("p2p") and "+" not in r["impl"]),
+                   key=lambda r: r["busbw_gbs"])
+        nccl = [r for r in rows if r["bytes"] == top and r["impl"] == "nccl"]
+        print(json.dumps({
+            "metric": "gradient all-reduce bus bandwidth, GB/s (largest size of the 1 KB - 1 GB sweep)",
+            "value": round(best["busbw_gbs"], 1), "unit": "GB/s", "n_gpus": world, "steps": None, "warmup": 3,
+            "higher_is_better": True, "scaling": "n/a", "vs_baseline": None, "dtype": "fp32", "impl": "ddpx_b200",
+            "data": "synthetic", "config": {"model": "all-reduce sweep", "bytes": top, "parallelism": f"dp{world}"},
+            "torch_stack_value": round(nccl[0]["busbw_gbs"], 1) if nccl else None,
+            "frac_of_900": round(best["busbw_gbs"] / 900.0, 3), "frac_of_measured_770": round(best["busbw_gbs"] / 770.0, 3),
+            "detail": {"rows": rows}}), flush=True)
+    ddpx.launch.teardown()
+
+
+def run_parity(args):
+    """4 steps of this framework and of the unmodified reference (torch DDP + NCCL at N > 1) from the same rank-0 weights
+    on the same batches: cosine and norm ratio of the two weight updates, per step loss of both."""
+    import numpy as np
+    import torch
+    import distributed_data_parallel_experiment_b200 as ddpx
+    ref_dir = REPO / "baseline" / "_ref"
+    rank, local_rank, world = dist_env()
+    if not (ref_dir / "multigpu.py").exists():
+        print(json.dumps({"mode": "parity", "unavailable": "baseline/_ref is missing (run baseline/install_ref.sh)"}))
+        return
+    sys.path.insert(0, str(ref_dir))
+    import multigpu as ref
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        ddpx.launch.setup_from_env()
+    torch.manual_seed(7)                                  # same initial weights on every rank and for both stacks
+    objs = ddpx.recipes.vgg_train_objs(world_size=world, synthetic=True)
+    ours_model = objs.model
+    state0 = {k: v.detach().clone() for k, v in ours_model.state_dict().items()}
+    ref_model = ref.VGG().cuda()
+    ref_model.load_state_dict(state0, strict=True)
+    ref_opt = torch.optim.SGD(ref_model.parameters(), lr=0.4, momentum=0.9, weight_decay=5e-4)
+    spe = 49 if world > 1 else 98
+    lam = lambda step: np.interp([step / spe], [0, 6, 20], [0, 1, 0])[0]
+    ref_sched = torch.optim.lr_scheduler.LambdaLR(ref_opt, lam)
+    ref_net = torch.nn.parallel.DistributedDataParallel(ref_model, device_ids=[local_rank]) if world > 1 else ref_model
+    trainer = ddpx.Trainer(ours_model, [], objs.optimizer, local_rank, 1, scheduler=objs.scheduler)
+    xs, ys = make_host_batches(args.parity_steps, BATCH_PER_GPU, seed=300 + rank)
+    lo, lr_ = [], []
+    for i in range(args.parity_steps):
+        x = xs[i].cuda(); y = ys[i].cuda()
+        lo.append(float(trainer._run_batch(x, y).item()))
+        ref_opt.zero_grad()
+        l = torch.nn.functional.cross_entropy(ref_net(x), y)
+        l.backward(); ref_opt.step(); ref_sched.step()
+        lr_.append(float(l.item()))
+    inner = trainer.model.module if hasattr(trainer.model, "module") else trainer.model
+    so, sr = inner.state_dict(), ref_model.state_dict()
+    du = torch.cat([(so[k].float() - state0[k].float()).flatten() for k in state0 if state0[k].dtype.is_floating_point and "running" not in k])
+    dr = torch.cat([(sr[k].float() - state0[k].float()).flatten() for k in state0 if state0[k].dtype.is_floating_point and "running" not in k])
+    cos = float(torch.dot(du.double(), dr.double()) / (du.double().norm() * dr.double().norm()).clamp_min(1e-300))
+    ratio = float(du.double().norm() / dr.double().norm().clamp_min(1e-300))
+    rep = sync_report(inner.parameters(), lo[-1], world)
+    if rank == 0:
+        print(json.dumps({"mode": "parity", "n_gpus": world, "steps": args.parity_steps, "update_cosine": round(cos, 6),
+                          "update_norm_ratio": round(ratio, 6), "loss_ours": lo, "loss_reference": lr_,
+                          "replicas_in_sync": rep["replicas_in_sync"],
+                          "note": "TF32 tensor-core convolutions on both sides: per-step rounding differs, direction and size of the update agree"}),
+              flush=True)
     if world > 1:
         ddpx.launch.teardown()
 
@@ -352,6 +571,13 @@ def main():
     ap.add_argument("--steps", type=int, default=100)      # ~0.5 s timed: enough nvidia-smi samples under load
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--config", default="vgg", choices=["vgg", "sweep"] + list(LM_CONFIGS),
+                    help="vgg = the reference's own workload (default, the only one with a reference-script arm); the others are "
+                         "the remaining BASELINE.json configurations, each printing torch_stack_value beside value")
+    ap.add_argument("--no-torch-stack", action="store_true", help="skip the torch-stack arm of the mlp / gpt2 configs")
+    ap.add_argument("--sweep-max-mb", type=int, default=1024)
+    ap.add_argument("--parity", action="store_true", help="compare 4 steps of this framework with the reference from the same weights")
+    ap.add_argument("--parity-steps", type=int, default=4)
     args = ap.parse_args()
     if args.warmup < 3:
         args.warmup = 3
@@ -360,9 +586,21 @@ def main():
         # convenience: re-launch under torchrun when invoked directly with --gpus N
         cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={args.gpus}",
                "--master-addr", "127.0.0.1", "--master-port", os.environ.get("MASTER_PORT", "29511"), __file__,
-               "--gpus", str(args.gpus), "--steps", str(args.steps), "--warmup", str(args.warmup), "--impl", args.impl]
+               "--gpus", str(args.gpus), "--steps", str(args.steps), "--warmup", str(args.warmup), "--impl", args.impl,
+               "--config", args.config, "--sweep-max-mb", str(args.sweep_max_mb), "--parity-steps", str(args.parity_steps)]
+        cmd += (["--parity"] if args.parity else []) + (["--no-torch-stack"] if args.no_torch_stack else [])
         raise SystemExit(subprocess.call(cmd))
-    if args.impl == "reference":
+    if args.parity:
+        run_parity(args)
+    elif args.config == "sweep":
+        run_sweep_config(args)
+    elif args.config != "vgg":
+        if args.impl == "reference":
+            print(json.dumps({"impl": "reference", "unavailable": "the reference is a CNN script (multigpu.py:36-71) and cannot run "
+                              "this configuration; its torch stack is measured as torch_stack_value in the default arm's line"}))
+        else:
+            run_lm(args)
+    elif args.impl == "reference":
         run_reference(args)
     else:
         run_ours(args)

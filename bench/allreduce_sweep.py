@@ -34,10 +34,9 @@ def _time(fn, iters, world):
     return float(t.item())
 
 
-def worker(rank, world, port, args):
-    os.environ["MASTER_ADDR"] = "127.0.0.1"; os.environ["MASTER_PORT"] = str(port)
+def run_sweep(rank, world, args):
+    """The sweep itself; the caller has set up the P2P backend (ddpx.ddp_setup / setup_from_env).  Returns the rows."""
     import distributed_data_parallel_experiment_b200 as ddpx
-    ddpx.ddp_setup(rank, world, backend="p2p")
     comm = ddpx.launch.get_comm()
     dtype = torch.float32 if args.dtype == "fp32" else torch.bfloat16
     es = 4 if dtype == torch.float32 else 2
@@ -83,9 +82,19 @@ def worker(rank, world, port, args):
         results.append({"impl": "nccl", "ctas": None, "bytes": size, "us": ms * 1e3, "algbw_gbs": algbw,
                         "busbw_gbs": algbw * 2 * (world - 1) / world})
         size *= 4
+    for r in results:
+        r.update({"world": world, "dtype": args.dtype, "frac_of_900": r["busbw_gbs"] / 900.0,
+                  "frac_of_measured_770": r["busbw_gbs"] / 770.0})
+    return results
+
+
+def worker(rank, world, port, args):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"; os.environ["MASTER_PORT"] = str(port)
+    import distributed_data_parallel_experiment_b200 as ddpx
+    ddpx.ddp_setup(rank, world, backend="p2p")
+    results = run_sweep(rank, world, args)
     if rank == 0:
         for r in results:
-            r.update({"world": world, "dtype": args.dtype, "frac_of_900": r["busbw_gbs"] / 900.0})
             print(json.dumps(r), flush=True)
     ddpx.teardown()
 

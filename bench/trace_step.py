@@ -38,6 +38,14 @@ with profile(activities=[ProfilerActivity.CUDA]) as prof:
     for _ in range(3):
         tr._run_batch(x, y)
     torch.cuda.synchronize()
+def _short(name: str) -> str:
+    import re
+    n = name.replace("(anonymous namespace)::", "").replace("<unnamed>::", "")
+    n = re.sub(r"^void\s+", "", n)
+    n = n.split("(")[0].strip()
+    return (n or name)[:64]
+
+
 if local_rank == 0:
     out = Path("gpurun_out"); out.mkdir(exist_ok=True)
     path = out / f"trace_w{world}_rank0.json"
@@ -55,11 +63,11 @@ if local_rank == 0:
         for e in step:
             s = e["args"].get("stream", "?")
             busy[s] = busy.get(s, 0.0) + e["dur"]
-            nm = e["name"].replace("(anonymous namespace)::", "").replace("void ", "").split("(")[0][:60]
+            nm = _short(e["name"])
             print(f"{e['ts'] - t0:9.1f} {e['dur']:8.1f}  s{s}  {nm}")
         agg = {}
         for e in step:
-            nm = e["name"].replace("(anonymous namespace)::", "").replace("void ", "").split("(")[0][:60]
+            nm = _short(e["name"])
             a = agg.setdefault(nm, [0, 0.0]); a[0] += 1; a[1] += e["dur"]
         print("# per kernel (calls, total us):")
         for nm, (c, d) in sorted(agg.items(), key=lambda kv: -kv[1][1]):

@@ -111,6 +111,77 @@ __global__ void bn_apply_kernel(const float* __restrict__ x, float* __restrict__
   }
 }
 
+// forward apply straight from the convolution epilogue's (sum, sum of squares): every block derives scale / shift for its
+// channels itself, so no separate finalize launch sits between the convolution and this pass (8 launches and ~64 us per
+// VGG step, most of it launch gaps); block 0 also writes mean / rstd for the backward and updates the running
+// statistics.  training = 0: statistics are the running ones (eval mode), nothing is updated.
+template <bool kPool>
+__global__ void bn_apply_stats_kernel(const float* __restrict__ x, float* __restrict__ y, const float* __restrict__ sum,
+                                      const float* __restrict__ sq, float count, float eps, float momentum,
+                                      const float* __restrict__ gamma, const float* __restrict__ beta,
+                                      float* running_mean, float* running_var, long long* num_batches_tracked,
+                                      float* __restrict__ mean_out, float* __restrict__ rstd_out, int training, int Nimg,
+                                      int H, int W, int C, int relu) {
+  const int groups = C >> 2;
+  const int Ho = kPool ? H / 2 : H, Wo = kPool ? W / 2 : W;
+  const long long total = static_cast<long long>(Nimg) * Ho * Wo * groups;
+  const float inv = 1.f / count;
+  if (blockIdx.x == 0) {
+    for (int c = threadIdx.x; c < C; c += blockDim.x) {
+      float m, var;
+      if (training) {
+        m = sum[c] * inv;
+        var = fmaxf(sq[c] * inv - m * m, 0.f);
+        if (running_mean != nullptr) {
+          const float unbiased = count > 1.f ? var * (count / (count - 1.f)) : var;
+          running_mean[c] = (1.f - momentum) * running_mean[c] + momentum * m;
+          running_var[c] = (1.f - momentum) * running_var[c] + momentum * unbiased;
+        }
+      } else {
+        m = running_mean[c];
+        var = running_var[c];
+      }
+      mean_out[c] = m;
+      rstd_out[c] = rsqrtf(var + eps);
+    }
+    if (threadIdx.x == 0 && training && num_batches_tracked != nullptr) *num_batches_tracked += 1;
+  }
+  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int g = static_cast<int>(i % groups);
+    const long long po = i / groups;
+    const int c = g * 4;
+    float4 m, v;
+    if (training) {
+      const float4 s4 = ld4(sum + c), q4 = ld4(sq + c);
+      m = make_float4(s4.x * inv, s4.y * inv, s4.z * inv, s4.w * inv);
+      v = make_float4(fmaxf(q4.x * inv - m.x * m.x, 0.f), fmaxf(q4.y * inv - m.y * m.y, 0.f),
+                      fmaxf(q4.z * inv - m.z * m.z, 0.f), fmaxf(q4.w * inv - m.w * m.w, 0.f));
+    } else {
+      // block 0 only READS the running statistics in eval mode, so every block may read them here
+      m = ld4(running_mean + c); v = ld4(running_var + c);
+    }
+    const float4 ga = ld4(gamma + c), be = ld4(beta + c);
+    const float4 sc = make_float4(ga.x * rsqrtf(v.x + eps), ga.y * rsqrtf(v.y + eps), ga.z * rsqrtf(v.z + eps),
+                                  ga.w * rsqrtf(v.w + eps));
+    const float4 sh = make_float4(be.x - m.x * sc.x, be.y - m.y * sc.y, be.z - m.z * sc.z, be.w - m.w * sc.w);
+    if (!kPool) {
+      st4(y + po * C + c, bn_relu4(ld4(x + po * C + c), sc, sh, relu));
+    } else {
+      const int wo = static_cast<int>(po % Wo);
+      const long long t = po / Wo;
+      const int ho = static_cast<int>(t % Ho);
+      const long long n = t / Ho;
+      const float* base = x + ((n * H + 2 * ho) * W + 2 * wo) * C + c;
+      float4 a = bn_relu4(ld4(base), sc, sh, relu);
+      float4 b = bn_relu4(ld4(base + C), sc, sh, relu);
+      float4 d = bn_relu4(ld4(base + static_cast<long long>(W) * C), sc, sh, relu);
+      float4 e = bn_relu4(ld4(base + static_cast<long long>(W) * C + C), sc, sh, relu);
+      st4(y + po * C + c, max4(max4(a, b), max4(d, e)));
+    }
+  }
+}
+
 // ------------------------------------------------------------------------------------------------
 // backward pass 1: per-channel sum(dz) and sum(dz * xhat), dz = gradient at the BN output after routing the
 // incoming gradient back through (pool arg-max,) ReLU mask.  Accumulated with atomics into pre-zeroed buffers.
@@ -123,77 +194,96 @@ __device__ __forceinline__ void route_pool(float za, float zb, float zd, float z
   if (ze > zmax) { zmax = ze; arg = 3; }
 }
 
-template <bool kPool>
-__global__ void bn_bwd_reduce_kernel(const float* __restrict__ x, const float* __restrict__ dout,
-                                     const float* __restrict__ mean, const float* __restrict__ rstd,
-                                     const float* __restrict__ gamma, const float* __restrict__ beta, int Nimg, int H,
-                                     int W, int C, int relu, float* __restrict__ sum_dz, float* __restrict__ sum_dzx) {
+// kU output pixels per thread per trip, every load issued before the first use (the kernel is pure bandwidth), few large
+// blocks, and ONE 16-byte vector reduction per channel group per block: the first version (one pixel per trip, 1184
+// blocks x 1024 scalar atomics onto the same 1024 addresses) spent 33 us on the 17 MB layers and ran the large ones at
+// 4.1 TB/s.
+template <bool kPool, int kU>
+__global__ void __launch_bounds__(256, 3)
+bn_bwd_reduce_kernel(const float* __restrict__ x, const float* __restrict__ dout,
+                     const float* __restrict__ mean, const float* __restrict__ rstd,
+                     const float* __restrict__ gamma, const float* __restrict__ beta, int Nimg, int H,
+                     int W, int C, int relu, float* __restrict__ sum_dz, float* __restrict__ sum_dzx) {
   const int groups = C >> 2;
   const int lanes = blockDim.x / groups;
   const int g = threadIdx.x % groups;
   const int pl = threadIdx.x / groups;
-  if (pl >= lanes) return;
+  const bool active = pl < lanes;          // every thread reaches the barrier below
   const int c = g * 4;
-  const float m[4] = {mean[c], mean[c + 1], mean[c + 2], mean[c + 3]};
-  const float r[4] = {rstd[c], rstd[c + 1], rstd[c + 2], rstd[c + 3]};
-  const float ga[4] = {gamma[c], gamma[c + 1], gamma[c + 2], gamma[c + 3]};
-  const float be[4] = {beta[c], beta[c + 1], beta[c + 2], beta[c + 3]};
+  const float4 m4 = ld4(mean + c), r4 = ld4(rstd + c), g4 = ld4(gamma + c), b4 = ld4(beta + c);
+  const float m[4] = {m4.x, m4.y, m4.z, m4.w}, r[4] = {r4.x, r4.y, r4.z, r4.w};
+  const float ga[4] = {g4.x, g4.y, g4.z, g4.w}, be[4] = {b4.x, b4.y, b4.z, b4.w};
   float s1[4] = {0, 0, 0, 0}, s2[4] = {0, 0, 0, 0};
   const int Ho = kPool ? H / 2 : H, Wo = kPool ? W / 2 : W;
-  const long long Pout = static_cast<long long>(Nimg) * Ho * Wo;
-  for (long long po = static_cast<long long>(blockIdx.x) * lanes + pl; po < Pout;
-       po += static_cast<long long>(gridDim.x) * lanes) {
-    const float4 d4 = ld4(dout + po * C + c);
-    const float d[4] = {d4.x, d4.y, d4.z, d4.w};
-    if (!kPool) {
-      const float4 x4 = ld4(x + po * C + c);
-      const float xv[4] = {x4.x, x4.y, x4.z, x4.w};
+  const long long Pout = active ? static_cast<long long>(Nimg) * Ho * Wo : 0;
+  const long long stride = static_cast<long long>(gridDim.x) * lanes;
+  for (long long p0 = static_cast<long long>(blockIdx.x) * lanes + pl; p0 < Pout; p0 += stride * kU) {
+    float4 dv[kU], xv[kU][kPool ? 4 : 1];
 #pragma unroll
-      for (int k = 0; k < 4; ++k) {
-        const float xh = (xv[k] - m[k]) * r[k];
-        const float z = fmaf(ga[k], xh, be[k]);
-        const float dz = (!relu || z > 0.f) ? d[k] : 0.f;
-        s1[k] += dz;
-        s2[k] += dz * xh;
+    for (int u = 0; u < kU; ++u) {
+      const long long po = p0 + u * stride;
+      if (po < Pout) {
+        dv[u] = ld4(dout + po * C + c);
+        if (!kPool) {
+          xv[u][0] = ld4(x + po * C + c);
+        } else {
+          const int wo = static_cast<int>(po % Wo);
+          const long long t = po / Wo;
+          const int ho = static_cast<int>(t % Ho);
+          const long long n = t / Ho;
+          const float* base = x + ((n * H + 2 * ho) * W + 2 * wo) * C + c;
+          xv[u][0] = ld4(base); xv[u][1] = ld4(base + C);
+          xv[u][2] = ld4(base + static_cast<long long>(W) * C); xv[u][3] = ld4(base + static_cast<long long>(W) * C + C);
+        }
       }
-    } else {
-      const int wo = static_cast<int>(po % Wo);
-      const long long t = po / Wo;
-      const int ho = static_cast<int>(t % Ho);
-      const long long n = t / Ho;
-      const float* base = x + ((n * H + 2 * ho) * W + 2 * wo) * C + c;
-      const float4 a4 = ld4(base), b4 = ld4(base + C), d04 = ld4(base + static_cast<long long>(W) * C),
-                   e4 = ld4(base + static_cast<long long>(W) * C + C);
-      const float xa[4] = {a4.x, a4.y, a4.z, a4.w}, xb[4] = {b4.x, b4.y, b4.z, b4.w};
-      const float xd[4] = {d04.x, d04.y, d04.z, d04.w}, xe[4] = {e4.x, e4.y, e4.z, e4.w};
+    }
 #pragma unroll
-      for (int k = 0; k < 4; ++k) {
-        const float ha = (xa[k] - m[k]) * r[k], hb = (xb[k] - m[k]) * r[k];
-        const float hd = (xd[k] - m[k]) * r[k], he = (xe[k] - m[k]) * r[k];
-        int arg; float zmax;
-        route_pool(fmaf(ga[k], ha, be[k]), fmaf(ga[k], hb, be[k]), fmaf(ga[k], hd, be[k]), fmaf(ga[k], he, be[k]), arg, zmax);
-        const float dz = (!relu || zmax > 0.f) ? d[k] : 0.f;
-        const float xh = arg == 0 ? ha : (arg == 1 ? hb : (arg == 2 ? hd : he));
-        s1[k] += dz;
-        s2[k] += dz * xh;
+    for (int u = 0; u < kU; ++u) {
+      if (p0 + u * stride >= Pout) break;
+      const float d[4] = {dv[u].x, dv[u].y, dv[u].z, dv[u].w};
+      if (!kPool) {
+        const float xs[4] = {xv[u][0].x, xv[u][0].y, xv[u][0].z, xv[u][0].w};
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          const float xh = (xs[k] - m[k]) * r[k];
+          const float z = fmaf(ga[k], xh, be[k]);
+          const float dz = (!relu || z > 0.f) ? d[k] : 0.f;
+          s1[k] += dz;
+          s2[k] += dz * xh;
+        }
+      } else {
+        const float xa[4] = {xv[u][0].x, xv[u][0].y, xv[u][0].z, xv[u][0].w}, xb[4] = {xv[u][1].x, xv[u][1].y, xv[u][1].z, xv[u][1].w};
+        const float xd[4] = {xv[u][2].x, xv[u][2].y, xv[u][2].z, xv[u][2].w}, xe[4] = {xv[u][3].x, xv[u][3].y, xv[u][3].z, xv[u][3].w};
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          const float ha = (xa[k] - m[k]) * r[k], hb = (xb[k] - m[k]) * r[k];
+          const float hd = (xd[k] - m[k]) * r[k], he = (xe[k] - m[k]) * r[k];
+          int arg; float zmax;
+          route_pool(fmaf(ga[k], ha, be[k]), fmaf(ga[k], hb, be[k]), fmaf(ga[k], hd, be[k]), fmaf(ga[k], he, be[k]), arg, zmax);
+          const float dz = (!relu || zmax > 0.f) ? d[k] : 0.f;
+          const float xh = arg == 0 ? ha : (arg == 1 ? hb : (arg == 2 ? hd : he));
+          s1[k] += dz;
+          s2[k] += dz * xh;
+        }
       }
     }
   }
-  // block-level reduce across pixel lanes through shared memory, then one atomic per channel per block
+  // block-level reduce across pixel lanes through shared memory, then one vector reduction per channel group per block
   extern __shared__ float red[];
-  float* r1 = red;
-  float* r2 = red + blockDim.x * 4;
-#pragma unroll
-  for (int k = 0; k < 4; ++k) { r1[threadIdx.x * 4 + k] = s1[k]; r2[threadIdx.x * 4 + k] = s2[k]; }
+  float4* r1 = reinterpret_cast<float4*>(red);
+  float4* r2 = r1 + blockDim.x;
+  r1[threadIdx.x] = make_float4(s1[0], s1[1], s1[2], s1[3]);
+  r2[threadIdx.x] = make_float4(s2[0], s2[1], s2[2], s2[3]);
   __syncthreads();
-  if (pl == 0) {
-#pragma unroll
-    for (int k = 0; k < 4; ++k) {
-      float a = 0.f, b = 0.f;
-      for (int l = 0; l < lanes; ++l) { a += r1[(l * groups + g) * 4 + k]; b += r2[(l * groups + g) * 4 + k]; }
-      atomicAdd(sum_dz + c + k, a);
-      atomicAdd(sum_dzx + c + k, b);
+  if (pl == 0 && active) {
+    float4 a = make_float4(0, 0, 0, 0), b = make_float4(0, 0, 0, 0);
+    for (int l = 0; l < lanes; ++l) {
+      const float4 u = r1[l * groups + g], v = r2[l * groups + g];
+      a.x += u.x; a.y += u.y; a.z += u.z; a.w += u.w;
+      b.x += v.x; b.y += v.y; b.z += v.z; b.w += v.w;
     }
+    asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(sum_dz + c), "f"(a.x), "f"(a.y), "f"(a.z), "f"(a.w) : "memory");
+    asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(sum_dzx + c), "f"(b.x), "f"(b.y), "f"(b.z), "f"(b.w) : "memory");
   }
 }
 
@@ -293,7 +383,7 @@ extern "C" int ddpx_bn_eval_stats(const float* running_mean, const float* runnin
 }
 
 extern "C" int ddpx_bn_stats(const float* x, long long P, int C, float* sum, float* sq, void* stream) {
-  if (C % 4 || C > 1024) return DDPX_ERR_SHAPE;
+  if (C <= 0 || C % 4 || C > 1024) return DDPX_ERR_SHAPE;
   const int groups = C / 4;
   int block = 256;
   if (groups > block) block = groups;
@@ -315,23 +405,47 @@ extern "C" int ddpx_bn_apply(const float* x, float* y, const float* mean, const 
   return cudaGetLastError() == cudaSuccess ? DDPX_OK : DDPX_ERR_LAUNCH;
 }
 
+// BatchNorm forward from raw (sum, sum of squares): finalize + running-statistics update + normalise (+ReLU, +pool) in ONE
+// launch.  training = 0 normalises with the running statistics (sum / sq may be null).  mean_rstd [2][C] is an output.
+extern "C" int ddpx_bn_apply_stats(const float* x, float* y, const float* sum, const float* sq, float count, float eps,
+                                   float momentum, const float* gamma, const float* beta, float* running_mean,
+                                   float* running_var, long long* num_batches_tracked, float* mean_rstd, int training,
+                                   int Nimg, int H, int W, int C, int relu, int pool, void* stream) {
+  if (C <= 0 || C % 4) return DDPX_ERR_SHAPE;
+  if (pool && ((H | W) & 1)) return DDPX_ERR_SHAPE;
+  if (training ? (sum == nullptr || sq == nullptr) : (running_mean == nullptr || running_var == nullptr)) return DDPX_ERR_ARG;
+  const long long total = static_cast<long long>(Nimg) * (pool ? H / 2 : H) * (pool ? W / 2 : W) * (C / 4);
+  const int block = 256;
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  if (pool)
+    bn_apply_stats_kernel<true><<<grid_for(total, block, 148 * 16), block, 0, s>>>(
+        x, y, sum, sq, count, eps, momentum, gamma, beta, running_mean, running_var, num_batches_tracked, mean_rstd,
+        mean_rstd + C, training, Nimg, H, W, C, relu);
+  else
+    bn_apply_stats_kernel<false><<<grid_for(total, block, 148 * 16), block, 0, s>>>(
+        x, y, sum, sq, count, eps, momentum, gamma, beta, running_mean, running_var, num_batches_tracked, mean_rstd,
+        mean_rstd + C, training, Nimg, H, W, C, relu);
+  return cudaGetLastError() == cudaSuccess ? DDPX_OK : DDPX_ERR_LAUNCH;
+}
+
 extern "C" int ddpx_bn_bwd_reduce(const float* x, const float* dout, const float* mean, const float* rstd,
                                   const float* gamma, const float* beta, int Nimg, int H, int W, int C, int relu, int pool,
                                   float* sum_dz, float* sum_dzx, void* stream) {
   if (C % 4 || C > 1024) return DDPX_ERR_SHAPE;
   if (pool && ((H | W) & 1)) return DDPX_ERR_SHAPE;
   const int groups = C / 4;
-  int block = 256;
-  if (groups > block) block = groups;
+  const int block = 256;
   const int lanes = block / groups;
   const long long Pout = static_cast<long long>(Nimg) * (pool ? H / 2 : H) * (pool ? W / 2 : W);
-  const int grid = grid_for(Pout, lanes, 148 * 4);
+  // sum_dz / sum_dzx take 16-byte vector reductions
+  if ((reinterpret_cast<uintptr_t>(sum_dz) | reinterpret_cast<uintptr_t>(sum_dzx)) & 15) return DDPX_ERR_ALIGN;
+  const int grid = grid_for(Pout, lanes * 4, 148 * 3);
   const size_t smem = static_cast<size_t>(block) * 8 * sizeof(float);
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   if (pool)
-    bn_bwd_reduce_kernel<true><<<grid, block, smem, s>>>(x, dout, mean, rstd, gamma, beta, Nimg, H, W, C, relu, sum_dz, sum_dzx);
+    bn_bwd_reduce_kernel<true, 2><<<grid, block, smem, s>>>(x, dout, mean, rstd, gamma, beta, Nimg, H, W, C, relu, sum_dz, sum_dzx);
   else
-    bn_bwd_reduce_kernel<false><<<grid, block, smem, s>>>(x, dout, mean, rstd, gamma, beta, Nimg, H, W, C, relu, sum_dz, sum_dzx);
+    bn_bwd_reduce_kernel<false, 4><<<grid, block, smem, s>>>(x, dout, mean, rstd, gamma, beta, Nimg, H, W, C, relu, sum_dz, sum_dzx);
   return cudaGetLastError() == cudaSuccess ? DDPX_OK : DDPX_ERR_LAUNCH;
 }
 
@@ -360,7 +474,10 @@ extern "C" int ddpx_bn_bwd_apply(const float* x, const float* dout, const float*
 extern "C" int ddpx_bn_train_fwd(const float* x, float* y, const float* gamma, const float* beta, float* running_mean,
                                  float* running_var, long long* num_batches_tracked, float momentum, float eps, int Nimg,
                                  int H, int W, int C, int relu, int pool, float* mean_rstd, float* workspace, void* stream) {
-  if (C % 4 || C > 1024) return DDPX_ERR_SHAPE;
+  // every argument check comes before the first memset / launch: a refused call leaves the running statistics untouched
+  if (C <= 0 || C % 4 || C > 1024) return DDPX_ERR_SHAPE;
+  if (pool && ((H | W) & 1)) return DDPX_ERR_SHAPE;
+  if (Nimg <= 0 || H <= 0 || W <= 0) return DDPX_ERR_ARG;
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   if (cudaMemsetAsync(workspace, 0, sizeof(float) * 2 * C, s) != cudaSuccess) return DDPX_ERR_LAUNCH;
   const long long P = static_cast<long long>(Nimg) * H * W;

@@ -4,6 +4,7 @@
 //   * NCHW <-> NHWC layout transposes, stand-alone ReLU / 2x2 max-pool forward+backward, spatial mean
 // Reference parity: conv0 at /root/reference/multigpu.py:53, pools :59, mean :68, DeepNN S:21-31.
 #include <cuda_runtime.h>
+#include <string.h>
 #include <stdint.h>
 #include "../../include/ddpx_kernels.h"
 
@@ -69,6 +70,86 @@ unpack_conv_wgrad_kernel(const float* __restrict__ wp, float* __restrict__ w, in
   for (int idx = threadIdx.x; idx < 32 * 288; idx += 256) {
     const int co = idx / 288, j = idx - co * 288;
     w[(static_cast<long long>(co0 + co) * Cin + ci0) * 9 + j] = tile[co][j];
+  }
+}
+
+// All conv layers of a model in ONE launch: per-layer tiles of the kernel above, dealt to a flat grid, plus the stem's
+// [Cout][27] -> [Cout][32] padding and the clearing of every layer's BatchNorm statistic accumulators.  Eight per-layer
+// launches with 8..256 blocks each took 113 us per VGG step for ~110 MB of traffic; one launch keeps every SM busy.
+constexpr int kMaxPackJobs = 32;
+struct PackJob {
+  const float* w;
+  float* wf;            // fprop layout [9][Cout][Cin]   (stem: [Cout][32])
+  float* wd;            // dgrad layout [9][Cin][Cout]   (may be null)
+  float* zero;          // floats to clear (BatchNorm sum / sum-of-squares of this layer), may be null
+  int zero_n;
+  int Cout, Cin;        // Cin == 3 marks the stem
+  int tiles_ci;         // Cin / 32
+  int block_begin;      // first block of this job in the flat grid
+};
+struct PackTable { PackJob j[kMaxPackJobs]; int n; };
+
+__global__ void __launch_bounds__(256)
+pack_conv_multi_kernel(const __grid_constant__ PackTable t) {
+  __shared__ float tile[32][289];
+  int ji = 0;
+  while (ji + 1 < t.n && static_cast<int>(blockIdx.x) >= t.j[ji + 1].block_begin) ++ji;
+  const PackJob& job = t.j[ji];
+  const int local = static_cast<int>(blockIdx.x) - job.block_begin;
+  if (local == 0 && job.zero != nullptr)
+    for (int i = threadIdx.x; i < job.zero_n; i += 256) job.zero[i] = 0.f;
+  if (job.Cin == 3) {
+    const int i = local * 256 + threadIdx.x;
+    if (i < job.Cout * 32) {
+      const int co = i >> 5, k = i & 31;
+      job.wf[i] = k < 27 ? job.w[co * 27 + k] : 0.f;
+    }
+    return;
+  }
+  const int Cout = job.Cout, Cin = job.Cin;
+  const int ci0 = (local % job.tiles_ci) * 32, co0 = (local / job.tiles_ci) * 32;
+  // 32 rows of 288 contiguous floats (16-byte aligned: ci0 * 36 bytes * 32) -> 72 float4 per row
+  for (int idx = threadIdx.x; idx < 32 * 72; idx += 256) {
+    const int co = idx / 72, j4 = idx - co * 72;
+    const float4 v = *reinterpret_cast<const float4*>(job.w + (static_cast<long long>(co0 + co) * Cin + ci0) * 9 + j4 * 4);
+    tile[co][j4 * 4] = v.x; tile[co][j4 * 4 + 1] = v.y; tile[co][j4 * 4 + 2] = v.z; tile[co][j4 * 4 + 3] = v.w;
+  }
+  __syncthreads();
+  for (int idx = threadIdx.x; idx < 9 * 1024; idx += 256) {
+    const int tap = idx >> 10, a = (idx >> 5) & 31, b = idx & 31;
+    job.wf[(static_cast<long long>(tap) * Cout + co0 + a) * Cin + ci0 + b] = tile[a][b * 9 + tap];
+    if (job.wd != nullptr)
+      job.wd[(static_cast<long long>(8 - tap) * Cin + ci0 + a) * Cout + co0 + b] = tile[b][a * 9 + tap];
+  }
+}
+
+// unpack that also clears the staging tile it has read: the staging buffer of a layer is persistent, so the next step's
+// weight-gradient kernel finds zeros without a memset launch (24 ddpx_zero launches, 133 us per VGG step, before)
+__global__ void __launch_bounds__(256)
+unpack_conv_wgrad_rezero_kernel(float* __restrict__ wp, float* __restrict__ w, int Cout, int Cin) {
+  __shared__ float tile[16][289];
+  const int ci0 = blockIdx.x * 32, co0 = blockIdx.y * 16;
+  // all 18 loads of a thread are issued before its first zero store: loads and stores hit the same addresses, so the
+  // compiler must keep their order, and load -> store -> load was 18 dependent round trips (242 us per step)
+  float v[18];
+#pragma unroll
+  for (int k = 0; k < 18; ++k) {
+    const int idx = threadIdx.x + k * 256;
+    const int tap = idx >> 9, co = (idx >> 5) & 15, ci = idx & 31;
+    v[k] = wp[(static_cast<long long>(tap) * Cout + co0 + co) * Cin + ci0 + ci];
+  }
+#pragma unroll
+  for (int k = 0; k < 18; ++k) {
+    const int idx = threadIdx.x + k * 256;
+    const int tap = idx >> 9, co = (idx >> 5) & 15, ci = idx & 31;
+    tile[co][ci * 9 + tap] = v[k];
+    wp[(static_cast<long long>(tap) * Cout + co0 + co) * Cin + ci0 + ci] = 0.f;
+  }
+  __syncthreads();
+  for (int idx = threadIdx.x; idx < 16 * 72; idx += 256) {
+    const int co = idx / 72, j4 = idx - co * 72;
+    *reinterpret_cast<float4*>(w + (static_cast<long long>(co0 + co) * Cin + ci0) * 9 + j4 * 4) =
+        make_float4(tile[co][j4 * 4], tile[co][j4 * 4 + 1], tile[co][j4 * 4 + 2], tile[co][j4 * 4 + 3]);
   }
 }
 
@@ -296,6 +377,44 @@ extern "C" int ddpx_pack_conv_weights(const float* w, float* w_fprop, float* w_d
     return LAUNCH_OK();
   }
   pack_conv_w_kernel<<<nblocks(total, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(w, w_fprop, w_dgrad, Cout, Cin);
+  return LAUNCH_OK();
+}
+
+// Weight packing for n conv layers in one launch (see pack_conv_multi_kernel).  Layer i: w[i] is [Cout][Cin][3][3];
+// wf[i] receives the fprop layout, wd[i] (may be null) the dgrad layout; zero[i] (may be null) are zero_n[i] floats to clear.
+// Cin == 3 marks the RGB stem (wf = [Cout][32] zero-padded rows).
+extern "C" int ddpx_pack_conv_weights_multi(int n, const void* const* w, void* const* wf, void* const* wd, void* const* zero,
+                                            const int* zero_n, const int* Cout, const int* Cin, void* stream) {
+  if (n < 1 || n > kMaxPackJobs) return DDPX_ERR_LIMIT;
+  PackTable t;
+  memset(&t, 0, sizeof(t));
+  t.n = n;
+  int blocks = 0;
+  for (int i = 0; i < n; ++i) {
+    PackJob& j = t.j[i];
+    j.w = static_cast<const float*>(w[i]); j.wf = static_cast<float*>(wf[i]);
+    j.wd = wd ? static_cast<float*>(wd[i]) : nullptr;
+    j.zero = zero ? static_cast<float*>(zero[i]) : nullptr;
+    j.zero_n = zero_n ? zero_n[i] : 0;
+    j.Cout = Cout[i]; j.Cin = Cin[i];
+    j.block_begin = blocks;
+    if (Cin[i] == 3) {
+      blocks += (Cout[i] * 32 + 255) / 256;
+    } else {
+      if (Cout[i] % 32 || Cin[i] % 32) return DDPX_ERR_SHAPE;
+      j.tiles_ci = Cin[i] / 32;
+      blocks += (Cout[i] / 32) * (Cin[i] / 32);
+    }
+  }
+  pack_conv_multi_kernel<<<blocks, 256, 0, static_cast<cudaStream_t>(stream)>>>(t);
+  return LAUNCH_OK();
+}
+
+// unpack + clear: dw_packed is left all-zero for the next accumulation
+extern "C" int ddpx_unpack_conv_wgrad_rezero(float* dw_packed, float* dw, int Cout, int Cin, void* stream) {
+  if (Cout % 32 || Cin % 32 || Cout / 16 > 65535) return DDPX_ERR_SHAPE;
+  dim3 grid(Cin / 32, Cout / 16);
+  unpack_conv_wgrad_rezero_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(dw_packed, dw, Cout, Cin);
   return LAUNCH_OK();
 }
 

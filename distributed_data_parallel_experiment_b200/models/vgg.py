@@ -55,6 +55,8 @@ class VGG(nn.Module):
 
     def _forward_fused(self, x: torch.Tensor) -> torch.Tensor:
         bb = self.backbone
+        # one launch packs every layer's weights into the tensor-core layouts and clears the BatchNorm accumulators
+        ops.functional.prepare_convs([getattr(bb, f"conv{idx}").weight for idx, _ in self._plan])
         for idx, pooled in self._plan:
             conv = getattr(bb, f"conv{idx}")
             bn = getattr(bb, f"bn{idx}")

@@ -61,6 +61,7 @@ def _check_f32(*ts):
 # ------------------------------------------------------------------------------------------------ conv (+BN+ReLU+pool)
 import os as _os
 _WGRAD_PACKED = _os.environ.get("DDPX_WGRAD_PACKED", "1") not in ("0", "")   # A/B switch for the staging-layout epilogue
+_BLOCK_CALLS = _os.environ.get("DDPX_BLOCK_CALLS", "1") not in ("0", "")      # A/B switch: 0 = one native call per kernel
 _STEM_SPLIT_K = 296   # two K-slices per SM for the pixels-long reduction of the stem weight gradient
 
 
@@ -113,6 +114,104 @@ def _conv_supported(Cin, Cout, H, W_):
     if Cin == 3:
         return Cout % 32 == 0
     return Cin % 32 == 0 and Cout % 32 == 0
+
+
+class ConvWorkspace:
+    """Persistent per-layer device buffers of the fused conv-BN block: packed forward / data-gradient weights, the
+    BatchNorm (sum, sum^2) accumulators and the tap-major weight-gradient staging buffer (kept all-zero between uses: the
+    unpack kernel clears what it reads).  Lives as an attribute of the weight Parameter."""
+    __slots__ = ("wf", "wd", "stats", "staging", "Cout", "Cin", "fresh", "ptr")
+
+    def __init__(self, w):
+        Cout, Cin = int(w.shape[0]), int(w.shape[1])
+        dev = w.device
+        self.Cout, self.Cin, self.ptr = Cout, Cin, w.data_ptr()
+        stem = Cin == 3
+        self.wf = torch.empty(Cout * 32 if stem else 9 * Cout * Cin, device=dev, dtype=torch.float32)
+        self.wd = None if stem else torch.empty(9 * Cout * Cin, device=dev, dtype=torch.float32)
+        self.stats = _zeros((2, Cout), dev)
+        self.staging = None if stem else _zeros((9 * Cout * Cin,), dev)
+        self.fresh = False
+
+
+def conv_workspace(w) -> ConvWorkspace:
+    ws = getattr(w, "_ddpx_conv_ws", None)
+    if ws is None or ws.ptr != w.data_ptr():
+        ws = ConvWorkspace(w.detach())
+        try:
+            w._ddpx_conv_ws = ws
+        except AttributeError:      # exotic tensor subclasses without a __dict__: per-call workspace
+            pass
+    return ws
+
+
+def prepare_convs(weights):
+    """Pack the weights of every listed conv layer (forward and data-gradient layouts) and clear their BatchNorm
+    accumulators in ONE launch.  Call once per forward, before the blocks (models.VGG does); a block whose workspace was
+    not prepared since its last use prepares itself."""
+    wss = [conv_workspace(w) for w in weights]
+    native.pack_conv_weights_multi([w.detach() for w in weights], [s.wf for s in wss], [s.wd for s in wss],
+                                   [s.stats for s in wss], [2 * s.Cout for s in wss], [s.Cout for s in wss],
+                                   [s.Cin for s in wss])
+    for s in wss:
+        s.fresh = True
+    return wss
+
+
+class _ConvBNBlock(Function):
+    """conv3x3(pad 1, no bias) -> BatchNorm2d -> [ReLU] -> [MaxPool2d(2)]: ONE native call per direction
+    (csrc/kernels/blocks.cu).  Forward: convolution (+ batch statistics in its epilogue) and a normalise pass that derives
+    mean / rstd itself; backward: BN reduce + apply, weight gradient into the persistent staging buffer, unpack, data
+    gradient."""
+
+    @staticmethod
+    def forward(ctx, x, beta, gamma, w, running_mean, running_var, nbt, training, momentum, eps, relu, pool, ws):
+        # input order (x, beta, gamma, w): gradients reach the parameters' accumulators - and the reducer's hooks - in the
+        # order torch's unfused modules deliver them (bn.bias, bn.weight, conv.weight), so the rebuilt buckets match
+        # torch DDP's layout (SURVEY.md appendix B)
+        _check_f32(x, w, gamma, beta)
+        N, Cin, H, W_ = x.shape
+        Cout = w.shape[0]
+        stem = Cin == 3
+        dev = x.device
+        need_dx = ctx.needs_input_grad[0]
+        if not ws.fresh:
+            prepare_convs([w])
+        ws.fresh = False
+        y = torch.empty((N, H, W_, Cout), device=dev, dtype=torch.float32)
+        Ho, Wo = (H // 2, W_ // 2) if pool else (H, W_)
+        out = torch.empty((N, Ho, Wo, Cout), device=dev, dtype=torch.float32)
+        mr = torch.empty((2, Cout), device=dev, dtype=torch.float32)
+        if stem:
+            xin = x if x.is_contiguous() else to_nchw_contiguous(x)
+            patches = torch.empty((N, H, W_, 32), device=dev, dtype=torch.float32)
+            native.conv_bn_fwd(xin, ws.wf, gamma, beta, running_mean, running_var, nbt, momentum, eps, N, H, W_, Cin, Cout,
+                               int(relu), int(pool), int(training), ws.stats, y, out, mr, patches)
+            saved_in = patches
+        else:
+            saved_in = to_nhwc(x)
+            native.conv_bn_fwd(saved_in, ws.wf, gamma, beta, running_mean, running_var, nbt, momentum, eps, N, H, W_, Cin,
+                               Cout, int(relu), int(pool), int(training), ws.stats, y, out, mr)
+        ctx.save_for_backward(saved_in, y, mr, gamma, beta)
+        ctx.ws = ws
+        ctx.cfg = (N, H, W_, Cin, Cout, bool(training), bool(relu), bool(pool), need_dx, tuple(w.shape))
+        return from_nhwc(out)
+
+    @staticmethod
+    def backward(ctx, dout):
+        xin, y, mr, gamma, beta = ctx.saved_tensors
+        N, H, W_, Cin, Cout, training, relu, pool, need_dx, wshape = ctx.cfg
+        ws = ctx.ws
+        dev = y.device
+        d = to_nhwc(dout)
+        sums = torch.empty((2, Cout), device=dev, dtype=torch.float32)
+        dconv = torch.empty_like(y)
+        dw = torch.empty(wshape, device=dev, dtype=torch.float32)
+        dx = torch.empty((N, H, W_, Cin), device=dev, dtype=torch.float32) if (need_dx and Cin != 3) else None
+        native.conv_bn_bwd(y, d, xin, ws.wd, mr, gamma, beta, N, H, W_, Cin, Cout, int(relu), int(pool), int(training), sums,
+                           dconv, ws.staging, dw, dx)
+        return ((from_nhwc(dx) if dx is not None else None), sums[0], sums[1], dw,
+                None, None, None, None, None, None, None, None, None)
 
 
 class _ConvBNAct(Function):
@@ -215,6 +314,12 @@ def conv_bn_act(x, w, gamma, beta, running_mean, running_var, num_batches_tracke
     """Fused VGG block (multigpu.py:53-59).  CPU tensors use the torch composition with the same semantics.
     ``sync = (StatSync, key)`` turns the BatchNorm into a SyncBatchNorm (statistics over all ranks)."""
     if x.is_cuda:
+        Cin, Cout = x.shape[1], w.shape[0]
+        use_sync = training and sync is not None and sync[0].world_size > 1
+        if _BLOCK_CALLS and not use_sync and x.dtype == torch.float32 and Cout % 32 == 0 and (Cin == 3 or Cin % 32 == 0) \
+                and running_mean is not None:
+            return _ConvBNBlock.apply(x, beta, gamma, w, running_mean, running_var, num_batches_tracked, training, momentum,
+                                      eps, relu, pool, conv_workspace(w))
         return _ConvBNAct.apply(x, w, gamma, beta, running_mean, running_var, num_batches_tracked, training, momentum, eps,
                                 relu, pool, sync)
     y = F.conv2d(x, w, None, padding=1)

@@ -125,6 +125,28 @@ def gemm_batched(A, B, D, M, N, K, lda, ldb, ldd, a_mn, b_mn, batch1, batch2, a_
           tag=f"[b{batch1 * batch2} {M}x{N}x{K} {'NT'[a_mn]}{'NT'[b_mn]} c{causal}]" if _PROFILE is not None else "")
 
 
+def conv_bn_fwd(x, wf, gamma, beta, rm, rv, nbt, momentum, eps, N, H, W, Cin, Cout, relu, pool, training, stats, y, out, mr,
+                patches=None):
+    """conv3x3 -> BatchNorm (finalize fused into the apply pass) -> [ReLU] -> [pool]: 2 launches (3 for the stem), 1 call."""
+    _call("ddpx_conv_bn_fwd", _P(x), _P(wf), _P(gamma), _P(beta), _P(rm), _P(rv), _P(nbt), c_float(momentum), c_float(eps),
+          c_int(N), c_int(H), c_int(W), c_int(Cin), c_int(Cout), c_int(relu), c_int(pool), c_int(training), _P(stats), _P(y),
+          _P(out), _P(mr), _P(patches), _st(), launches=3 if Cin == 3 else 2,
+          tag=(f"[{Cin}->{Cout}@{H}]" if _PROFILE is not None else ""))
+
+
+def conv_bn_bwd(y, dout, xin, wd, mr, gamma, beta, N, H, W, Cin, Cout, relu, pool, training, sums, dconv, staging, dw, dx):
+    _call("ddpx_conv_bn_bwd", _P(y), _P(dout), _P(xin), _P(wd), _P(mr), _P(gamma), _P(beta), c_int(N), c_int(H), c_int(W),
+          c_int(Cin), c_int(Cout), c_int(relu), c_int(pool), c_int(training), _P(sums), _P(dconv), _P(staging), _P(dw), _P(dx),
+          _st(), launches=3 if Cin == 3 else (5 if dx is not None else 4),
+          tag=(f"[{Cin}->{Cout}@{H}]" if _PROFILE is not None else ""))
+
+
+def pack_conv_weights_multi(ws, wfs, wds, zeros, zero_ns, couts, cins):
+    n = len(ws)
+    _call("ddpx_pack_conv_weights_multi", c_int(n), _ptr_array(ws), _ptr_array(wfs), _ptr_array(wds), _ptr_array(zeros),
+          (c_int * n)(*zero_ns), (c_int * n)(*couts), (c_int * n)(*cins), _st())
+
+
 def pack_conv_weights(w, w_fprop, w_dgrad, Cout, Cin):
     _call("ddpx_pack_conv_weights", _P(w), _P(w_fprop), _P(w_dgrad), c_int(Cout), c_int(Cin), _st())
 

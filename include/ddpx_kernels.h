@@ -60,6 +60,8 @@ int ddpx_conv3x3_wgrad(const float* dy, const float* x, float* dw, int Nimg, int
 int ddpx_conv3x3_wgrad_packed(const float* dy, const float* x, float* dw_packed, int Nimg, int H, int W, int Cin, int Cout,
                               int split_k, void* stream);
 int ddpx_unpack_conv_wgrad(const float* dw_packed, float* dw, int Cout, int Cin, void* stream);
+/* same, and the staging buffer is left all-zero: a persistent per-layer staging buffer never needs a memset launch */
+int ddpx_unpack_conv_wgrad_rezero(float* dw_packed, float* dw, int Cout, int Cin, void* stream);
 /* RGB stem on tensor cores (M:53 conv0, K = 27 padded to 32): patches[P][32] = im2col(x_nchw); forward =
  * ddpx_conv1x1_fprop(patches, wp[Cout][32]) with the same epilogue as the 3x3 kernel; weight gradient =
  * ddpx_gemm(dy^T, patches) with split-K. */
@@ -72,6 +74,10 @@ int ddpx_conv1x1_fprop(const float* x, const float* wpacked, float* y, int Nimg,
 /* ---- convolution helpers (csrc/kernels/conv_aux.cu) ---------------------------------------- */
 /* torch-layout weights [Cout][Cin][3][3] -> w_fprop [tap][Cout][Cin] and/or w_dgrad [8-tap][Cin][Cout] (either may be NULL) */
 int ddpx_pack_conv_weights(const float* w, float* w_fprop, float* w_dgrad, int Cout, int Cin, void* stream);
+/* the same for n <= 32 layers in ONE launch; zero[i] / zero_n[i]: floats to clear per layer (BatchNorm accumulators), may
+ * be NULL; Cin[i] == 3 marks the RGB stem (wf[i] = [Cout][32] zero-padded rows, wd[i] ignored) */
+int ddpx_pack_conv_weights_multi(int n, const void* const* w, void* const* wf, void* const* wd, void* const* zero,
+                                 const int* zero_n, const int* Cout, const int* Cin, void* stream);
 /* RGB stem (Cin == 3, K = 27): direct conv, NCHW input -> NHWC output, optional bias / ReLU / BN statistics (M:53 conv0) */
 int ddpx_conv_stem_fprop(const float* x_nchw, const float* w, const float* bias, float* y_nhwc, int Nimg, int H, int W,
                          int Cout, int act, float* stat_sum, float* stat_sq, void* stream);
@@ -100,6 +106,12 @@ int ddpx_bn_eval_stats(const float* running_mean, const float* running_var, floa
 int ddpx_bn_stats(const float* x, long long P, int C, float* sum, float* sq, void* stream);
 int ddpx_bn_apply(const float* x, float* y, const float* mean, const float* rstd, const float* gamma, const float* beta,
                   int Nimg, int H, int W, int C, int relu, int pool, void* stream);
+/* finalize + running-statistics update + normalise (+ReLU, +pool) in ONE launch from the convolution epilogue's raw
+ * (sum, sum of squares); training = 0 normalises with the running statistics.  mean_rstd [2][C] is an output. */
+int ddpx_bn_apply_stats(const float* x, float* y, const float* sum, const float* sq, float count, float eps, float momentum,
+                        const float* gamma, const float* beta, float* running_mean, float* running_var,
+                        long long* num_batches_tracked, float* mean_rstd, int training, int Nimg, int H, int W, int C,
+                        int relu, int pool, void* stream);
 /* one-call training forward: statistics -> finalize -> apply; `workspace` = 2*C floats of scratch (cleared by the call),
  * `mean_rstd` = [2][C] output saved for the backward */
 int ddpx_bn_train_fwd(const float* x, float* y, const float* gamma, const float* beta, float* running_mean,
@@ -121,6 +133,26 @@ int ddpx_bn_bwd_reduce(const float* x, const float* dout, const float* mean, con
 int ddpx_bn_bwd_apply(const float* x, const float* dout, const float* mean, const float* rstd, const float* gamma,
                       const float* beta, const float* sum_dz, const float* sum_dzx, int Nimg, int H, int W, int C, int relu,
                       int pool, int use_batch_stats, float* dx, void* stream);
+
+/* ---- block-level entry points (csrc/kernels/blocks.cu): every kernel of a conv-BN-ReLU(-pool) group (M:53-59) and
+ * direction in one call; all workspaces are the caller's (see the comments in blocks.cu for each argument) ---------- */
+int ddpx_conv_bn_fwd(const float* x, const float* wf, const float* gamma, const float* beta, float* running_mean,
+                     float* running_var, long long* num_batches_tracked, float momentum, float eps, int Nimg, int H, int W,
+                     int Cin, int Cout, int relu, int pool, int training, float* stats, float* y, float* out,
+                     float* mean_rstd, float* patches, void* stream);
+int ddpx_conv_bn_bwd(const float* y, const float* dout, const float* xin, const float* wd, const float* mean_rstd,
+                     const float* gamma, const float* beta, int Nimg, int H, int W, int Cin, int Cout, int relu, int pool,
+                     int training, float* sums, float* dconv, float* staging, float* dw, float* dx, void* stream);
+
+/* ---- fused causal attention, bf16, head dimension 64 (csrc/kernels/attn_sm100.cu, attn_bwd_sm100.cu) ---------------
+ * qkv [B][T][3*H*64] (q | k | v, heads contiguous inside each), out / dout [B][T][H*64], lse2 / delta [B][H][Tp] fp32 with
+ * Tp = T rounded up to 128 (lse2 = base-2 log-sum-exp of the scaled scores; delta is scratch of the backward).
+ * No counterpart in the reference (a CNN); serves the GPT-2 configurations of BASELINE.json. */
+int ddpx_attn_fwd(const void* qkv, void* out, float* lse2, int B, int T, int H, float scale, void* stream);
+int ddpx_attn_bwd(const void* qkv, const void* out, const void* dout, const float* lse2, float* delta, void* dqkv, int B,
+                  int T, int H, float scale, void* stream);
+unsigned int ddpx_attn_read_error_word(void);
+unsigned int ddpx_attn_bwd_read_error_word(void);
 
 /* ---- losses and optimizers (csrc/kernels/loss_optim.cu) ------------------------------------ */
 /* softmax cross-entropy fwd+bwd fused (M:95): loss_sum[0] = mean NLL, dlogits = (softmax - onehot) * grad_scale / rows */
