@@ -68,6 +68,12 @@ struct TcParams {
                             // memory and stores whole 64/128-byte row segments (coalesced) instead of 16 B per lane
   int act;                  // 0 none, 1 relu, 2 gelu(tanh)
   const float* bias;        // GEMM: per output column; FPROP: per output channel (row)
+  int bias_bf16;            // GEMM: `bias` points at bf16 values (transformer layers keep their biases in bf16)
+  // split-K with an in-kernel fix-up (GEMM): partial tiles are reduced into the fp32 workspace `fix_ws` [M][N] with vector
+  // reductions; every epilogue warp counts its arrivals per sub-block in `fix_cnt`, and the warp that arrives last
+  // converts the finished sub-block to bf16 into `out` and leaves workspace and counter at zero for the next call
+  float* fix_ws;
+  unsigned int* fix_cnt;
   float* stat_sum;          // FPROP: per-channel sum / sum-of-squares of the raw conv output
   float* stat_sq;
 };
@@ -361,7 +367,16 @@ tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
         }
         if constexpr (kMode == MODE_GEMM) {
           if (row < p.M) {
-            if (p.atomic) {
+            if (p.fix_ws != nullptr) {
+              // host guarantees N % 32 == 0 and no batching: whole 128-byte row segments, eight vector reductions
+              float* o = p.fix_ws + static_cast<long long>(row) * p.N + n0 + c0;
+#pragma unroll
+              for (int j = 0; j < 32; j += 4)
+                asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(o + j), "f"(__uint_as_float(v[j]) * p.alpha),
+                             "f"(__uint_as_float(v[j + 1]) * p.alpha), "f"(__uint_as_float(v[j + 2]) * p.alpha),
+                             "f"(__uint_as_float(v[j + 3]) * p.alpha)
+                             : "memory");
+            } else if (p.atomic) {
               float* o = reinterpret_cast<float*>(p.out) + boff + static_cast<long long>(row) * p.ldo + n0 + c0;
 #pragma unroll
               for (int j = 0; j < 32; ++j)
@@ -372,7 +387,9 @@ tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
             // one bias load per lane per 32-column chunk, handed round with shuffles: a per-element __ldg put a
             // load-latency stall (and a branch) on every output element and paced the whole kernel (ncu: 25% long_sb)
             float bl = 0.f;
-            if (p.bias != nullptr && n0 + c0 + lane < p.N) bl = __ldg(p.bias + n0 + c0 + lane);
+            if (p.bias != nullptr && n0 + c0 + lane < p.N)
+              bl = p.bias_bf16 ? __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(p.bias)[n0 + c0 + lane])
+                               : __ldg(p.bias + n0 + c0 + lane);
             float f[32];
 #pragma unroll
             for (int j = 0; j < 32; ++j) f[j] = fmaf(__uint_as_float(v[j]), p.alpha, __shfl_sync(0xffffffffu, bl, j));
@@ -490,6 +507,43 @@ tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
         if (p.stat_sum != nullptr && row < p.M) {
           atomicAdd(p.stat_sum + row, ssum);
           atomicAdd(p.stat_sq + row, ssq);
+        }
+      }
+      if constexpr (kMode == MODE_GEMM) {
+        if (p.fix_ws != nullptr) {
+          // this warp's share of the item is in the workspace; the last of the num_splits arrivals for this sub-block
+          // (same warp slot of the same tile in every split) owns the finished sums
+          __threadfence();
+          __syncwarp();
+          unsigned int old = 0;
+          const int slot = ((m_blk * p.n_blocks + n_blk) * kCG + static_cast<int>(cta_rank)) * 8 + (warp - 4);
+          if (lane == 0) old = atomicAdd(p.fix_cnt + slot, 1u);
+          old = __shfl_sync(0xffffffffu, old, 0);
+          if (old == static_cast<unsigned int>(p.num_splits - 1)) {
+            __threadfence();
+            if (row < p.M) {
+              for (int cc = cc_begin; cc < cc_end; cc += 32) {
+                float* w = p.fix_ws + static_cast<long long>(row) * p.N + n0 + cc;
+                __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(p.out) + static_cast<long long>(row) * p.ldo + n0 + cc;
+                float4 q[8];
+#pragma unroll
+                for (int j = 0; j < 8; ++j) q[j] = __ldcg(reinterpret_cast<const float4*>(w) + j);
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                  __nv_bfloat162 h0 = __floats2bfloat162_rn(q[2 * j].x, q[2 * j].y), h1 = __floats2bfloat162_rn(q[2 * j].z, q[2 * j].w);
+                  __nv_bfloat162 h2 = __floats2bfloat162_rn(q[2 * j + 1].x, q[2 * j + 1].y), h3 = __floats2bfloat162_rn(q[2 * j + 1].z, q[2 * j + 1].w);
+                  uint4 u;
+                  u.x = *reinterpret_cast<uint32_t*>(&h0); u.y = *reinterpret_cast<uint32_t*>(&h1);
+                  u.z = *reinterpret_cast<uint32_t*>(&h2); u.w = *reinterpret_cast<uint32_t*>(&h3);
+                  reinterpret_cast<uint4*>(o)[j] = u;
+                }
+#pragma unroll
+                for (int j = 0; j < 8; ++j) reinterpret_cast<float4*>(w)[j] = make_float4(0.f, 0.f, 0.f, 0.f);
+              }
+            }
+            __syncwarp();
+            if (lane == 0) p.fix_cnt[slot] = 0u;
+          }
         }
       }
       tc_fence_before();
@@ -658,11 +712,12 @@ static int launch_tc(const CUtensorMap& a, const CUtensorMap& b, TcParams& p, cu
 using namespace ddpx;
 
 // Batched GEMM: problem (b1, b2) reads A + b1*a_bs1 + b2*a_bs2 (elements) etc.  All strides in elements.
-extern "C" int ddpx_gemm_batched(const void* A, const void* B, void* D, int M, int N, int K, long long lda, long long ldb,
-                                 long long ldd, int a_mn, int b_mn, int bf16, int out_bf16, const float* bias, int act,
-                                 float alpha, int split_k, int accumulate, int batch1, int batch2, long long a_bs1,
-                                 long long a_bs2, long long b_bs1, long long b_bs2, long long d_bs1, long long d_bs2,
-                                 int causal, void* stream_) {
+static int gemm_impl(const void* A, const void* B, void* D, int M, int N, int K, long long lda, long long ldb,
+                     long long ldd, int a_mn, int b_mn, int bf16, int out_bf16, const void* bias_, int bias_bf16, int act,
+                     float alpha, int split_k, int accumulate, int batch1, int batch2, long long a_bs1,
+                     long long a_bs2, long long b_bs1, long long b_bs2, long long d_bs1, long long d_bs2,
+                     int causal, void* stream_, float* fix_ws = nullptr, unsigned int* fix_cnt = nullptr) {
+  const float* bias = static_cast<const float*>(bias_);
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
   const int elt = bf16 ? 2 : 4;
   const int bk = 128 / elt, chunk = 128 / elt;
@@ -697,8 +752,16 @@ extern "C" int ddpx_gemm_batched(const void* A, const void* B, void* D, int M, i
   p.a_mn = a_mn; p.b_mn = b_mn;
   p.out = D; p.ldo = ldd; p.out_bf16 = out_bf16;
   p.atomic = (accumulate || p.num_splits > 1) ? 1 : 0;
-  if (p.atomic && out_bf16) return DDPX_ERR_ARG;
-  p.act = act; p.bias = bias;
+  if (fix_ws != nullptr) {
+    // split-K with the in-kernel fix-up: bf16 result, fp32 partial sums in the caller's (all-zero) workspace
+    if (!out_bf16 || N % 32 || batch1 * batch2 != 1 || accumulate || bias != nullptr || act != 0 || (ldd % 8) ||
+        (reinterpret_cast<uintptr_t>(D) & 15) || (reinterpret_cast<uintptr_t>(fix_ws) & 15) || fix_cnt == nullptr)
+      return DDPX_ERR_ARG;
+    p.fix_ws = fix_ws; p.fix_cnt = fix_cnt; p.atomic = 1;
+  } else if (p.atomic && out_bf16) {
+    return DDPX_ERR_ARG;
+  }
+  p.act = act; p.bias = bias; p.bias_bf16 = bias_bf16;
   {
     const int oe = out_bf16 ? 2 : 4;
     p.st_vec = ((ldd * oe) % 16 == 0 && (d_bs1 * oe) % 16 == 0 && (d_bs2 * oe) % 16 == 0 &&
@@ -739,6 +802,34 @@ extern "C" int ddpx_gemm_batched(const void* A, const void* B, void* D, int M, i
     if (!p.b_big && (rc = make_tmap(&tb, B, bf16, 4, dims, str, box, b_mn && !bf16)) != DDPX_OK) return rc;
   }
   return bf16 ? launch_tc<MODE_GEMM, true>(ta, tb, p, stream, cg) : launch_tc<MODE_GEMM, false>(ta, tb, p, stream, cg);
+}
+
+extern "C" int ddpx_gemm_batched(const void* A, const void* B, void* D, int M, int N, int K, long long lda, long long ldb,
+                                 long long ldd, int a_mn, int b_mn, int bf16, int out_bf16, const float* bias, int act,
+                                 float alpha, int split_k, int accumulate, int batch1, int batch2, long long a_bs1,
+                                 long long a_bs2, long long b_bs1, long long b_bs2, long long d_bs1, long long d_bs2,
+                                 int causal, void* stream_) {
+  return gemm_impl(A, B, D, M, N, K, lda, ldb, ldd, a_mn, b_mn, bf16, out_bf16, bias, 0, act, alpha, split_k, accumulate,
+                   batch1, batch2, a_bs1, a_bs2, b_bs1, b_bs2, d_bs1, d_bs2, causal, stream_);
+}
+
+// Split-K GEMM with a bf16 result and no separate memset / cast launches: D[M,N] (bf16) = op(A) op(B), K split `split_k`
+// ways.  ws = fp32 [M*N] and cnt = uint32 [(ceil(M/128) * ceil(N/64) + 1) * 16] must be ALL ZERO on entry and are left all
+// zero (persistent scratch: zero them once).  N % 32 == 0, ldd % 8 == 0.  Calls that share ws / cnt must be stream-ordered.
+extern "C" int ddpx_gemm_splitk_bf16(const void* A, const void* B, void* D, int M, int N, int K, long long lda, long long ldb,
+                                     long long ldd, int a_mn, int b_mn, int split_k, float* ws, unsigned int* cnt,
+                                     void* stream_) {
+  if (split_k < 1) return DDPX_ERR_ARG;
+  return gemm_impl(A, B, D, M, N, K, lda, ldb, ldd, a_mn, b_mn, 1, 1, nullptr, 0, 0, 1.0f, split_k, 0, 1, 1, 0, 0, 0, 0, 0, 0,
+                   0, stream_, ws, cnt);
+}
+
+// ddpx_gemm with the bias given in bf16 (bias_bf16 = 1) or fp32 (0)
+extern "C" int ddpx_gemm_bias(const void* A, const void* B, void* D, int M, int N, int K, long long lda, long long ldb,
+                              long long ldd, int a_mn, int b_mn, int bf16, int out_bf16, const void* bias, int bias_bf16,
+                              int act, int split_k, int accumulate, void* stream_) {
+  return gemm_impl(A, B, D, M, N, K, lda, ldb, ldd, a_mn, b_mn, bf16, out_bf16, bias, bias_bf16, act, 1.0f, split_k,
+                   accumulate, 1, 1, 0, 0, 0, 0, 0, 0, 0, stream_);
 }
 
 extern "C" int ddpx_gemm(const void* A, const void* B, void* D, int M, int N, int K, long long lda, long long ldb,

@@ -65,6 +65,9 @@ layernorm_bwd_kernel(const T* __restrict__ x, const T* __restrict__ dy, const T*
                      const float* __restrict__ mean, const float* __restrict__ rstd, T* __restrict__ dx,
                      float* __restrict__ dgamma, float* __restrict__ dbeta, long long rows, int C) {
   constexpr int V = VecOf<T>::N;
+  // rows up to 4 vectors per lane (C <= 1024 in bf16) stay in registers between the two passes over a row; wider rows
+  // are read again (from L1 / L2) for the second pass
+  constexpr bool kKeep = NV <= 4;
   extern __shared__ float acc[];   // [2][C]
   const int lane = threadIdx.x & 31;
   const long long warp0 = (static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
@@ -82,6 +85,7 @@ layernorm_bwd_kernel(const T* __restrict__ x, const T* __restrict__ dy, const T*
     const T* dr = dy + r * C;
     const float m = mean[r], rs = rstd[r];
     float s1 = 0.f, s2 = 0.f;
+    float kf[kKeep ? NV : 1][V], kd[kKeep ? NV : 1][V];      // x-hat and dy * gamma of this lane's columns
 #pragma unroll
     for (int j = 0; j < NV; ++j) {
       const int i = lane + j * 32;
@@ -95,6 +99,7 @@ layernorm_bwd_kernel(const T* __restrict__ x, const T* __restrict__ dy, const T*
           s1 += gd; s2 += gd * xh;
           ag[j][k] += d[k] * xh;
           ab[j][k] += d[k];
+          if constexpr (kKeep) { kf[j][k] = xh; kd[j][k] = gd; }
         }
       }
     }
@@ -105,12 +110,18 @@ layernorm_bwd_kernel(const T* __restrict__ x, const T* __restrict__ dy, const T*
     for (int j = 0; j < NV; ++j) {
       const int i = lane + j * 32;
       if (i < nvec) {
-        float f[V], d[V], g[V];
-        vload(xr + i * V, f); vload(dr + i * V, d); vload(gamma + i * V, g);
+        float f[V];
+        if constexpr (kKeep) {
 #pragma unroll
-        for (int k = 0; k < V; ++k) {
-          const float xh = (f[k] - m) * rs;
-          f[k] = rs * (d[k] * g[k] - a - xh * b);
+          for (int k = 0; k < V; ++k) f[k] = rs * (kd[j][k] - a - kf[j][k] * b);
+        } else {
+          float d[V], g[V];
+          vload(xr + i * V, f); vload(dr + i * V, d); vload(gamma + i * V, g);
+#pragma unroll
+          for (int k = 0; k < V; ++k) {
+            const float xh = (f[k] - m) * rs;
+            f[k] = rs * (d[k] * g[k] - a - xh * b);
+          }
         }
         vstore(dxr + i * V, f);
       }
@@ -128,9 +139,12 @@ layernorm_bwd_kernel(const T* __restrict__ x, const T* __restrict__ dy, const T*
     }
   }
   __syncthreads();
-  for (int c = threadIdx.x; c < C; c += blockDim.x) {
-    atomicAdd(dgamma + c, acc[c]);
-    atomicAdd(dbeta + c, acc[C + c]);
+  // one 16-byte vector reduction per four columns (C % 4 == 0; dgamma / dbeta are 16-byte aligned: checked on the host)
+  for (int c = threadIdx.x * 4; c < C; c += blockDim.x * 4) {
+    asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(dgamma + c), "f"(acc[c]), "f"(acc[c + 1]), "f"(acc[c + 2]),
+                 "f"(acc[c + 3]) : "memory");
+    asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(dbeta + c), "f"(acc[C + c]), "f"(acc[C + c + 1]),
+                 "f"(acc[C + c + 2]), "f"(acc[C + c + 3]) : "memory");
   }
 }
 
@@ -287,6 +301,7 @@ extern "C" int ddpx_layernorm_bwd(const void* x, const void* dy, const void* gam
   const int nv = (C / V + 31) / 32;
   const size_t smem = static_cast<size_t>(2) * C * sizeof(float);
   if (nv > 16 || smem > 48 * 1024) return DDPX_ERR_SHAPE;
+  if ((reinterpret_cast<uintptr_t>(dgamma) | reinterpret_cast<uintptr_t>(dbeta)) & 15) return DDPX_ERR_ALIGN;
   // every warp carries register accumulators across its rows: a few rows per warp amortise the final fold
   const int grid = cap_blocks((rows + 31) / 32, 148 * 2);
   if (is_bf16)

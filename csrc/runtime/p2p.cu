@@ -10,7 +10,8 @@
 //     covers - no NCCL call and no separate elementwise kernel on that path;
 //   * a pull-based broadcast (rank 0 packs tensors into its staging buffer, peers copy them out over NVLink) used for
 //     the initial parameter sync and the per-forward BatchNorm-buffer sync.
-// Every spin is bounded: after ~20 s a rank writes an error code into its pad and traps instead of hanging the box.
+// Every spin is bounded: after the configured timeout (ddpx_p2p_set_timeout) a rank writes an error code into its pad and
+// traps instead of hanging the box.
 #include <cuda_runtime.h>
 #include <cstdlib>
 #include <cuda_bf16.h>
@@ -30,10 +31,18 @@ constexpr int PAD_BCAST = 24;     // [1]  source finished packing broadcast gene
 constexpr int PAD_ACK = 32;       // [8]  peer r consumed broadcast generation g   (lives on the source's pad)
 constexpr int PAD_ERROR = 48;     // [1]  non-zero after a timed-out wait
 constexpr int PAD_COUNTER = 56;   // [4]  local CTA-arrival counters (never touched by peers)
-constexpr unsigned long long kTimeoutNs = 20ull * 1000ull * 1000ull * 1000ull;
+// How long a device-side flag wait may last before the rank gives up (writes PAD_ERROR, traps).  Set per device by
+// ddpx_p2p_set_timeout (config.wait_timeout_s, default 600 s like torch's process-group timeout): inter-rank skew is
+// legitimate - rank 0 writing a checkpoint while the peers already wait in the next step's collective (the reference saves
+// without a barrier, multigpu.py:118), a stalled data loader, a debugger.
+__device__ unsigned long long g_timeout_ns = 600ull * 1000ull * 1000ull * 1000ull;
 
 __device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
   asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+// monotonic publish: the flag only ever grows, whichever of two writers (two successive broadcast sources) lands last
+__device__ __forceinline__ void red_max_release_sys(uint32_t* p, uint32_t v) {
+  asm volatile("red.release.sys.global.max.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
 __device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
   uint32_t v;
@@ -51,7 +60,7 @@ __device__ __forceinline__ void wait_flag(uint32_t* flag, uint32_t gen, uint32_t
   const unsigned long long t0 = globaltimer();
   while (static_cast<int32_t>(ld_acquire_sys(flag) - gen) < 0) {
     __nanosleep(64);
-    if (globaltimer() - t0 > kTimeoutNs) {
+    if (globaltimer() - t0 > g_timeout_ns) {
       pad[PAD_ERROR] = code;
       __threadfence_system();
       asm volatile("trap;");
@@ -354,6 +363,155 @@ __device__ __forceinline__ void reduce_shard_nvls(const Peers& P, long long v0, 
 }
 
 // ------------------------------------------------------------------------------------------------
+// Shard update (two-shot / NVLS with an optimizer): rank r owns elements [e0, e1) of the bucket.  For every parameter
+// slot that intersects the shard it sums the gradient from every rank's bucket (or lets the NVSwitch do it), applies
+// SGD-momentum / AdamW to ITS slice of the parameter with ITS slice of the optimizer state, and stores the UPDATED
+// PARAMETER into every rank's bucket.  After the hand-over barrier every rank copies the slices it does not own from its
+// bucket into its parameters.  Compared with "all-gather the averaged gradient, then every rank updates the whole
+// bucket" this reads grad + param + state and writes param + state for 1/world of the bucket instead of all of it; the
+// rest is a plain copy.  (The full update of a 27 MB VGG bucket ran next to the bandwidth-bound BatchNorm backward and
+// cost it 124 instead of 70 us: profiles/raw/trace_w2_round2.log.)  Optimizer state is therefore current only on its
+// owner; FusedUpdate.gather_state() re-replicates it before a state_dict() or a bucket rebuild.
+// ------------------------------------------------------------------------------------------------
+template <typename T, int kW, int kU, bool kNvls>
+__device__ __forceinline__ void shard_update(const Peers& P, const Hyper& h, const SlotTable& slots, long long e0, long long e1) {
+  constexpr int V = Vec<T>::N;
+  const long long tid = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  const long long nth = static_cast<long long>(gridDim.x) * blockDim.x;
+  const bool has0 = (h.opt == 2) || (h.opt == 1 && h.momentum != 0.f);
+  const bool has1 = (h.opt == 2);
+  const bool rd0 = has0 && !(h.opt == 1 && h.first_step);
+  for (int si = 0; si < slots.n; ++si) {
+    const Slot& s = slots.s[si];
+    const long long a = max(s.offset, e0), b = min(s.offset + s.numel, e1);
+    if (a >= b) continue;
+    const long long j_first = a - s.offset;                       // first element of the slice inside the parameter
+    const uintptr_t align = reinterpret_cast<uintptr_t>(s.param) | (has0 ? reinterpret_cast<uintptr_t>(s.state0) : 0) |
+                            (has1 ? reinterpret_cast<uintptr_t>(s.state1) : 0) | static_cast<uintptr_t>(j_first * sizeof(T));
+    const long long nv = (align & 15) ? 0 : (b - a) / V;
+    uint4* pp = reinterpret_cast<uint4*>(static_cast<T*>(s.param) + j_first);
+    uint4* q0 = reinterpret_cast<uint4*>(static_cast<T*>(s.state0) + j_first);
+    uint4* q1 = reinterpret_cast<uint4*>(static_cast<T*>(s.state1) + j_first);
+    const long long vb = a / V;                                   // vector index of the slice inside the bucket (a % V == 0)
+    for (long long j0 = tid; j0 < nv; j0 += nth * kU) {
+      uint4 gq[kU][kNvls ? 1 : kW], pq[kU], aq[kU], bq[kU];
+#pragma unroll
+      for (int u = 0; u < kU; ++u) {
+        const long long j = j0 + u * nth;
+        if (j < nv) {
+          if constexpr (kNvls) {
+            const uint4* mc = reinterpret_cast<const uint4*>(P.mc) + vb + j;
+            if constexpr (sizeof(T) == 4)
+              asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0,%1,%2,%3}, [%4];"
+                           : "=r"(gq[u][0].x), "=r"(gq[u][0].y), "=r"(gq[u][0].z), "=r"(gq[u][0].w) : "l"(mc) : "memory");
+            else
+              asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v4.bf16x2 {%0,%1,%2,%3}, [%4];"
+                           : "=r"(gq[u][0].x), "=r"(gq[u][0].y), "=r"(gq[u][0].z), "=r"(gq[u][0].w) : "l"(mc) : "memory");
+          } else {
+#pragma unroll
+            for (int r = 0; r < kW; ++r)
+              if (r < P.world) gq[u][r] = reinterpret_cast<const uint4*>(P.buf[r])[vb + j];
+          }
+          pq[u] = pp[j];
+          if (rd0) aq[u] = q0[j];
+          if (has1) bq[u] = q1[j];
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < kU; ++u) {
+        const long long j = j0 + u * nth;
+        if (j >= nv) break;
+        float g[V], pf[V], s0[V], s1[V];
+        if constexpr (kNvls) {
+          unpack<T>(gq[u][0], g);
+        } else {
+#pragma unroll
+          for (int k = 0; k < V; ++k) g[k] = 0.f;
+#pragma unroll
+          for (int r = 0; r < kW; ++r) {
+            if (r < P.world) {
+              float f[V];
+              unpack<T>(gq[u][r], f);
+#pragma unroll
+              for (int k = 0; k < V; ++k) g[k] += f[k];
+            }
+          }
+        }
+        unpack<T>(pq[u], pf);
+        if (rd0) unpack<T>(aq[u], s0);
+        else {
+#pragma unroll
+          for (int k = 0; k < V; ++k) s0[k] = 0.f;
+        }
+        if (has1) unpack<T>(bq[u], s1);
+        update_regs<V>(h, g, pf, s0, s1);
+        const uint4 o = pack<T>(pf);
+        pp[j] = o;
+        if (has0) q0[j] = pack<T>(s0);
+        if (has1) q1[j] = pack<T>(s1);
+        if constexpr (kNvls) {
+          uint4* mc = reinterpret_cast<uint4*>(P.mc) + vb + j;
+          if constexpr (sizeof(T) == 4)
+            asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(mc), "r"(o.x), "r"(o.y), "r"(o.z), "r"(o.w) : "memory");
+          else
+            asm volatile("multimem.st.relaxed.sys.global.v4.bf16x2 [%0], {%1,%2,%3,%4};" ::"l"(mc), "r"(o.x), "r"(o.y), "r"(o.z), "r"(o.w) : "memory");
+        } else {
+#pragma unroll
+          for (int r = 0; r < kW; ++r)
+            if (r < P.world && r != P.rank) reinterpret_cast<uint4*>(P.buf[r])[vb + j] = o;
+        }
+      }
+    }
+    // scalar tail of the slice (and slices whose pointers are not 16-byte aligned)
+    for (long long j = nv * V + tid; j < b - a; j += nth) {
+      float g = 0.f;
+#pragma unroll 1
+      for (int r = 0; r < P.world; ++r) g += ldT(static_cast<const T*>(P.buf[r]) + a + j);
+      apply_update<T>(h, s, j_first + j, g);
+      const T pn = static_cast<const T*>(s.param)[j_first + j];
+#pragma unroll 1
+      for (int r = 0; r < P.world; ++r)
+        if (r != P.rank) static_cast<T*>(P.buf[r])[a + j] = pn;
+    }
+  }
+}
+
+// after the hand-over: parameters <- bucket for everything this rank does not own
+template <typename T>
+__device__ __forceinline__ void copy_foreign_params(const Peers& P, const SlotTable& slots, long long e0, long long e1) {
+  constexpr int V = Vec<T>::N;
+  constexpr int kU = 4;
+  const long long tid = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  const long long nth = static_cast<long long>(gridDim.x) * blockDim.x;
+  const T* bucket = static_cast<const T*>(P.buf[P.rank]);
+  for (int si = 0; si < slots.n; ++si) {
+    const Slot& s = slots.s[si];
+    const long long end = s.offset + s.numel;
+#pragma unroll 1
+    for (int part = 0; part < 2; ++part) {
+      // part 0: the slice before my shard; part 1: the slice after it
+      const long long a = part == 0 ? s.offset : max(s.offset, e1);
+      const long long b = part == 0 ? min(end, e0) : end;
+      if (a >= b) continue;
+      const long long j_first = a - s.offset;
+      T* dst = static_cast<T*>(s.param) + j_first;
+      const bool aligned = ((reinterpret_cast<uintptr_t>(dst) | static_cast<uintptr_t>(a * sizeof(T))) & 15) == 0;
+      const long long nv = aligned ? (b - a) / V : 0;
+      const uint4* src4 = reinterpret_cast<const uint4*>(bucket + a);
+      uint4* dst4 = reinterpret_cast<uint4*>(dst);
+      for (long long j0 = tid; j0 < nv; j0 += nth * kU) {
+        uint4 v[kU];
+#pragma unroll
+        for (int u = 0; u < kU; ++u) if (j0 + u * nth < nv) v[u] = src4[j0 + u * nth];
+#pragma unroll
+        for (int u = 0; u < kU; ++u) if (j0 + u * nth < nv) dst4[j0 + u * nth] = v[u];
+      }
+      for (long long j = nv * V + tid; j < b - a; j += nth) dst[j] = bucket[a + j];
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
 // fused all-reduce (+ optimizer).  n = bucket elements (multiple of the vector width).
 // mode 0 = two-shot, mode 1 = one-shot (requires opt != 0: the local bucket is not rewritten)
 // ------------------------------------------------------------------------------------------------
@@ -370,27 +528,38 @@ allreduce_fused_kernel(const Peers P, const uint32_t gen, const long long n, con
   __syncthreads();
 
   if (mode == 0 || mode == 2) {
-    // ---- 2. reduce my shard from every rank's bucket (fixed rank order => identical bits everywhere),
-    //         store it into every rank's bucket
     const long long per = (nvec + P.world - 1) / P.world;
-    const long long v0 = per * P.rank, v1 = min(v0 + per, nvec);
+    const long long v0 = min(per * P.rank, nvec), v1 = min(v0 + per, nvec);
+    if (h.opt != 0) {
+      // ---- 2. my shard: reduce (peer loads, fixed rank order => identical bits everywhere, or in the NVSwitch), update my
+      //         slice of the parameters / optimizer state, hand the updated parameters to every rank's bucket
+      const long long e0 = v0 * V, e1 = v1 * V;
+      if (mode == 2) shard_update<T, 1, 4, true>(P, h, slots, e0, e1);
+      else if (P.world <= 2) shard_update<T, 2, 4, false>(P, h, slots, e0, e1);
+      else if (P.world <= 4) shard_update<T, 4, 2, false>(P, h, slots, e0, e1);
+      else shard_update<T, kMaxRanks, 2, false>(P, h, slots, e0, e1);
+      // ---- 3. when the whole grid is done with the shard, tell every peer; 4. wait for every other shard
+      last_cta_does(pad + PAD_COUNTER, [&] {
+        for (int r = 0; r < P.world; ++r) st_release_sys(P.pad[r] + PAD_DONE + P.rank, gen);
+      });
+      if (threadIdx.x < P.world) wait_flag(pad + PAD_DONE + threadIdx.x, gen, pad, 0xA2000000u | threadIdx.x);
+      __syncthreads();
+      // ---- 5. the parameters this rank does not own come out of its bucket
+      if (P.world > 1) copy_foreign_params<T>(P, slots, e0, e1);
+      return;
+    }
+    // ---- plain all-reduce (no optimizer bound): reduce my shard, store the sum into every rank's bucket
     // U vectors per thread per trip, all peer loads issued before the first add: the ~2 us NVLink load latency needs
     // tens of 16-byte requests in flight per thread to reach link bandwidth
     if (mode == 2) reduce_shard_nvls<T>(P, v0, v1);
     else if (P.world <= 2) reduce_shard<T, 2, 8>(P, v0, v1);
     else if (P.world <= 4) reduce_shard<T, 4, 4>(P, v0, v1);
     else reduce_shard<T, kMaxRanks, 2>(P, v0, v1);
-    // ---- 3. when the whole grid is done with the shard, tell every peer
     last_cta_does(pad + PAD_COUNTER, [&] {
       for (int r = 0; r < P.world; ++r) st_release_sys(P.pad[r] + PAD_DONE + P.rank, gen);
     });
-    // ---- 4. wait until every shard of my bucket has been delivered
     if (threadIdx.x < P.world) wait_flag(pad + PAD_DONE + threadIdx.x, gen, pad, 0xA2000000u | threadIdx.x);
     __syncthreads();
-    // ---- 5. optimizer update of every parameter slot of the bucket from the (now averaged) local bucket
-    if (h.opt != 0) {
-      for (int si = 0; si < slots.n; ++si) update_slot<T, false>(P, h, slots.s[si]);
-    }
   } else {
     // ---- one-shot: every rank reduces the whole bucket from peer memory and updates its replica directly
     for (int si = 0; si < slots.n; ++si) update_slot<T, true>(P, h, slots.s[si]);
@@ -423,17 +592,20 @@ __device__ __forceinline__ void copy_bytes(uint8_t* dst, const uint8_t* src, lon
 }
 
 __global__ void __launch_bounds__(512)
-bcast_src_kernel(const Peers P, const uint32_t gen, uint8_t* staging, const __grid_constant__ CopyTable tab) {
+bcast_src_kernel(const Peers P, const uint32_t gen, const uint32_t prev_gen, uint8_t* staging,
+                 const __grid_constant__ CopyTable tab) {
   uint32_t* pad = P.pad[P.rank];
-  // the staging slot was last used two generations ago: wait until every peer consumed that one
-  if (gen >= 2 && threadIdx.x < P.world && static_cast<int>(threadIdx.x) != P.rank)
-    wait_flag(pad + PAD_ACK + threadIdx.x, gen - 2, pad, 0xB1000000u | threadIdx.x);
+  // prev_gen = the generation in which THIS rank last filled this staging slot as a source (0 = never): wait until every
+  // peer has consumed that one.  (Not "gen - 2": with changing sources the previous generations were acknowledged on
+  // other ranks' pads, and a source waiting for them on its own pad waited forever.)
+  if (prev_gen != 0 && threadIdx.x < P.world && static_cast<int>(threadIdx.x) != P.rank)
+    wait_flag(pad + PAD_ACK + threadIdx.x, prev_gen, pad, 0xB1000000u | threadIdx.x);
   __syncthreads();
   for (int i = 0; i < tab.n; ++i)
     copy_bytes(staging + tab.e[i].offset, static_cast<const uint8_t*>(tab.e[i].ptr), tab.e[i].bytes);
   last_cta_does(pad + PAD_COUNTER + 1, [&] {
     for (int r = 0; r < P.world; ++r)
-      if (r != P.rank) st_release_sys(P.pad[r] + PAD_BCAST, gen);
+      if (r != P.rank) red_max_release_sys(P.pad[r] + PAD_BCAST, gen);
   });
 }
 
@@ -493,6 +665,20 @@ extern "C" int ddpx_p2p_can_access(int dev, int peer) {
   int ok = 0;
   if (cudaDeviceCanAccessPeer(&ok, dev, peer) != cudaSuccess) return 0;
   return ok;
+}
+// Collective sequence numbers.  Every rank issues the same collectives in the same order, so a per-process counter gives
+// every all-reduce / broadcast the same generation number on every rank, whoever launches it (the Python backend object
+// or the native reducer).
+static unsigned int g_gen[2] = {0, 0};
+extern "C" unsigned int ddpx_p2p_next_gen(void) { g_gen[0] = (g_gen[0] + 1) & 0x7FFFFFFFu; return g_gen[0]; }
+extern "C" unsigned int ddpx_p2p_next_bcast_gen(void) { g_gen[1] = (g_gen[1] + 1) & 0x7FFFFFFFu; return g_gen[1]; }
+extern "C" void ddpx_p2p_reset_gens(void) { g_gen[0] = g_gen[1] = 0; }
+
+// device-side wait timeout of the current device, in seconds (> 0)
+extern "C" int ddpx_p2p_set_timeout(double seconds) {
+  if (!(seconds > 0.0)) return DDPX_ERR_ARG;
+  const unsigned long long ns = static_cast<unsigned long long>(seconds * 1e9);
+  return CUDA_OK(cudaMemcpyToSymbol(g_timeout_ns, &ns, sizeof(ns)));
 }
 extern "C" unsigned int ddpx_p2p_read_error(void* pad) {
   uint32_t v = 0;
@@ -573,9 +759,9 @@ extern "C" int ddpx_p2p_allreduce_nvls(int rank, int world, void* const* bufs, v
 }
 
 // broadcast one chunk: `ptrs[i]` (bytes[i] long) <-> staging offset offs[i].  is_src selects the role.
-extern "C" int ddpx_p2p_broadcast(int rank, int world, void* const* pads, int src, unsigned int gen, void* staging_of_src,
-                                  int n, void* const* ptrs, const long long* offs, const long long* bytes, int ctas,
-                                  void* stream) {
+extern "C" int ddpx_p2p_broadcast(int rank, int world, void* const* pads, int src, unsigned int gen, unsigned int prev_gen,
+                                  void* staging_of_src, int n, void* const* ptrs, const long long* offs,
+                                  const long long* bytes, int ctas, void* stream) {
   Peers P;
   int rc = fill_peers(P, rank, world, nullptr, pads);
   if (rc != DDPX_OK) return rc;
@@ -587,7 +773,7 @@ extern "C" int ddpx_p2p_broadcast(int rank, int world, void* const* pads, int sr
   if (ctas < 1) ctas = 1;
   if (ctas > 148) ctas = 148;
   cudaStream_t s = static_cast<cudaStream_t>(stream);
-  if (rank == src) bcast_src_kernel<<<ctas, 512, 0, s>>>(P, gen, static_cast<uint8_t*>(staging_of_src), tab);
+  if (rank == src) bcast_src_kernel<<<ctas, 512, 0, s>>>(P, gen, prev_gen, static_cast<uint8_t*>(staging_of_src), tab);
   else bcast_dst_kernel<<<ctas, 512, 0, s>>>(P, src, gen, static_cast<const uint8_t*>(staging_of_src), tab);
   return CUDA_OK(cudaGetLastError());
 }

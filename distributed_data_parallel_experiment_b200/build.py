@@ -86,6 +86,41 @@ def build(verbose: bool = True, force: bool = False) -> Path:
     return LIB_PATH
 
 
+EXT_SRC = REPO / "csrc" / "torch_ext" / "autograd_hooks.cpp"
+EXT_PATH = LIB_DIR / "ddpx_autograd.so"
+
+
+def build_torch_ext(verbose: bool = True, force: bool = False) -> Path:
+    """Compile the C++ autograd-hook extension (csrc/torch_ext) in-tree against the installed torch headers.
+    No CUDA and no nvcc involved; ~25 s with g++."""
+    import sysconfig
+    import torch
+    import logging
+    logging.getLogger("torch.utils.cpp_extension").setLevel(logging.ERROR)
+    from torch.utils import cpp_extension as ce
+    OBJ_DIR.mkdir(parents=True, exist_ok=True)
+    LIB_DIR.mkdir(parents=True, exist_ok=True)
+    h = hashlib.sha1(EXT_SRC.read_bytes())
+    h.update(torch.__version__.encode())
+    stamp = OBJ_DIR / "ddpx_autograd.sha1"
+    if EXT_PATH.exists() and stamp.exists() and stamp.read_text() == h.hexdigest() and not force:
+        return EXT_PATH
+    incs = [f"-I{p}" for p in ce.include_paths()] + [f"-I{sysconfig.get_paths()['include']}"]
+    libdir = ce.library_paths()[0]
+    abi = int(bool(torch._C._GLIBCXX_USE_CXX11_ABI))
+    cmd = [os.environ.get("CXX", "g++"), "-O2", "-std=c++17", "-fPIC", "-shared", f"-D_GLIBCXX_USE_CXX11_ABI={abi}",
+           "-DTORCH_EXTENSION_NAME=ddpx_autograd", "-DTORCH_API_INCLUDE_EXTENSION_H", *incs, str(EXT_SRC), "-o", str(EXT_PATH),
+           f"-L{libdir}", "-ltorch_python", "-ltorch", "-ltorch_cpu", "-lc10", f"-Wl,-rpath,{libdir}"]
+    if verbose:
+        print("[ddpx.build]", " ".join(cmd), flush=True)
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    if r.returncode != 0:
+        raise RuntimeError(f"torch extension build failed:\n{r.stdout}\n{r.stderr}")
+    stamp.write_text(h.hexdigest())
+    return EXT_PATH
+
+
 if __name__ == "__main__":
     p = build(verbose=True, force="--force" in sys.argv)
     print(p)
+    print(build_torch_ext(verbose=True, force="--force" in sys.argv))

@@ -29,7 +29,9 @@ class RuntimeConfig:
     comm_ctas: int = 64                 # CTAs of a communication kernel (64 x 512 threads measured best, 2 and 8 GPUs)
     fuse_optimizer: bool = True
     broadcast_buffers: bool = True      # DataParallel default (torch DDP default); DDPX_BROADCAST_BUFFERS=0 for diagnosis
-    wait_timeout_s: float = 30.0        # device-side flag waits give up after this long
+    early_buffer_sync: bool = True      # buffer broadcast of the next forward runs on the comm stream during backward
+    split_tail_bytes: int = 65536       # P2P: the parameters that become ready last (<= this many bytes) get a bucket of their own
+    wait_timeout_s: float = 600.0       # device-side flag waits and the control-plane store give up after this long (torch: 10 min)
     checkpoint_path: str = "checkpoint.pt"   # multigpu.py:111
     metrics_jsonl: str = ""
 
@@ -44,6 +46,8 @@ class RuntimeConfig:
         c.comm_ctas = _env_int("DDPX_COMM_CTAS", c.comm_ctas)
         c.fuse_optimizer = _env_int("DDPX_FUSE_OPTIMIZER", 1) == 1
         c.broadcast_buffers = _env_int("DDPX_BROADCAST_BUFFERS", 1) == 1
+        c.early_buffer_sync = _env_int("DDPX_EARLY_BUFFER_SYNC", 1) == 1
+        c.split_tail_bytes = _env_int("DDPX_SPLIT_TAIL_BYTES", c.split_tail_bytes)
         c.wait_timeout_s = float(_env_str("DDPX_WAIT_TIMEOUT_S", str(c.wait_timeout_s)))
         c.checkpoint_path = _env_str("DDPX_CHECKPOINT_PATH", c.checkpoint_path)
         c.metrics_jsonl = _env_str("DDPX_METRICS_JSONL", c.metrics_jsonl)

@@ -87,9 +87,15 @@ class StepMetrics:
     only once they have completed - so logging never puts a synchronisation into the training loop.
 
     One line per optimizer step: rank, step, device_ms, samples, samples_per_s, loss (when already on the host), world
-    size, and - on a data-parallel model - backend, number of buckets and whether the optimizer is fused."""
+    size, and - on a data-parallel model - backend, number of buckets, whether the optimizer is fused, and the
+    communication fields of ``comm_probe`` (c10d::Logger's runtime stats, logger.hpp:42-127): comm_ms (sum of the
+    buckets' kernel times), exposed_comm_ms (how long the compute stream waited for the last buckets) and per bucket
+    its bytes, kernel time, algorithm (oneshot / twoshot / nvls) and bus GB/s.  The probe reads the most recent
+    iteration's timers, so it is attached to the newest completed step of a flush."""
 
-    def __init__(self, path: str, rank: int = 0, device: Optional[torch.device] = None, static: Optional[dict] = None):
+    def __init__(self, path: str, rank: int = 0, device: Optional[torch.device] = None, static: Optional[dict] = None,
+                 comm_probe=None):
+        self.comm_probe = comm_probe
         self.rank = rank
         self.log = JsonlLogger(path.replace("{rank}", str(rank)) if path else "")
         self.cuda = torch.cuda.is_available() and device is not None and torch.device(device).type == "cuda"
@@ -123,7 +129,7 @@ class StepMetrics:
         self.flush(block=False)
 
     def flush(self, block: bool = True):
-        keep = []
+        keep, done = [], []
         for step, samples, a, b in self._pending:
             if self.cuda:
                 if not block and not b.query():
@@ -133,8 +139,16 @@ class StepMetrics:
                 ms = a.elapsed_time(b)
             else:
                 ms = (b - a) * 1e3
+            done.append((step, samples, ms))
+        for i, (step, samples, ms) in enumerate(done):
+            extra = {}
+            if self.comm_probe is not None and i == len(done) - 1 and not keep:
+                try:
+                    extra = self.comm_probe() or {}
+                except Exception as e:      # diagnostics must not take the training loop down
+                    extra = {"comm_probe_error": f"{type(e).__name__}: {e}"}
             self.log.log(rank=self.rank, step=step, device_ms=round(ms, 4), samples=samples,
-                         samples_per_s=round(samples / (ms / 1e3), 1) if ms > 0 else None, **self.static)
+                         samples_per_s=round(samples / (ms / 1e3), 1) if ms > 0 else None, **self.static, **extra)
         self._pending = keep
 
     def close(self):

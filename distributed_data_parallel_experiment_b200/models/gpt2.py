@@ -2,8 +2,9 @@
 
 Parameter names follow the Hugging Face GPT-2 layout (``wte``, ``wpe``, ``h.{i}.ln_1``, ``attn.c_attn`` ...) with
 ``nn.Linear``-style [out, in] weights; the LM head is tied to ``wte``.  Every matmul is the tcgen05 GEMM (bias / GELU
-fused in the epilogue), LayerNorm / softmax-cross-entropy / embedding are hand-written kernels, attention is a fused
-causal kernel - see ops/functional.py.
+fused in the epilogue), LayerNorm / softmax-cross-entropy / embedding are hand-written kernels, attention is ONE fused
+tcgen05 kernel forward and two backward (csrc/kernels/attn_sm100.cu, attn_bwd_sm100.cu; no [B,H,T,T] tensor), and on
+CUDA in bf16 a whole block runs as one autograd node over two native calls (csrc/kernels/blocks_lm.cu).
 """
 from __future__ import annotations
 
@@ -90,7 +91,18 @@ class Block(nn.Module):
         self.ln_2 = LayerNorm(cfg.n_embd)
         self.mlp = MLPBlock(cfg)
 
+    def _params(self):
+        return (self.ln_1.weight, self.ln_1.bias, self.attn.c_attn.weight, self.attn.c_attn.bias, self.attn.c_proj.weight,
+                self.attn.c_proj.bias, self.ln_2.weight, self.ln_2.bias, self.mlp.c_fc.weight, self.mlp.c_fc.bias,
+                self.mlp.c_proj.weight, self.mlp.c_proj.bias)
+
     def forward(self, x):
+        if x.is_cuda:
+            from ..ops import transformer as TR
+            params = self._params()
+            if TR.gpt2_block_supported(x, self.attn.n_head, params, 0.0) and self.ln_1.eps == self.ln_2.eps:
+                # the whole block as one autograd node over two native calls (csrc/kernels/blocks_lm.cu)
+                return TR.GPT2BlockFn.apply(x, self.attn.n_head, self.ln_1.eps, *params)
         x = FX.add(x, self.attn(self.ln_1(x)))
         x = FX.add(x, self.mlp(self.ln_2(x)))
         return x

@@ -411,3 +411,22 @@ def attn_error_word() -> int:
         fn.restype = ctypes.c_uint
         v |= int(fn())
     return v
+
+
+# ------------------------------------------------------------------------------------------------ transformer block
+def gpt2_block_fwd(x, params, acts, stats, tmp, out, B, T, C, H, eps):
+    """One GPT-2 block forward in one call (10 launches).  params / acts: lists of device pointers (ints)."""
+    _call("ddpx_gpt2_block_fwd", _P(x), (c_void_p * 12)(*params), (c_void_p * 7)(*acts), _P(stats), _P(tmp), _P(out),
+          c_int(B), c_int(T), c_int(C), c_int(H), c_float(eps), _st(), launches=10)
+
+
+def gpt2_block_bwd(x, dout, params, acts, stats, grads, dx, wsb, ws32, cnt, B, T, C, H):
+    _call("ddpx_gpt2_block_bwd", _P(x), _P(dout), (c_void_p * 12)(*params), (c_void_p * 7)(*acts), _P(stats),
+          (c_void_p * 12)(*grads), _P(dx), _P(wsb), _P(ws32), _P(cnt), c_int(B), c_int(T), c_int(C), c_int(H), _st(),
+          launches=30)
+
+
+def gemm_splitk_bf16(A, B, D, M, N, K, lda, ldb, ldd, a_mn, b_mn, split_k, ws, cnt):
+    """bf16 split-K GEMM with the fix-up inside the kernel; ws (fp32 [M*N]) and cnt (int32) all zero before and after."""
+    _call("ddpx_gemm_splitk_bf16", _P(A), _P(B), _P(D), c_int(M), c_int(N), c_int(K), c_longlong(lda), c_longlong(ldb),
+          c_longlong(ldd), c_int(a_mn), c_int(b_mn), c_int(split_k), _P(ws), _P(cnt), _st())

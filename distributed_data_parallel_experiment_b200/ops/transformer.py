@@ -188,3 +188,74 @@ class DropoutFn(Function):
         dx = torch.empty_like(gc)
         native.dropout(gc, dx, p, seed)       # same mask (counter-based RNG), same 1/(1-p) scale
         return dx, None
+
+
+_BLOCK_CALLS = os.environ.get("DDPX_BLOCK_CALLS", "1") not in ("0", "")
+_BLOCK_WS = {}       # (device index, M, C, B*H*Tp) -> (bf16 scratch [M, 9C], fp32 scratch): shared by every block, stream-ordered
+
+
+def _block_workspace(dev, M, C, lse_elems):
+    key = (dev.index, M, C, lse_elems)
+    ws = _BLOCK_WS.get(key)
+    if ws is None:
+        _BLOCK_WS.clear()            # one shape at a time: a new (batch, sequence) shape replaces the old scratch
+        # the fp32 scratch starts with the split-K accumulation area and comes with arrival counters: both must be zero
+        # before the first use and are left zero by the kernels that use them
+        ws = (torch.empty(M * 9 * C, device=dev, dtype=torch.bfloat16),
+              native.zero_(torch.empty(4 * C * C + 6 * C + lse_elems, device=dev, dtype=torch.float32)),
+              native.zero_(torch.empty(16 * (4 * C * C // 8192 + 64), device=dev, dtype=torch.int32)))
+        _BLOCK_WS[key] = ws
+    return ws
+
+
+class GPT2BlockFn(Function):
+    """A whole GPT-2 block (LayerNorm, qkv projection, fused causal attention, output projection, residual, LayerNorm,
+    MLP with GELU, residual) as ONE autograd node over two native calls (csrc/kernels/blocks_lm.cu).  bf16, 64-wide
+    heads, no dropout.  Activations needed by the backward live in one flat buffer; the backward's scratch is shared by
+    all blocks."""
+
+    # element offsets (in units of M*C) of the saved activations inside the flat buffer: LN1, qkv, attention, x1, LN2,
+    # fc pre-activation, fc activation
+    _OFFS = (0, 1, 4, 5, 6, 7, 11)
+    _TOTAL = 15
+
+    @staticmethod
+    def forward(ctx, x, n_head, eps, *params):
+        B, T, C = x.shape
+        M = B * T
+        xc = x if x.is_contiguous() else x.contiguous()
+        dev = x.device
+        Tp = (T + 127) // 128 * 128
+        lse_elems = B * n_head * Tp
+        acts = torch.empty(GPT2BlockFn._TOTAL * M * C, device=dev, dtype=torch.bfloat16)
+        stats = torch.empty(4 * M + lse_elems, device=dev, dtype=torch.float32)
+        out = torch.empty((B, T, C), device=dev, dtype=torch.bfloat16)
+        tmp = _block_workspace(dev, M, C, lse_elems)[0]          # first M*C elements double as the forward's scratch
+        base = acts.data_ptr()
+        act_ptrs = [base + o * M * C * 2 for o in GPT2BlockFn._OFFS]
+        pp = [p.data_ptr() for p in params]
+        native.gpt2_block_fwd(xc, pp, act_ptrs, stats, tmp, out, B, T, C, n_head, eps)
+        ctx.save_for_backward(xc, acts, stats, *params)
+        ctx.cfg = (B, T, C, n_head, lse_elems)
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        xc, acts, stats, *params = ctx.saved_tensors
+        B, T, C, n_head, lse_elems = ctx.cfg
+        M = B * T
+        dev = xc.device
+        do = dout if dout.is_contiguous() else dout.contiguous()
+        wsb, ws32, cnt = _block_workspace(dev, M, C, lse_elems)
+        grads = [torch.empty_like(p) for p in params]
+        dx = torch.empty_like(xc)
+        base = acts.data_ptr()
+        act_ptrs = [base + o * M * C * 2 for o in GPT2BlockFn._OFFS]
+        native.gpt2_block_bwd(xc, do, [p.data_ptr() for p in params], act_ptrs, stats, [g.data_ptr() for g in grads], dx,
+                              wsb, ws32, cnt, B, T, C, n_head)
+        return (dx, None, None, *grads)
+
+
+def gpt2_block_supported(x, n_head, params, dropout) -> bool:
+    return (_BLOCK_CALLS and x.is_cuda and x.dtype == torch.bfloat16 and x.dim() == 3 and x.shape[-1] == n_head * 64
+            and dropout == 0.0 and all(p.dtype == torch.bfloat16 and p.is_contiguous() for p in params))

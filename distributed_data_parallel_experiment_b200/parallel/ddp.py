@@ -67,6 +67,15 @@ class DataParallel(nn.Module):
             self._sync_module_states()
         self.reducer = Reducer(self._params, comm, self.bucket_bytes_cap,
                                first_bucket_bytes=self._first_bucket_bytes, fused=self.fused)
+        # X4 moved off the critical path: rank 0's buffers (BatchNorm running statistics) are final once ITS forward has
+        # run, so the broadcast that torch DDP issues at the head of the next forward is enqueued on the communication
+        # stream when the first gradient bucket launches and overlaps the rest of backward (it used to open every step
+        # with a flag round trip on the compute stream: 25 us + rank skew).  DDPX_EARLY_BUFFER_SYNC=0 restores the old place.
+        self._buffers_synced_early = False
+        self._early_event = None
+        if (self.broadcast_buffers and self._buffers_list and self.world_size > 1 and cfg.early_buffer_sync
+                and getattr(comm, "stream", None) is not None and hasattr(comm, "broadcast_tensors_")):
+            self.reducer.on_first_launch = self._early_buffer_sync
 
     # ------------------------------------------------------------------------------------------ construction
     def _verify_params(self):
@@ -112,13 +121,26 @@ class DataParallel(nn.Module):
         with torch.no_grad():
             self._flat_broadcast(self._buffers_list)
 
+    def _early_buffer_sync(self):
+        """Called by the reducer right after the first bucket of a synchronised backward was enqueued."""
+        comm = self.comm
+        with torch.no_grad(), torch.cuda.stream(comm.stream):
+            self._flat_broadcast(self._buffers_list)
+            ev = torch.cuda.Event()
+            ev.record(comm.stream)
+        self._early_event = ev
+        self._buffers_synced_early = True
+
     # ------------------------------------------------------------------------------------------ forward
     def forward(self, *inputs, **kwargs):
         grad_on = torch.is_grad_enabled()
         if grad_on and self.require_backward_grad_sync:
-            if self.reducer.rebuild_buckets() and self.fused is not None:
-                pass
-        if self.require_forward_param_sync and self.broadcast_buffers and self._buffers_list:
+            self.reducer.rebuild_buckets()
+        if self._buffers_synced_early:
+            # this forward's buffer broadcast already ran during the previous backward (see __init__)
+            self._buffers_synced_early = False
+            torch.cuda.current_stream().wait_event(self._early_event)
+        elif self.require_forward_param_sync and self.broadcast_buffers and self._buffers_list:
             self._sync_buffers()
         out = self.module(*inputs, **kwargs)
         if grad_on and self.require_backward_grad_sync:

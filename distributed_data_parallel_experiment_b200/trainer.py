@@ -78,7 +78,27 @@ class Trainer:
             info = self.model.get_logging_data()
             static.update(backend=info["backend"], fused_optimizer=info["fused_optimizer"])
         from . import metrics as _metrics
-        self._metrics = _metrics.StepMetrics(config.get().metrics_jsonl, self._rank, self.device, static)
+        self._metrics = _metrics.StepMetrics(config.get().metrics_jsonl, self._rank, self.device, static,
+                                             comm_probe=self._comm_probe if isinstance(self.model, DataParallel) else None)
+        if self._metrics.enabled and isinstance(self.model, DataParallel) and self.device.type == "cuda":
+            self.model.measure_exposed_comm(True)
+
+    def _comm_probe(self) -> dict:
+        """Communication fields of a metrics line: per-bucket kernel time / algorithm / bus bandwidth from the native
+        reducer's device timers, and the exposed communication of the last synchronised backward."""
+        red = self.model.reducer
+        out = {}
+        buckets = red.bucket_times() if hasattr(red, "bucket_times") else []
+        if buckets:
+            out["buckets"] = [{k: (round(v, 4) if isinstance(v, float) else v) for k, v in b.items()} for b in buckets]
+            out["comm_ms"] = round(sum(b["ms"] for b in buckets if b["ms"] is not None), 4)
+        evs = red.stats.get("exposed_events") or []
+        if evs:
+            a, b = evs[-1]
+            b.synchronize()
+            out["exposed_comm_ms"] = round(a.elapsed_time(b), 4)
+            del evs[:-4]
+        return out
 
     def _describe_state(self) -> str:
         parts = [f"global step {self.global_step}"]

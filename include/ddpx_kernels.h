@@ -36,6 +36,17 @@ int ddpx_gemm(const void* A, const void* B, void* D, int M, int N, int K, long l
               long long ldd, int a_mn, int b_mn, int bf16, int out_bf16, const float* bias, int act,
               int split_k, int accumulate, void* stream);
 
+/* the same with the bias in bf16 (bias_bf16 = 1) or fp32 (0): transformer layers keep their biases in the activation dtype */
+int ddpx_gemm_bias(const void* A, const void* B, void* D, int M, int N, int K, long long lda, long long ldb, long long ldd,
+                   int a_mn, int b_mn, int bf16, int out_bf16, const void* bias, int bias_bf16, int act, int split_k,
+                   int accumulate, void* stream);
+
+/* Split-K GEMM, bf16 in and out, with the fix-up inside the kernel (no memset / cast launches): partial tiles are reduced into
+ * ws (fp32 [M*N]); the epilogue warp that delivers the last partial sum of a sub-block converts it into D and clears ws.
+ * ws and cnt (uint32 [(ceil(M/128)*ceil(N/64)+1)*16]) must be all zero on entry and are left all zero. */
+int ddpx_gemm_splitk_bf16(const void* A, const void* B, void* D, int M, int N, int K, long long lda, long long ldb,
+                          long long ldd, int a_mn, int b_mn, int split_k, float* ws, unsigned int* cnt, void* stream);
+
 /* Batched form: problem (b1,b2), b1 < batch1, b2 < batch2, reads A + b1*a_bs1 + b2*a_bs2 (element strides), same for
  * B and D; D = act(alpha * A*B + bias).  causal = 1 skips output tiles entirely above the diagonal (attention scores),
  * causal = 2 stops the K loop at the diagonal (probabilities x values).  Used for the attention GEMMs of GPT-2. */
@@ -144,6 +155,18 @@ int ddpx_conv_bn_bwd(const float* y, const float* dout, const float* xin, const 
                      const float* gamma, const float* beta, int Nimg, int H, int W, int Cin, int Cout, int relu, int pool,
                      int training, float* sums, float* dconv, float* staging, float* dw, float* dx, void* stream);
 
+/* ---- a whole GPT-2 block per direction in one call (csrc/kernels/blocks_lm.cu; bf16, 64-wide heads).  params[12] =
+ * ln_1.{weight,bias}, attn.c_attn.{weight,bias}, attn.c_proj.{weight,bias}, ln_2.{weight,bias}, mlp.c_fc.{weight,bias},
+ * mlp.c_proj.{weight,bias}; acts[7] = LN1 out, qkv, attention out, x1, LN2 out, fc pre-activation, fc activation (kept
+ * for the backward); stats = fp32 [4*B*T + B*H*Tp]; tmp = bf16 [B*T, C]; backward scratch: wsb = bf16 [B*T, 9C],
+ * ws32 = fp32 [4C*C + 6C + B*H*Tp] (first 4C*C all zero on entry, left all zero), cnt = uint32 [16*(4C*C/8192 + 64)] all
+ * zero on entry and exit.  Nothing is allocated.  No counterpart in the reference (a CNN). */
+int ddpx_gpt2_block_fwd(const void* x, void* const* params, void* const* acts, float* stats, void* tmp, void* out, int B,
+                        int T, int C, int H, float eps, void* stream);
+int ddpx_gpt2_block_bwd(const void* x, const void* dout, void* const* params, void* const* acts, const float* stats,
+                        void* const* grads, void* dx, void* wsb, float* ws32, unsigned int* cnt, int B, int T, int C, int H,
+                        void* stream);
+
 /* ---- fused causal attention, bf16, head dimension 64 (csrc/kernels/attn_sm100.cu, attn_bwd_sm100.cu) ---------------
  * qkv [B][T][3*H*64] (q | k | v, heads contiguous inside each), out / dout [B][T][H*64], lse2 / delta [B][H][Tp] fp32 with
  * Tp = T rounded up to 128 (lse2 = base-2 log-sum-exp of the scaled scores; delta is scratch of the backward).
@@ -213,6 +236,12 @@ int ddpx_p2p_import(const unsigned char* handle64, void** out);
 int ddpx_p2p_unimport(void* p);
 int ddpx_p2p_can_access(int dev, int peer);
 unsigned int ddpx_p2p_read_error(void* pad);
+/* how long a device-side flag wait may last on the current device before the rank traps (seconds; default 600) */
+int ddpx_p2p_set_timeout(double seconds);
+/* collective sequence numbers shared by every launcher in the process (same order on every rank => same numbers) */
+unsigned int ddpx_p2p_next_gen(void);
+unsigned int ddpx_p2p_next_bcast_gen(void);
+void ddpx_p2p_reset_gens(void);
 int ddpx_p2p_allreduce_fused(int rank, int world, void* const* bufs, void* const* pads, unsigned int gen, long long n,
                              int is_bf16, int mode, int opt, const float* hyper, int nesterov, int first_step, int nslots,
                              void* const* params, void* const* state0, void* const* state1, const long long* offsets,
@@ -223,12 +252,35 @@ int ddpx_p2p_allreduce_nvls(int rank, int world, void* const* bufs, void* mc_buf
                             long long n, int is_bf16, int opt, const float* hyper, int nesterov, int first_step, int nslots,
                             void* const* params, void* const* state0, void* const* state1, const long long* offsets,
                             const long long* numels, int ctas, void* stream);
-int ddpx_p2p_broadcast(int rank, int world, void* const* pads, int src, unsigned int gen, void* staging_of_src, int n,
-                       void* const* ptrs, const long long* offs, const long long* bytes, int ctas, void* stream);
+/* prev_gen: the generation in which `src` last filled the same staging slot as a source (0 = never); the source waits for
+ * every peer's acknowledgement of that generation before it overwrites the slot */
+int ddpx_p2p_broadcast(int rank, int world, void* const* pads, int src, unsigned int gen, unsigned int prev_gen,
+                       void* staging_of_src, int n, void* const* ptrs, const long long* offs, const long long* bytes,
+                       int ctas, void* stream);
 
 /* ---- reducer core (csrc/runtime/reducer_core.cpp): host-side bucket assignment + ready/launch state machine ----
  * Counterpart of c10d::compute_bucket_assignment_by_size and the bookkeeping of c10d::Reducer that torch DDP builds
  * for the reference at M:89. */
+/* ---- native reducer (csrc/runtime/reducer.cu): per-gradient / per-bucket work of a synchronised backward without Python:
+ * ready counting, strict bucket order, gradient gather (x 1/world), event hand-over to the communication stream, launch of
+ * the fused all-reduce(+optimizer) kernel, completion events, per-bucket device timers.  The hot half of c10d::Reducer
+ * (M:89); driven by the C++ autograd hooks of csrc/torch_ext/autograd_hooks.cpp. */
+void* ddpx_nreducer_create(int n_params, int n_buckets, const int* bucket_of_param, int rank, int world, void* const* pads,
+                           void* comm_stream, int ctas);
+void ddpx_nreducer_destroy(void* h);
+int ddpx_nreducer_set_bucket(void* h, int b, int n, const int* pids, const long long* offsets, const long long* numels,
+                             void* const* bufs, void* mc, long long numel, int is_bf16);
+int ddpx_nreducer_set_slots(void* h, int b, int n, void* const* params, void* const* state0, void* const* state1);
+int ddpx_nreducer_set_step(void* h, int b, int mode, int opt, const float* hyper9, int nesterov, int first_step);
+void ddpx_nreducer_arm(void* h, int timing);
+/* returns flags: 1 a bucket launched, 2 all buckets launched, 4 the iteration's first bucket launched; < 0 error */
+int ddpx_nreducer_mark_ready(void* h, int pid, const void* grad_ptr, void* compute_stream);
+int ddpx_nreducer_wait(void* h, void* compute_stream);
+int ddpx_nreducer_bucket_times(void* h, float* out_ms, int* out_mode, int max_out);
+int ddpx_nreducer_ready_order(void* h, int* out, int max_out);
+int ddpx_nreducer_unmarked(void* h, int* out, int max_out);
+int ddpx_nreducer_launched(void* h);
+
 /* ---- control-plane store (csrc/runtime/store.cpp): TCP key-value store hosted by rank 0; the bootstrap exchanges CUDA-IPC
  * handles, bucket orders and barriers through it.  Status < 0: -1 missing key / timeout, -2 connection, <= -16 buffer too
  * small (-16 - needed).  Stands where c10d::TCPStore stands for the reference (multigpu.py:30-32). */

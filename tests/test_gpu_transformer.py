@@ -94,6 +94,50 @@ def test_flash_attention_matches_materialised_path(monkeypatch):
     assert rel_l2(res[0][0], res[1][0]) < 2e-2 and rel_l2(res[0][1], res[1][1]) < 3e-2
 
 
+@pytest.mark.parametrize("B,T,C,H", [(2, 256, 128, 2), (1, 200, 256, 4), (4, 1024, 768, 12)])
+def test_gpt2_block_single_call_matches_per_op_path(monkeypatch, B, T, C, H):
+    """The block as one autograd node over two native calls (blocks_lm.cu) against the same block run op by op."""
+    from distributed_data_parallel_experiment_b200.ops import transformer as TR
+    from distributed_data_parallel_experiment_b200.models.gpt2 import Block, GPT2Config
+    torch.manual_seed(11)
+    blk = Block(GPT2Config(n_embd=C, n_head=H, n_layer=1)).cuda().bfloat16()
+    for p in blk.parameters():
+        torch.nn.init.normal_(p, std=0.05 if p.dim() > 1 else 0.1)      # non-trivial biases and LayerNorm parameters
+    blk.ln_1.weight.data.add_(1.0); blk.ln_2.weight.data.add_(1.0)
+    x = torch.randn(B, T, C, device="cuda").bfloat16()
+    g = torch.randn(B, T, C, device="cuda").bfloat16()
+    res = []
+    for fused in (True, False):
+        monkeypatch.setattr(TR, "_BLOCK_CALLS", fused)
+        blk.zero_grad()
+        xi = x.clone().requires_grad_()
+        y = blk(xi)
+        y.backward(g)
+        res.append((y.detach(), xi.grad, {n: p.grad.clone() for n, p in blk.named_parameters()}))
+    assert rel_l2(res[0][0], res[1][0]) < 1e-2
+    assert rel_l2(res[0][1], res[1][1]) < 2e-2
+    for n in res[0][2]:
+        assert rel_l2(res[0][2][n], res[1][2][n]) < 3e-2, n
+
+
+@pytest.mark.parametrize("Mo,No,Kr,split", [(768, 3072, 8192, 2), (1600, 1600, 2048, 3), (200, 96, 4096, 8), (2304, 768, 4096, 1)])
+def test_splitk_gemm_with_in_kernel_fixup(Mo, No, Kr, split):
+    """dW = d^T x (both operands MN-major) split along the token dimension; the last-arriving epilogue warp converts the fp32
+    partial sums to bf16 and leaves workspace and counters at zero, so the same scratch serves the next call."""
+    torch.manual_seed(7)
+    d = (torch.randn(Kr, Mo, device="cuda") * 0.1).bfloat16()
+    x = (torch.randn(Kr, No, device="cuda") * 0.1).bfloat16()
+    ws = torch.zeros(Mo * No, device="cuda", dtype=torch.float32)
+    cnt = torch.zeros(16 * ((Mo + 127) // 128 * ((No + 63) // 64) + 1), device="cuda", dtype=torch.int32)
+    ref = d.double().t() @ x.double()
+    for _ in range(2):                                  # second call reuses the scratch the first one left behind
+        out = torch.empty(Mo, No, device="cuda", dtype=torch.bfloat16)
+        native.gemm_splitk_bf16(d, x, out, Mo, No, Kr, Mo, No, No, 1, 1, split, ws, cnt)
+        torch.cuda.synchronize()
+        assert rel_l2(out, ref) < 1e-2
+        assert float(ws.abs().max()) == 0.0 and int(cnt.abs().max()) == 0
+
+
 def test_embedding_sum_and_padded_ce():
     torch.manual_seed(3)
     V, Vp, C, B, T = 1000, 1024, 128, 4, 64
