@@ -24,11 +24,12 @@ if model_name == "vgg":
     tr = ddpx.Trainer(objs.model, [], objs.optimizer, local_rank, 1, scheduler=objs.scheduler)
     x = torch.rand(512, 3, 32, 32, device="cuda"); y = torch.randint(0, 10, (512,), device="cuda")
     first_kernel = "im2col"
-else:                                   # gpt2 | gpt2-medium | ... : batch 8 x seq 1024, bf16, AdamW
+else:                                   # gpt2 | gpt2-medium | ... [batch]: seq 1024, bf16, AdamW
     objs, loss_fn = ddpx.recipes.make(model_name, world_size=world, synthetic=True, synthetic_size=0)
     tr = ddpx.Trainer(objs.model, [], objs.optimizer, local_rank, 1, loss_fn=loss_fn)
     V = objs.model.cfg.vocab_size
-    x = torch.randint(0, V, (8, 1024), device="cuda"); y = torch.randint(0, V, (8, 1024), device="cuda")
+    Bt = int(sys.argv[2]) if len(sys.argv) > 2 else (2 if "xl" in model_name else 8)     # BASELINE.json micro-batches
+    x = torch.randint(0, V, (Bt, 1024), device="cuda"); y = torch.randint(0, V, (Bt, 1024), device="cuda")
     first_kernel = "embedding"
 for _ in range(6):
     tr._run_batch(x, y)

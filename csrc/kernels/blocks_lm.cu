@@ -27,11 +27,12 @@ int linear_fwd(const void* x, const void* W, const void* b, void* y, int M, int 
 }
 
 // Backward of y = x W^T + b for bf16 tensors: dx[M,K] = d W (skipped when dx is null), dW[N,K] = d^T x, db[N] = colsum(d).
-// ws32: fp32 scratch of at least N*K + N elements: [0, N*K) accumulates a split-K dW and must be ALL ZERO on entry (the
-// GEMM's in-kernel fix-up converts the finished sums to bf16 and leaves it zero again - no memset, no cast launch),
-// [N*K, N*K + N) takes the bias sums.  cnt: the fix-up's arrival counters (all zero on entry and on exit).
-int linear_bwd(const void* d, const void* x, const void* W, void* dx, void* dW, void* db, float* ws32, unsigned int* cnt, int M,
-               int N, int K, void* stream) {
+// ws32: fp32 scratch of at least N*K elements that accumulates a split-K dW and must be ALL ZERO on entry (the GEMM's
+// in-kernel fix-up converts the finished sums to bf16 and leaves it zero again - no memset, no cast launch); db32: N floats
+// for the bias sums, OUTSIDE that zero-invariant area (layers of different sizes share ws32 from offset 0);
+// cnt: the fix-up's arrival counters (all zero on entry and on exit).
+int linear_bwd(const void* d, const void* x, const void* W, void* dx, void* dW, void* db, float* ws32, float* db32,
+               unsigned int* cnt, int M, int N, int K, void* stream) {
   if (dx != nullptr) CHECK(ddpx_gemm(d, W, dx, M, K, N, N, K, K, 0, 1, 1, 1, nullptr, 0, 1, 0, stream));     // d[M,N] @ W[N,K]
   // A weight gradient has few output tiles and a long reduction (the tokens): when 256x256 tiles cannot fill the 74 CTA
   // pairs, split the reduction and accumulate in fp32 (then cast) instead of shrinking the tiles.
@@ -47,7 +48,6 @@ int linear_bwd(const void* d, const void* x, const void* W, void* dx, void* dW, 
   } else {
     CHECK(ddpx_gemm(d, x, dW, N, K, M, N, K, K, 1, 1, 1, 1, nullptr, 0, 1, 0, stream));
   }
-  float* db32 = ws32 + static_cast<size_t>(N) * K;
   CHECK(ddpx_colsum_bf16(d, db32, M, N, stream));
   return ddpx_cast_scale(db32, db, N, 1.f, 0, stream);
 }
@@ -96,22 +96,23 @@ extern "C" int ddpx_gpt2_block_bwd(const void* x, const void* dout, void* const*
   bf16* d_a = d_fc + 4 * MC;                            // [M,C]
   bf16* d_b = d_a + MC;                                 // [M,C]
   bf16* dqkv = d_b + MC;                                // [M,3C]
-  float* lnacc = ws32 + static_cast<size_t>(4) * C * C + 4 * C;      // [2C] LayerNorm dgamma / dbeta accumulators
+  float* db32 = ws32 + static_cast<size_t>(4) * C * C;               // [4C] bias sums (behind the zero-invariant dW area)
+  float* lnacc = db32 + 4 * C;                                       // [2C] LayerNorm dgamma / dbeta accumulators
   float* delta = lnacc + 2 * C;                         // attention backward scratch [B*H*Tp]
 
   // ---- MLP: out = x1 + proj2(gelu(fc(LN2(x1))))
-  CHECK(linear_bwd(dout, acts[A_FCACT], params[PROJ2_W], d_fc, grads[PROJ2_W], grads[PROJ2_B], ws32, cnt, M, C, 4 * C, stream));
+  CHECK(linear_bwd(dout, acts[A_FCACT], params[PROJ2_W], d_fc, grads[PROJ2_W], grads[PROJ2_B], ws32, db32, cnt, M, C, 4 * C, stream));
   CHECK(ddpx_gelu_bwd(acts[A_FCPRE], d_fc, d_fc, 4 * MC, 1, stream));
-  CHECK(linear_bwd(d_fc, acts[A_LN2], params[FC_W], d_a, grads[FC_W], grads[FC_B], ws32, cnt, M, 4 * C, C, stream));
+  CHECK(linear_bwd(d_fc, acts[A_LN2], params[FC_W], d_a, grads[FC_W], grads[FC_B], ws32, db32, cnt, M, 4 * C, C, stream));
   if (cudaMemsetAsync(lnacc, 0, sizeof(float) * 2 * C, s) != cudaSuccess) return DDPX_ERR_LAUNCH;
   CHECK(ddpx_layernorm_bwd(acts[A_X1], d_a, params[LN2_W], ln2_mean, ln2_rstd, d_b, lnacc, lnacc + C, M, C, 1, stream));
   CHECK(ddpx_cast_scale(lnacc, grads[LN2_W], C, 1.f, 0, stream));
   CHECK(ddpx_cast_scale(lnacc + C, grads[LN2_B], C, 1.f, 0, stream));
   CHECK(ddpx_add(d_b, dout, d_b, MC, 1, stream));                       // d_x1 = through LN2 + the residual branch
   // ---- attention: x1 = x + proj(attention(qkv(LN1(x))))
-  CHECK(linear_bwd(d_b, acts[A_ATT], params[PROJ_W], d_a, grads[PROJ_W], grads[PROJ_B], ws32, cnt, M, C, C, stream));
+  CHECK(linear_bwd(d_b, acts[A_ATT], params[PROJ_W], d_a, grads[PROJ_W], grads[PROJ_B], ws32, db32, cnt, M, C, C, stream));
   CHECK(ddpx_attn_bwd(acts[A_QKV], acts[A_ATT], d_a, lse2, delta, dqkv, B, T, H, 0.125f, stream));
-  CHECK(linear_bwd(dqkv, acts[A_LN1], params[ATTN_W], d_a, grads[ATTN_W], grads[ATTN_B], ws32, cnt, M, 3 * C, C, stream));
+  CHECK(linear_bwd(dqkv, acts[A_LN1], params[ATTN_W], d_a, grads[ATTN_W], grads[ATTN_B], ws32, db32, cnt, M, 3 * C, C, stream));
   if (cudaMemsetAsync(lnacc, 0, sizeof(float) * 2 * C, s) != cudaSuccess) return DDPX_ERR_LAUNCH;
   CHECK(ddpx_layernorm_bwd(x, d_a, params[LN1_W], ln1_mean, ln1_rstd, dx, lnacc, lnacc + C, M, C, 1, stream));
   CHECK(ddpx_cast_scale(lnacc, grads[LN1_W], C, 1.f, 0, stream));

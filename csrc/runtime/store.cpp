@@ -177,7 +177,10 @@ struct Client {
 
 // ------------------------------------------------------------------------------------------------ C ABI
 // Errors: -1 = no such key / timeout, -2 = connection problem, -3 = buffer too small (needed size is returned negated - 16)
-extern "C" void* ddpx_store_server_start(int port, int* bound_port) {
+// bind_host: dotted IPv4 address to listen on (the job's MASTER_ADDR; "127.0.0.1" for the single-host jobs this framework
+// runs).  NULL / "" / "0.0.0.0" listens on every interface.  The store is unauthenticated and its Python client unpickles
+// what it reads, so it should never be reachable from outside the job: the default of the Python side is the loopback.
+extern "C" void* ddpx_store_server_start_on(const char* bind_host, int port, int* bound_port) {
   int fd = ::socket(AF_INET, SOCK_STREAM, 0);
   if (fd < 0) return nullptr;
   int one = 1;
@@ -185,6 +188,11 @@ extern "C" void* ddpx_store_server_start(int port, int* bound_port) {
   sockaddr_in addr{};
   addr.sin_family = AF_INET;
   addr.sin_addr.s_addr = htonl(INADDR_ANY);
+  if (bind_host != nullptr && bind_host[0] != 0) {
+    in_addr a{};
+    if (inet_pton(AF_INET, bind_host, &a) == 1) addr.sin_addr = a;
+    else { ::close(fd); return nullptr; }
+  }
   addr.sin_port = htons(static_cast<uint16_t>(port));
   if (::bind(fd, reinterpret_cast<sockaddr*>(&addr), sizeof(addr)) != 0 || ::listen(fd, 128) != 0) {
     ::close(fd);
@@ -198,6 +206,10 @@ extern "C" void* ddpx_store_server_start(int port, int* bound_port) {
   if (bound_port) *bound_port = s->port;
   s->thread = std::thread([s] { s->run(); });
   return s;
+}
+
+extern "C" void* ddpx_store_server_start(int port, int* bound_port) {
+  return ddpx_store_server_start_on(nullptr, port, bound_port);
 }
 
 extern "C" void ddpx_store_server_stop(void* h) {

@@ -18,6 +18,8 @@ def _fns():
     lib = _lib.lib()
     lib.ddpx_store_server_start.restype = ctypes.c_void_p
     lib.ddpx_store_server_start.argtypes = [ctypes.c_int, ctypes.POINTER(ctypes.c_int)]
+    lib.ddpx_store_server_start_on.restype = ctypes.c_void_p
+    lib.ddpx_store_server_start_on.argtypes = [ctypes.c_char_p, ctypes.c_int, ctypes.POINTER(ctypes.c_int)]
     lib.ddpx_store_server_stop.argtypes = [ctypes.c_void_p]
     lib.ddpx_store_connect.restype = ctypes.c_void_p
     lib.ddpx_store_connect.argtypes = [ctypes.c_char_p, ctypes.c_int, ctypes.c_int]
@@ -36,6 +38,11 @@ class StoreError(RuntimeError):
     pass
 
 
+def _is_ipv4(h: str) -> bool:
+    parts = h.split(".")
+    return len(parts) == 4 and all(p.isdigit() and 0 <= int(p) <= 255 for p in parts)
+
+
 class NativeStore:
     def __init__(self, host: str, port: int, rank: int, world_size: int, timeout_s: float = 60.0,
                  is_server: Optional[bool] = None):
@@ -46,7 +53,10 @@ class NativeStore:
         self.port = port
         if is_server if is_server is not None else rank == 0:
             bound = ctypes.c_int(0)
-            self._server = self._lib.ddpx_store_server_start(port, ctypes.byref(bound))
+            # listen only on the job's address (the loopback for the single-host jobs of this framework): the store is
+            # unauthenticated and values are unpickled by the clients, so it must not be reachable from elsewhere
+            bind = host if _is_ipv4(host) else "127.0.0.1"
+            self._server = self._lib.ddpx_store_server_start_on(bind.encode(), port, ctypes.byref(bound))
             if not self._server:
                 raise StoreError(f"store: cannot listen on port {port}")
             self.port = bound.value

@@ -284,7 +284,8 @@ int ddpx_nreducer_launched(void* h);
 /* ---- control-plane store (csrc/runtime/store.cpp): TCP key-value store hosted by rank 0; the bootstrap exchanges CUDA-IPC
  * handles, bucket orders and barriers through it.  Status < 0: -1 missing key / timeout, -2 connection, <= -16 buffer too
  * small (-16 - needed).  Stands where c10d::TCPStore stands for the reference (multigpu.py:30-32). */
-void* ddpx_store_server_start(int port, int* bound_port);       /* port 0 = pick one */
+void* ddpx_store_server_start(int port, int* bound_port);       /* port 0 = pick one; listens on every interface */
+void* ddpx_store_server_start_on(const char* bind_host, int port, int* bound_port);   /* listen on one IPv4 address only */
 void ddpx_store_server_stop(void* server);
 void* ddpx_store_connect(const char* host, int port, int timeout_ms);
 void ddpx_store_close(void* client);

@@ -114,10 +114,27 @@ def test_gpt2_block_single_call_matches_per_op_path(monkeypatch, B, T, C, H):
         y = blk(xi)
         y.backward(g)
         res.append((y.detach(), xi.grad, {n: p.grad.clone() for n, p in blk.named_parameters()}))
-    assert rel_l2(res[0][0], res[1][0]) < 1e-2
-    assert rel_l2(res[0][1], res[1][1]) < 2e-2
+    # oracle: the same block in float64 torch math
+    P = {n: p.detach().double().requires_grad_() for n, p in blk.named_parameters()}
+    xr = x.double().requires_grad_()
+    h = F.layer_norm(xr, (C,), P["ln_1.weight"], P["ln_1.bias"], blk.ln_1.eps)
+    q, k, v = F.linear(h, P["attn.c_attn.weight"], P["attn.c_attn.bias"]).split(C, dim=2)
+    q, k, v = (t.view(B, T, H, C // H).transpose(1, 2) for t in (q, k, v))
+    a = F.scaled_dot_product_attention(q, k, v, is_causal=True).transpose(1, 2).reshape(B, T, C)
+    x1 = xr + F.linear(a, P["attn.c_proj.weight"], P["attn.c_proj.bias"])
+    h2 = F.layer_norm(x1, (C,), P["ln_2.weight"], P["ln_2.bias"], blk.ln_2.eps)
+    m = F.linear(F.gelu(F.linear(h2, P["mlp.c_fc.weight"], P["mlp.c_fc.bias"]), approximate="tanh"),
+                 P["mlp.c_proj.weight"], P["mlp.c_proj.bias"])
+    yr = x1 + m
+    yr.backward(g.double())
+    for fused, (y, dx, grads) in zip((True, False), res):
+        assert rel_l2(y, yr) < 1e-2, fused
+        assert rel_l2(dx, xr.grad) < 3e-2, fused
+    # every parameter gradient of the single-call path is as close to the float64 oracle as the per-op path's is (both are
+    # chains of bf16 roundings: they differ from each other by about as much as each differs from the oracle)
     for n in res[0][2]:
-        assert rel_l2(res[0][2][n], res[1][2][n]) < 3e-2, n
+        e_fused, e_ops = rel_l2(res[0][2][n], P[n].grad), rel_l2(res[1][2][n], P[n].grad)
+        assert e_fused < 4e-2 and e_fused < 2.0 * e_ops + 5e-3, (n, e_fused, e_ops)
 
 
 @pytest.mark.parametrize("Mo,No,Kr,split", [(768, 3072, 8192, 2), (1600, 1600, 2048, 3), (200, 96, 4096, 8), (2304, 768, 4096, 1)])

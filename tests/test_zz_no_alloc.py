@@ -48,6 +48,16 @@ def _run_pair(lib, N, H, W, C, relu, pool, seed):
         assert rc == 0, f"{variant}: return code {rc}"
         torch.cuda.synchronize()
         outs.append((y, rm, rv, nbt, mr))
+    # independent oracle: plain PyTorch BatchNorm (+ReLU, +2x2 max-pool) in fp32 on the same data
+    import torch.nn.functional as F
+    xr = x.permute(0, 3, 1, 2).contiguous()
+    rm_ref = torch.zeros(C, device=dev); rv_ref = torch.ones(C, device=dev)
+    ref = F.batch_norm(xr, rm_ref, rv_ref, gamma, beta, True, 0.1, 1e-5)
+    if relu:
+        ref = F.relu(ref)
+    if pool:
+        ref = F.max_pool2d(ref, 2)
+    outs.append((ref.permute(0, 2, 3, 1).contiguous(), rm_ref, rv_ref))
     return outs
 
 
@@ -60,8 +70,10 @@ def test_static_scratch_variant_matches_workspace_variant_twice_in_a_row():
     lib = _lib.lib()
     # first call: 256 channels, ReLU + pool; second call right after it: fewer channels, other data, no pool
     for (N, H, W, C, relu, pool, seed) in [(8, 16, 16, 256, 1, 1, 0), (4, 8, 8, 64, 0, 0, 1)]:
-        (y0, rm0, rv0, n0, mr0), (y1, rm1, rv1, n1, mr1) = _run_pair(lib, N, H, W, C, relu, pool, seed)
+        (y0, rm0, rv0, n0, mr0), (y1, rm1, rv1, n1, mr1), (yr, rmr, rvr) = _run_pair(lib, N, H, W, C, relu, pool, seed)
         assert _close(y1, y0) and _close(mr1, mr0) and _close(rm1, rm0) and _close(rv1, rv0)
+        # and both agree with torch's own BatchNorm, output and running statistics
+        assert _close(y1, yr, 1e-4) and _close(rm1, rmr, 1e-4) and _close(rv1, rvr, 1e-4)
         assert int(n0) == 1 and int(n1) == 1
         assert torch.isfinite(y1).all()
 
