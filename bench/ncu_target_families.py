@@ -64,6 +64,14 @@ algo["layernorm_fwd"] = 2 * x.numel() * 2
 dgb = torch.zeros(2, Cm, device=dev); dx = torch.empty_like(x)
 native.layernorm_bwd(x, dy, g, sm[0], sm[1], dx, dgb[0], dgb[1], M, Cm)
 algo["layernorm_bwd"] = 3 * x.numel() * 2
+# the same at a GPT-2 XL micro-batch: 2048 x 1600
+Mx, Cx = 2048, 1600
+xx = torch.randn(Mx, Cx, device=dev).bfloat16(); dyx = torch.randn(Mx, Cx, device=dev).bfloat16()
+gx = (torch.rand(Cx, device=dev) + 0.5).bfloat16(); smx = torch.empty(2, Mx, device=dev); yx = torch.empty_like(xx)
+native.layernorm_fwd(xx, gx, gx, yx, smx[0], smx[1], Mx, Cx, 1e-5)
+dgbx = torch.zeros(2, Cx, device=dev)
+native.layernorm_bwd(xx, dyx, gx, smx[0], smx[1], yx, dgbx[0], dgbx[1], Mx, Cx)
+algo["layernorm_bwd 2048x1600"] = 3 * xx.numel() * 2
 h = torch.randn(M, 4 * Cm, device=dev).bfloat16(); hh = torch.empty_like(h)
 native.gelu_fwd(h, hh); algo["gelu_fwd"] = 2 * h.numel() * 2
 native.gelu_bwd(h, hh, hh); algo["gelu_bwd"] = 3 * h.numel() * 2

@@ -21,17 +21,27 @@ enum { LN1_W, LN1_B, ATTN_W, ATTN_B, PROJ_W, PROJ_B, LN2_W, LN2_B, FC_W, FC_B, P
 // activations a block keeps for its backward (bf16 unless noted)
 enum { A_LN1, A_QKV, A_ATT, A_X1, A_LN2, A_FCPRE, A_FCACT, kNumActs };
 
+// fp32 -> bf16 for up to 8 small vectors in one launch (bias and LayerNorm gradients of a block: eight tiny cast launches
+// per block and direction before)
+struct CastTable { const float* src[8]; bf16* dst[8]; int n[8]; int count; };
+__global__ void cast_multi_kernel(const CastTable t) {
+  const int seg = blockIdx.y;
+  if (seg >= t.count) return;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < t.n[seg]; i += gridDim.x * blockDim.x)
+    t.dst[seg][i] = __float2bfloat16(t.src[seg][i]);
+}
+
 // y[M,N] = act(x[M,K] W[N,K]^T + b)
 int linear_fwd(const void* x, const void* W, const void* b, void* y, int M, int N, int K, int act, void* stream) {
   return ddpx_gemm_bias(x, W, y, M, N, K, K, K, N, 0, 0, 1, 1, b, 1, act, 1, 0, stream);
 }
 
-// Backward of y = x W^T + b for bf16 tensors: dx[M,K] = d W (skipped when dx is null), dW[N,K] = d^T x, db[N] = colsum(d).
+// Backward of y = x W^T + b for bf16 tensors: dx[M,K] = d W (skipped when dx is null), dW[N,K] = d^T x, db32[N] = colsum(d) in fp32.
 // ws32: fp32 scratch of at least N*K elements that accumulates a split-K dW and must be ALL ZERO on entry (the GEMM's
 // in-kernel fix-up converts the finished sums to bf16 and leaves it zero again - no memset, no cast launch); db32: N floats
 // for the bias sums, OUTSIDE that zero-invariant area (layers of different sizes share ws32 from offset 0);
 // cnt: the fix-up's arrival counters (all zero on entry and on exit).
-int linear_bwd(const void* d, const void* x, const void* W, void* dx, void* dW, void* db, float* ws32, float* db32,
+int linear_bwd(const void* d, const void* x, const void* W, void* dx, void* dW, float* ws32, float* db32,
                unsigned int* cnt, int M, int N, int K, void* stream) {
   if (dx != nullptr) CHECK(ddpx_gemm(d, W, dx, M, K, N, N, K, K, 0, 1, 1, 1, nullptr, 0, 1, 0, stream));     // d[M,N] @ W[N,K]
   // A weight gradient has few output tiles and a long reduction (the tokens): when 256x256 tiles cannot fill the 74 CTA
@@ -48,8 +58,7 @@ int linear_bwd(const void* d, const void* x, const void* W, void* dx, void* dW, 
   } else {
     CHECK(ddpx_gemm(d, x, dW, N, K, M, N, K, K, 1, 1, 1, 1, nullptr, 0, 1, 0, stream));
   }
-  CHECK(ddpx_colsum_bf16(d, db32, M, N, stream));
-  return ddpx_cast_scale(db32, db, N, 1.f, 0, stream);
+  return ddpx_colsum_bf16(d, db32, M, N, stream);       // fp32 sums; the block casts all its small gradients at the end
 }
 }  // namespace
 
@@ -80,7 +89,7 @@ extern "C" int ddpx_gpt2_block_fwd(const void* x, void* const* params, void* con
 
 // Backward of ddpx_gpt2_block_fwd.  dout [M,C] is the gradient of the block output; x, acts, stats are the forward's.
 // grads[12] receive the parameter gradients (bf16, same order as params), dx [M,C] the input gradient.
-// wsb: bf16 scratch [M, 9C];  ws32: fp32 scratch [4C*C + 6C + B*H*Tp] whose first 4C*C elements must be all zero on entry
+// wsb: bf16 scratch [M, 9C];  ws32: fp32 scratch [4C*C + 13C + B*H*Tp] whose first 4C*C elements must be all zero on entry
 // (they are left all zero);  cnt: uint32 [16 * (4C*C/8192 + 64)] arrival counters, all zero on entry and on exit.
 extern "C" int ddpx_gpt2_block_bwd(const void* x, const void* dout, void* const* params, void* const* acts, const float* stats,
                                    void* const* grads, void* dx, void* wsb, float* ws32, unsigned int* cnt, int B, int T,
@@ -96,26 +105,33 @@ extern "C" int ddpx_gpt2_block_bwd(const void* x, const void* dout, void* const*
   bf16* d_a = d_fc + 4 * MC;                            // [M,C]
   bf16* d_b = d_a + MC;                                 // [M,C]
   bf16* dqkv = d_b + MC;                                // [M,3C]
-  float* db32 = ws32 + static_cast<size_t>(4) * C * C;               // [4C] bias sums (behind the zero-invariant dW area)
-  float* lnacc = db32 + 4 * C;                                       // [2C] LayerNorm dgamma / dbeta accumulators
-  float* delta = lnacc + 2 * C;                         // attention backward scratch [B*H*Tp]
+  // small fp32 results behind the zero-invariant dW area: bias sums of the four linears, then the LayerNorm accumulators
+  float* small32 = ws32 + static_cast<size_t>(4) * C * C;
+  float* b_proj2 = small32, *b_fc = small32 + C, *b_proj = small32 + 5 * C, *b_attn = small32 + 6 * C;
+  float* ln2acc = small32 + 9 * C;                                   // [2C] dgamma, dbeta of LayerNorm 2
+  float* ln1acc = small32 + 11 * C;                                  // [2C] of LayerNorm 1
+  float* delta = small32 + 13 * C;                                   // attention backward scratch [B*H*Tp]
+  if (cudaMemsetAsync(ln2acc, 0, sizeof(float) * 4 * C, s) != cudaSuccess) return DDPX_ERR_LAUNCH;
 
   // ---- MLP: out = x1 + proj2(gelu(fc(LN2(x1))))
-  CHECK(linear_bwd(dout, acts[A_FCACT], params[PROJ2_W], d_fc, grads[PROJ2_W], grads[PROJ2_B], ws32, db32, cnt, M, C, 4 * C, stream));
+  CHECK(linear_bwd(dout, acts[A_FCACT], params[PROJ2_W], d_fc, grads[PROJ2_W], ws32, b_proj2, cnt, M, C, 4 * C, stream));
   CHECK(ddpx_gelu_bwd(acts[A_FCPRE], d_fc, d_fc, 4 * MC, 1, stream));
-  CHECK(linear_bwd(d_fc, acts[A_LN2], params[FC_W], d_a, grads[FC_W], grads[FC_B], ws32, db32, cnt, M, 4 * C, C, stream));
-  if (cudaMemsetAsync(lnacc, 0, sizeof(float) * 2 * C, s) != cudaSuccess) return DDPX_ERR_LAUNCH;
-  CHECK(ddpx_layernorm_bwd(acts[A_X1], d_a, params[LN2_W], ln2_mean, ln2_rstd, d_b, lnacc, lnacc + C, M, C, 1, stream));
-  CHECK(ddpx_cast_scale(lnacc, grads[LN2_W], C, 1.f, 0, stream));
-  CHECK(ddpx_cast_scale(lnacc + C, grads[LN2_B], C, 1.f, 0, stream));
+  CHECK(linear_bwd(d_fc, acts[A_LN2], params[FC_W], d_a, grads[FC_W], ws32, b_fc, cnt, M, 4 * C, C, stream));
+  CHECK(ddpx_layernorm_bwd(acts[A_X1], d_a, params[LN2_W], ln2_mean, ln2_rstd, d_b, ln2acc, ln2acc + C, M, C, 1, stream));
   CHECK(ddpx_add(d_b, dout, d_b, MC, 1, stream));                       // d_x1 = through LN2 + the residual branch
   // ---- attention: x1 = x + proj(attention(qkv(LN1(x))))
-  CHECK(linear_bwd(d_b, acts[A_ATT], params[PROJ_W], d_a, grads[PROJ_W], grads[PROJ_B], ws32, db32, cnt, M, C, C, stream));
+  CHECK(linear_bwd(d_b, acts[A_ATT], params[PROJ_W], d_a, grads[PROJ_W], ws32, b_proj, cnt, M, C, C, stream));
   CHECK(ddpx_attn_bwd(acts[A_QKV], acts[A_ATT], d_a, lse2, delta, dqkv, B, T, H, 0.125f, stream));
-  CHECK(linear_bwd(dqkv, acts[A_LN1], params[ATTN_W], d_a, grads[ATTN_W], grads[ATTN_B], ws32, db32, cnt, M, 3 * C, C, stream));
-  if (cudaMemsetAsync(lnacc, 0, sizeof(float) * 2 * C, s) != cudaSuccess) return DDPX_ERR_LAUNCH;
-  CHECK(ddpx_layernorm_bwd(x, d_a, params[LN1_W], ln1_mean, ln1_rstd, dx, lnacc, lnacc + C, M, C, 1, stream));
-  CHECK(ddpx_cast_scale(lnacc, grads[LN1_W], C, 1.f, 0, stream));
-  CHECK(ddpx_cast_scale(lnacc + C, grads[LN1_B], C, 1.f, 0, stream));
+  CHECK(linear_bwd(dqkv, acts[A_LN1], params[ATTN_W], d_a, grads[ATTN_W], ws32, b_attn, cnt, M, 3 * C, C, stream));
+  CHECK(ddpx_layernorm_bwd(x, d_a, params[LN1_W], ln1_mean, ln1_rstd, dx, ln1acc, ln1acc + C, M, C, 1, stream));
+  // ---- every small gradient fp32 -> bf16 in one launch
+  CastTable t;
+  const float* srcs[8] = {b_proj2, b_fc, b_proj, b_attn, ln2acc, ln2acc + C, ln1acc, ln1acc + C};
+  const int dsts[8] = {PROJ2_B, FC_B, PROJ_B, ATTN_B, LN2_W, LN2_B, LN1_W, LN1_B};
+  const int lens[8] = {C, 4 * C, C, 3 * C, C, C, C, C};
+  for (int i = 0; i < 8; ++i) { t.src[i] = srcs[i]; t.dst[i] = static_cast<bf16*>(grads[dsts[i]]); t.n[i] = lens[i]; }
+  t.count = 8;
+  cast_multi_kernel<<<dim3((4 * C + 255) / 256, 8), 256, 0, s>>>(t);
+  if (cudaGetLastError() != cudaSuccess) return DDPX_ERR_LAUNCH;
   return ddpx_add(dx, d_b, dx, MC, 1, stream);
 }

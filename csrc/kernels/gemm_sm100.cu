@@ -368,14 +368,16 @@ tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
         if constexpr (kMode == MODE_GEMM) {
           if (row < p.M) {
             if (p.fix_ws != nullptr) {
-              // host guarantees N % 32 == 0 and no batching: whole 128-byte row segments, eight vector reductions
+              // host guarantees N % 32 == 0 and no batching: a chunk is either whole or entirely past the last column
               float* o = p.fix_ws + static_cast<long long>(row) * p.N + n0 + c0;
+              if (n0 + c0 < p.N) {
 #pragma unroll
-              for (int j = 0; j < 32; j += 4)
-                asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(o + j), "f"(__uint_as_float(v[j]) * p.alpha),
-                             "f"(__uint_as_float(v[j + 1]) * p.alpha), "f"(__uint_as_float(v[j + 2]) * p.alpha),
-                             "f"(__uint_as_float(v[j + 3]) * p.alpha)
-                             : "memory");
+                for (int j = 0; j < 32; j += 4)
+                  asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(o + j), "f"(__uint_as_float(v[j]) * p.alpha),
+                               "f"(__uint_as_float(v[j + 1]) * p.alpha), "f"(__uint_as_float(v[j + 2]) * p.alpha),
+                               "f"(__uint_as_float(v[j + 3]) * p.alpha)
+                               : "memory");
+              }
             } else if (p.atomic) {
               float* o = reinterpret_cast<float*>(p.out) + boff + static_cast<long long>(row) * p.ldo + n0 + c0;
 #pragma unroll
@@ -522,7 +524,7 @@ tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
           if (old == static_cast<unsigned int>(p.num_splits - 1)) {
             __threadfence();
             if (row < p.M) {
-              for (int cc = cc_begin; cc < cc_end; cc += 32) {
+              for (int cc = cc_begin; cc < cc_end && n0 + cc < p.N; cc += 32) {
                 float* w = p.fix_ws + static_cast<long long>(row) * p.N + n0 + cc;
                 __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(p.out) + static_cast<long long>(row) * p.ldo + n0 + cc;
                 float4 q[8];
@@ -736,6 +738,24 @@ static int gemm_impl(const void* A, const void* B, void* D, int M, int N, int K,
   const int want_splits = split_k > 1 ? split_k : 1;      // split-K multiplies the number of work items
   while (bn > 64 && static_cast<long long>(mb) * ((N + bn - 1) / bn) * nb_total * want_splits < num_sms()) bn /= 2;
   while (bn > min_bn && bn / 2 >= N) bn /= 2;
+  // Compute-bound bf16 problems (>= 1024 rows, long K) that the rule above would cut into 128- or 64-column tiles to get a
+  // tile per SM: an SS-mode MMA costs ~118 cycles whatever its N (profiles/probe_findings.md section 1), so a 128-column
+  // tile runs the tensor pipe at half rate.  Compare modelled times (waves x k-steps x MMA cost + epilogue per item) of the
+  // narrow choice and of 256-column tiles and keep the cheaper: GPT-2 XL's 2048 x 1600 outputs went from 208 tiles of
+  // 128 x 128 (two waves at half rate) to 56 CTA-pair tiles of 256 x 256 (one wave at full rate).
+  if (bf16 && bn < 256 && N >= 256 && M >= 1024 && K >= 512 && nb_total == 1 && causal == 0 && min_bn <= 256) {
+    auto model = [&](int tile_m, int tile_n, int units) {
+      const long long items = static_cast<long long>((M + tile_m - 1) / tile_m) * ((N + tile_n - 1) / tile_n) * want_splits;
+      const long long waves = (items + units - 1) / units;
+      const long long ksteps = ((K + bk - 1) / bk + want_splits - 1) / want_splits;
+      const long long mma = 4LL * (tile_n / 2 > 118 ? tile_n / 2 : 118);      // 4 MMAs per 64-element k-step
+      return waves * (ksteps * mma + 1500);
+    };
+    const long long narrow = model(kBlockM, bn, num_sms());
+    const long long wide1 = model(kBlockM, 256, num_sms());
+    const long long wide2 = pairs_enabled() && M >= 256 ? model(256, 256, num_sms() / 2) : (1LL << 62);
+    if (wide1 < narrow || wide2 < narrow) bn = 256;
+  }
   if (causal == 1 && bn > kBlockM) bn = kBlockM;      // square tiles so whole tiles fall above the diagonal
   if (bn < min_bn) bn = min_bn;
   // CTA pairs (256-row tiles) whenever the problem is tall and wide enough for 256x256 tiles to fill the machine

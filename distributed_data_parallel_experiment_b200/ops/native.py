@@ -423,7 +423,7 @@ def gpt2_block_fwd(x, params, acts, stats, tmp, out, B, T, C, H, eps):
 def gpt2_block_bwd(x, dout, params, acts, stats, grads, dx, wsb, ws32, cnt, B, T, C, H):
     _call("ddpx_gpt2_block_bwd", _P(x), _P(dout), (c_void_p * 12)(*params), (c_void_p * 7)(*acts), _P(stats),
           (c_void_p * 12)(*grads), _P(dx), _P(wsb), _P(ws32), _P(cnt), c_int(B), c_int(T), c_int(C), c_int(H), _st(),
-          launches=30)
+          launches=24)
 
 
 def gemm_splitk_bf16(A, B, D, M, N, K, lda, ldb, ldd, a_mn, b_mn, split_k, ws, cnt):

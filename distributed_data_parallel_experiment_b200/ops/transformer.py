@@ -202,7 +202,7 @@ def _block_workspace(dev, M, C, lse_elems):
         # the fp32 scratch starts with the split-K accumulation area and comes with arrival counters: both must be zero
         # before the first use and are left zero by the kernels that use them
         ws = (torch.empty(M * 9 * C, device=dev, dtype=torch.bfloat16),
-              native.zero_(torch.empty(4 * C * C + 6 * C + lse_elems, device=dev, dtype=torch.float32)),
+              native.zero_(torch.empty(4 * C * C + 13 * C + lse_elems, device=dev, dtype=torch.float32)),
               native.zero_(torch.empty(16 * (4 * C * C // 8192 + 64), device=dev, dtype=torch.int32)))
         _BLOCK_WS[key] = ws
     return ws

@@ -159,7 +159,7 @@ int ddpx_conv_bn_bwd(const float* y, const float* dout, const float* xin, const 
  * ln_1.{weight,bias}, attn.c_attn.{weight,bias}, attn.c_proj.{weight,bias}, ln_2.{weight,bias}, mlp.c_fc.{weight,bias},
  * mlp.c_proj.{weight,bias}; acts[7] = LN1 out, qkv, attention out, x1, LN2 out, fc pre-activation, fc activation (kept
  * for the backward); stats = fp32 [4*B*T + B*H*Tp]; tmp = bf16 [B*T, C]; backward scratch: wsb = bf16 [B*T, 9C],
- * ws32 = fp32 [4C*C + 6C + B*H*Tp] (first 4C*C all zero on entry, left all zero), cnt = uint32 [16*(4C*C/8192 + 64)] all
+ * ws32 = fp32 [4C*C + 13C + B*H*Tp] (first 4C*C all zero on entry, left all zero), cnt = uint32 [16*(4C*C/8192 + 64)] all
  * zero on entry and exit.  Nothing is allocated.  No counterpart in the reference (a CNN). */
 int ddpx_gpt2_block_fwd(const void* x, void* const* params, void* const* acts, float* stats, void* tmp, void* out, int B,
                         int T, int C, int H, float eps, void* stream);
