@@ -34,6 +34,30 @@ if which == "linear":      # small-K Linear shape of GPT-2 (epilogue-paced)
     yy = torch.empty(8192, 3072, device="cuda", dtype=torch.bfloat16); bb = torch.zeros(3072, device="cuda")
     for _ in range(3):
         native.gemm(xx, ww, yy, 8192, 3072, 768, 768, 768, 3072, 0, 0, bb, 0)
+if which == "xl":          # GPT-2 XL block shapes (2048 tokens, C = 1600): forward, data gradient, weight gradient
+    M, C = 2048, 1600
+    xa = torch.randn(M, C, device="cuda").bfloat16(); x4 = torch.randn(M, 4 * C, device="cuda").bfloat16()
+    wfc = torch.randn(4 * C, C, device="cuda").bfloat16(); wpr = torch.randn(C, C, device="cuda").bfloat16()
+    y4 = torch.empty(M, 4 * C, device="cuda", dtype=torch.bfloat16); y1 = torch.empty(M, C, device="cuda", dtype=torch.bfloat16)
+    dwf = torch.empty(4 * C, C, device="cuda", dtype=torch.bfloat16)
+    cases = {
+        "fc fwd    [2048x6400x1600] K,K": lambda: native.gemm(xa, wfc, y4, M, 4 * C, C, C, C, 4 * C, 0, 0),
+        "proj fwd  [2048x1600x1600] K,K": lambda: native.gemm(xa, wpr, y1, M, C, C, C, C, C, 0, 0),
+        "fc dgrad  [2048x1600x6400] K,MN": lambda: native.gemm(x4, wfc, y1, M, C, 4 * C, 4 * C, C, C, 0, 1),
+        "fc wgrad  [6400x1600x2048] MN,MN": lambda: native.gemm(x4, xa, dwf, 4 * C, C, M, 4 * C, C, C, 1, 1),
+    }
+    timing = os.environ.get("NCU_TIMING", "0") == "1"
+    for name, fn in cases.items():
+        fn()
+        if timing:
+            for _ in range(5): fn()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            torch.cuda.synchronize(); e0.record()
+            for _ in range(20): fn()
+            e1.record(); torch.cuda.synchronize()
+            us = e0.elapsed_time(e1) * 50.0
+            flops = 2.0 * 2048 * 1600 * (6400 if "6400" in name else 1600)
+            print(f"{name:36s} {us:7.1f} us  {flops / us * 1e-6:7.1f} TFLOP/s")
 torch.cuda.synchronize()
 assert native.read_error_word() == 0
 print("ok")

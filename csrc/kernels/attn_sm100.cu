@@ -136,20 +136,38 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const AttnParams p) {
       mbar_wait(s_full, j & 1, 0x560u);
       tc_fence_after();
       const bool diag = (j == qt);                      // only the last block crosses the diagonal
-      float mx = -INFINITY;
-#pragma unroll 1
+      // Both passes over the 128 scores are software-pipelined: the tcgen05.ld of chunk c+1 is in flight while chunk c
+      // is processed (ncu: with one load + wait per chunk the softmax warps spent more time on the TMEM round trips than
+      // on arithmetic).  Maxima and sums run as independent chains.
+      uint32_t va[32], vb[32];
+      float mx0 = -INFINITY, mx1 = -INFINITY, mx2 = -INFINITY, mx3 = -INFINITY;
+      tmem_ld_32x32(tS, va);
+#pragma unroll
       for (int c = 0; c < 4; ++c) {
-        uint32_t v[32];
-        tmem_ld_32x32(tS + c * 32, v);
+        uint32_t (&v)[32] = (c & 1) ? vb : va;
         tmem_ld_wait();
+        if (c < 3) tmem_ld_32x32(tS + (c + 1) * 32, (c & 1) ? va : vb);
         if (diag) {
 #pragma unroll
-          for (int i = 0; i < 32; ++i) if (c * 32 + i <= r) mx = fmaxf(mx, __uint_as_float(v[i]));
+          for (int i = 0; i < 32; i += 4) {
+            if (c * 32 + i <= r) mx0 = fmaxf(mx0, __uint_as_float(v[i]));
+            if (c * 32 + i + 1 <= r) mx1 = fmaxf(mx1, __uint_as_float(v[i + 1]));
+            if (c * 32 + i + 2 <= r) mx2 = fmaxf(mx2, __uint_as_float(v[i + 2]));
+            if (c * 32 + i + 3 <= r) mx3 = fmaxf(mx3, __uint_as_float(v[i + 3]));
+          }
         } else {
 #pragma unroll
-          for (int i = 0; i < 32; ++i) mx = fmaxf(mx, __uint_as_float(v[i]));
+          for (int i = 0; i < 32; i += 4) {
+            mx0 = fmaxf(mx0, __uint_as_float(v[i]));
+            mx1 = fmaxf(mx1, __uint_as_float(v[i + 1]));
+            mx2 = fmaxf(mx2, __uint_as_float(v[i + 2]));
+            mx3 = fmaxf(mx3, __uint_as_float(v[i + 3]));
+          }
         }
       }
+      // the second pass starts with chunk 0 again: issue its load before the bookkeeping
+      tmem_ld_32x32(tS, va);
+      const float mx = fmaxf(fmaxf(mx0, mx1), fmaxf(mx2, mx3));
       const float m_new = fmaxf(m, mx);
       if (j > 0) {
         // the previous blocks were accumulated relative to the old maximum: rescale the sum and (only if some row of
@@ -157,24 +175,27 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const AttnParams p) {
         const float alpha = ex2((m - m_new) * sl2);
         l *= alpha;
         if (__any_sync(0xffffffffu, m_new > m)) {
-#pragma unroll 1
-          for (int c = 0; c < 2; ++c) {
-            uint32_t o[32];
-            tmem_ld_32x32(tO + c * 32, o);
-            tmem_ld_wait();
+          uint32_t o[32];
+          tmem_ld_wait();                       // chunk 0 of the scores (in va) and nothing else is outstanding
+          tmem_ld_32x32(tO, o);
+          tmem_ld_32x32(tO + 32, vb);
+          tmem_ld_wait();
 #pragma unroll
-            for (int i = 0; i < 32; ++i) o[i] = __float_as_uint(__uint_as_float(o[i]) * alpha);
-            tmem_st_32x32(tO + c * 32, o);
-          }
+          for (int i = 0; i < 32; ++i) o[i] = __float_as_uint(__uint_as_float(o[i]) * alpha);
+          tmem_st_32x32(tO, o);
+#pragma unroll
+          for (int i = 0; i < 32; ++i) vb[i] = __float_as_uint(__uint_as_float(vb[i]) * alpha);
+          tmem_st_32x32(tO + 32, vb);
         }
       }
       m = m_new;
       const float moff = m * sl2;
-#pragma unroll 1
+      float l0 = 0.f, l1 = 0.f;
+#pragma unroll
       for (int c = 0; c < 4; ++c) {
-        uint32_t v[32];
-        tmem_ld_32x32(tS + c * 32, v);
+        uint32_t (&v)[32] = (c & 1) ? vb : va;
         tmem_ld_wait();
+        if (c < 3) tmem_ld_32x32(tS + (c + 1) * 32, (c & 1) ? va : vb);
         uint32_t pk[16];
 #pragma unroll
         for (int i = 0; i < 32; i += 2) {
@@ -184,11 +205,12 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const AttnParams p) {
             if (c * 32 + i > r) p0 = 0.f;
             if (c * 32 + i + 1 > r) p1 = 0.f;
           }
-          l += p0 + p1;
+          l0 += p0; l1 += p1;
           pk[i >> 1] = pack_bf16(p0, p1);
         }
         tmem_st_32x16(tP + c * 16, pk);
       }
+      l += l0 + l1;
       tmem_st_wait();
       tc_fence_before();
       __syncwarp();

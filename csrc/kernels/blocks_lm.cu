@@ -89,7 +89,7 @@ extern "C" int ddpx_gpt2_block_fwd(const void* x, void* const* params, void* con
 
 // Backward of ddpx_gpt2_block_fwd.  dout [M,C] is the gradient of the block output; x, acts, stats are the forward's.
 // grads[12] receive the parameter gradients (bf16, same order as params), dx [M,C] the input gradient.
-// wsb: bf16 scratch [M, 9C];  ws32: fp32 scratch [4C*C + 13C + B*H*Tp] whose first 4C*C elements must be all zero on entry
+// wsb: bf16 scratch [M, 9C];  ws32: fp32 scratch [4C*C + 13C + B*H*Tp + ddpx_layernorm_bwd_scratch_floats(M, C)] whose first 4C*C elements must be all zero on entry
 // (they are left all zero);  cnt: uint32 [16 * (4C*C/8192 + 64)] arrival counters, all zero on entry and on exit.
 extern "C" int ddpx_gpt2_block_bwd(const void* x, const void* dout, void* const* params, void* const* acts, const float* stats,
                                    void* const* grads, void* dx, void* wsb, float* ws32, unsigned int* cnt, int B, int T,
@@ -111,19 +111,22 @@ extern "C" int ddpx_gpt2_block_bwd(const void* x, const void* dout, void* const*
   float* ln2acc = small32 + 9 * C;                                   // [2C] dgamma, dbeta of LayerNorm 2
   float* ln1acc = small32 + 11 * C;                                  // [2C] of LayerNorm 1
   float* delta = small32 + 13 * C;                                   // attention backward scratch [B*H*Tp]
-  if (cudaMemsetAsync(ln2acc, 0, sizeof(float) * 4 * C, s) != cudaSuccess) return DDPX_ERR_LAUNCH;
+  // per-block partial sums of the LayerNorm backward ([<= 296][2C], behind delta; lse_pad = B*H*Tp)
+  const int Tp = (T + 127) / 128 * 128;
+  float* ln_scratch = delta + static_cast<size_t>(B) * H * Tp;
 
   // ---- MLP: out = x1 + proj2(gelu(fc(LN2(x1))))
   CHECK(linear_bwd(dout, acts[A_FCACT], params[PROJ2_W], d_fc, grads[PROJ2_W], ws32, b_proj2, cnt, M, C, 4 * C, stream));
   CHECK(ddpx_gelu_bwd(acts[A_FCPRE], d_fc, d_fc, 4 * MC, 1, stream));
   CHECK(linear_bwd(d_fc, acts[A_LN2], params[FC_W], d_a, grads[FC_W], ws32, b_fc, cnt, M, 4 * C, C, stream));
-  CHECK(ddpx_layernorm_bwd(acts[A_X1], d_a, params[LN2_W], ln2_mean, ln2_rstd, d_b, ln2acc, ln2acc + C, M, C, 1, stream));
+  CHECK(ddpx_layernorm_bwd_ws(acts[A_X1], d_a, params[LN2_W], ln2_mean, ln2_rstd, d_b, ln2acc, ln2acc + C, M, C, 1, ln_scratch,
+                              stream));
   CHECK(ddpx_add(d_b, dout, d_b, MC, 1, stream));                       // d_x1 = through LN2 + the residual branch
   // ---- attention: x1 = x + proj(attention(qkv(LN1(x))))
   CHECK(linear_bwd(d_b, acts[A_ATT], params[PROJ_W], d_a, grads[PROJ_W], ws32, b_proj, cnt, M, C, C, stream));
   CHECK(ddpx_attn_bwd(acts[A_QKV], acts[A_ATT], d_a, lse2, delta, dqkv, B, T, H, 0.125f, stream));
   CHECK(linear_bwd(dqkv, acts[A_LN1], params[ATTN_W], d_a, grads[ATTN_W], ws32, b_attn, cnt, M, 3 * C, C, stream));
-  CHECK(ddpx_layernorm_bwd(x, d_a, params[LN1_W], ln1_mean, ln1_rstd, dx, ln1acc, ln1acc + C, M, C, 1, stream));
+  CHECK(ddpx_layernorm_bwd_ws(x, d_a, params[LN1_W], ln1_mean, ln1_rstd, dx, ln1acc, ln1acc + C, M, C, 1, ln_scratch, stream));
   // ---- every small gradient fp32 -> bf16 in one launch
   CastTable t;
   const float* srcs[8] = {b_proj2, b_fc, b_proj, b_attn, ln2acc, ln2acc + C, ln1acc, ln1acc + C};

@@ -60,21 +60,21 @@ layernorm_fwd_kernel(const T* __restrict__ x, const T* __restrict__ gamma, const
 // the rows its warp visits (NV vectors per lane), then the block folds them through shared memory and issues one
 // atomic per column into the fp32 accumulators (pre-zeroed).
 template <typename T, int NV>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, (NV <= 4 ? 2 : 1))
 layernorm_bwd_kernel(const T* __restrict__ x, const T* __restrict__ dy, const T* __restrict__ gamma,
                      const float* __restrict__ mean, const float* __restrict__ rstd, T* __restrict__ dx,
-                     float* __restrict__ dgamma, float* __restrict__ dbeta, long long rows, int C) {
+                     float* __restrict__ dgamma, float* __restrict__ dbeta, long long rows, int C,
+                     float* __restrict__ partial) {
   constexpr int V = VecOf<T>::N;
-  // rows up to 4 vectors per lane (C <= 1024 in bf16) stay in registers between the two passes over a row; wider rows
-  // are read again (from L1 / L2) for the second pass
-  constexpr bool kKeep = NV <= 4;
+  // rows up to 2 vectors per lane (C <= 512 in bf16) stay in registers between the two passes over a row; wider rows
+  // are read again (from L1) for the second pass - registers go to the column sums instead, so that two blocks fit on
+  // an SM up to NV = 4 (the kernel is latency-bound: ncu showed 12 % occupancy and 24 us for 38 MB with one block)
+  constexpr bool kKeep = NV <= 2;
   extern __shared__ float acc[];   // [2][C]
   const int lane = threadIdx.x & 31;
   const long long warp0 = (static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
   const long long nwarps = (static_cast<long long>(gridDim.x) * blockDim.x) >> 5;
   const int nvec = C / V;
-  for (int c = threadIdx.x; c < 2 * C; c += blockDim.x) acc[c] = 0.f;
-  __syncthreads();
   float ag[NV][V], ab[NV][V];
 #pragma unroll
   for (int j = 0; j < NV; ++j)
@@ -127,24 +127,69 @@ layernorm_bwd_kernel(const T* __restrict__ x, const T* __restrict__ dy, const T*
       }
     }
   }
+  // fold the warps' register sums into acc one warp at a time (plain vector read-modify-write: shared-memory float
+  // atomics compile to compare-and-swap spin loops, and 2 * NV * V of them per lane with eight warps on the same
+  // addresses cost more than the rest of the kernel)
+  const int nw = blockDim.x >> 5, wid = threadIdx.x >> 5;
+  for (int w = 0; w < nw; ++w) {
+    if (wid == w) {
 #pragma unroll
-  for (int j = 0; j < NV; ++j) {
-    const int i = lane + j * 32;
-    if (i < nvec) {
+      for (int j = 0; j < NV; ++j) {
+        const int i = lane + j * 32;
+        if (i < nvec) {
 #pragma unroll
-      for (int k = 0; k < V; ++k) {
-        atomicAdd(&acc[i * V + k], ag[j][k]);
-        atomicAdd(&acc[C + i * V + k], ab[j][k]);
+          for (int k = 0; k < V; k += 4) {
+            float4* pg = reinterpret_cast<float4*>(&acc[i * V + k]);
+            float4* pb = reinterpret_cast<float4*>(&acc[C + i * V + k]);
+            float4 g4 = make_float4(ag[j][k], ag[j][k + 1], ag[j][k + 2], ag[j][k + 3]);
+            float4 b4 = make_float4(ab[j][k], ab[j][k + 1], ab[j][k + 2], ab[j][k + 3]);
+            if (w > 0) {
+              const float4 og = *pg, ob = *pb;
+              g4.x += og.x; g4.y += og.y; g4.z += og.z; g4.w += og.w;
+              b4.x += ob.x; b4.y += ob.y; b4.z += ob.z; b4.w += ob.w;
+            }
+            *pg = g4; *pb = b4;
+          }
+        }
       }
     }
+    __syncthreads();
   }
-  __syncthreads();
+  if (partial != nullptr) {
+    // the block's sums go to its own row of the scratch matrix [grid][2C] with plain stores; ln_partial_reduce_kernel adds
+    // the rows up.  (Reductions from every block onto the same C addresses cost ~30 us per call, whatever the tensor size.)
+    float* row = partial + static_cast<size_t>(blockIdx.x) * 2 * C;
+    for (int c = threadIdx.x * 4; c < 2 * C; c += blockDim.x * 4)
+      *reinterpret_cast<float4*>(row + c) = make_float4(acc[c], acc[c + 1], acc[c + 2], acc[c + 3]);
+    return;
+  }
   // one 16-byte vector reduction per four columns (C % 4 == 0; dgamma / dbeta are 16-byte aligned: checked on the host)
   for (int c = threadIdx.x * 4; c < C; c += blockDim.x * 4) {
     asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(dgamma + c), "f"(acc[c]), "f"(acc[c + 1]), "f"(acc[c + 2]),
                  "f"(acc[c + 3]) : "memory");
     asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(dbeta + c), "f"(acc[C + c]), "f"(acc[C + c + 1]),
                  "f"(acc[C + c + 2]), "f"(acc[C + c + 3]) : "memory");
+  }
+}
+
+// out[c] = sum over the nrows rows of partial[nrows][n2] (n2 = 2C: dgamma | dbeta).  Block = 32 columns x 8 row groups:
+// a thread's loads are independent (a single thread walking all rows pays an L2 round trip per few loads).
+__global__ void __launch_bounds__(256) ln_partial_reduce_kernel(const float* __restrict__ partial, int nrows, int n2, int C,
+                                                               float* __restrict__ dgamma, float* __restrict__ dbeta) {
+  __shared__ float red[8][33];
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  const int c = blockIdx.x * 32 + tx;
+  float s = 0.f;
+  if (c < n2) {
+#pragma unroll 8
+    for (int r = ty; r < nrows; r += 8) s += __ldcg(partial + static_cast<size_t>(r) * n2 + c);
+  }
+  red[ty][tx] = s;
+  __syncthreads();
+  if (ty == 0 && c < n2) {
+#pragma unroll
+    for (int j = 1; j < 8; ++j) s += red[j][tx];
+    if (c < C) dgamma[c] = s; else dbeta[c - C] = s;
   }
 }
 
@@ -260,8 +305,8 @@ __global__ void dropout_kernel(const T* __restrict__ x, T* __restrict__ y, long 
 
 template <typename T>
 int launch_ln_bwd(int nv, int grid, size_t smem, cudaStream_t s, const T* x, const T* dy, const T* g, const float* mean,
-                  const float* rstd, T* dx, float* dgamma, float* dbeta, long long rows, int C) {
-#define LN_CASE(NVV) case NVV: layernorm_bwd_kernel<T, NVV><<<grid, 256, smem, s>>>(x, dy, g, mean, rstd, dx, dgamma, dbeta, rows, C); break;
+                  const float* rstd, T* dx, float* dgamma, float* dbeta, long long rows, int C, float* partial) {
+#define LN_CASE(NVV) case NVV: layernorm_bwd_kernel<T, NVV><<<grid, 256, smem, s>>>(x, dy, g, mean, rstd, dx, dgamma, dbeta, rows, C, partial); break;
   switch (nv) {
     LN_CASE(1) LN_CASE(2) LN_CASE(3) LN_CASE(4) LN_CASE(5) LN_CASE(6) LN_CASE(7) LN_CASE(8)
     LN_CASE(9) LN_CASE(10) LN_CASE(11) LN_CASE(12) LN_CASE(13) LN_CASE(14) LN_CASE(15) LN_CASE(16)
@@ -293,26 +338,46 @@ extern "C" int ddpx_layernorm_fwd(const void* x, const void* gamma, const void* 
   return LAUNCH_OK();
 }
 
-// dgamma / dbeta are fp32 [C] accumulators that must be zero on entry
-extern "C" int ddpx_layernorm_bwd(const void* x, const void* dy, const void* gamma, const float* mean, const float* rstd,
-                                  void* dx, float* dgamma, float* dbeta, long long rows, int C, int is_bf16, void* stream) {
+// dgamma / dbeta: fp32 [C].  Without scratch they are accumulators that must be zero on entry (every block reduces into
+// them); with `scratch` (fp32, at least ddpx_layernorm_bwd_scratch_floats(rows, C) elements) the blocks store partial sums
+// there, a second small kernel adds them up and OVERWRITES dgamma / dbeta - no zeroing needed and ~25 us less per call.
+static int ln_bwd_grid(long long rows, int nv) { return cap_blocks((rows + 7) / 8, nv <= 4 ? 296 : 148); }
+
+extern "C" long long ddpx_layernorm_bwd_scratch_floats(long long rows, int C) {
+  return static_cast<long long>(ln_bwd_grid(rows, 1)) * 2 * C;          // the larger of the two grids
+}
+
+extern "C" int ddpx_layernorm_bwd_ws(const void* x, const void* dy, const void* gamma, const float* mean, const float* rstd,
+                                     void* dx, float* dgamma, float* dbeta, long long rows, int C, int is_bf16, float* scratch,
+                                     void* stream) {
   const int V = is_bf16 ? 8 : 4;
   if (C % V) return DDPX_ERR_SHAPE;
   const int nv = (C / V + 31) / 32;
   const size_t smem = static_cast<size_t>(2) * C * sizeof(float);
   if (nv > 16 || smem > 48 * 1024) return DDPX_ERR_SHAPE;
-  if ((reinterpret_cast<uintptr_t>(dgamma) | reinterpret_cast<uintptr_t>(dbeta)) & 15) return DDPX_ERR_ALIGN;
-  // every warp carries register accumulators across its rows and every block ends with 2*C/4 vector reductions onto the
-  // same C addresses: the kernel took ~30 us whatever the tensor size (8192 x 768 and 2048 x 1600 alike) with 256-444
-  // blocks, so the per-address serialisation of those reductions is what one pays for - one block per SM keeps it short
-  const int grid = cap_blocks((rows + 7) / 8, 148);
+  if ((reinterpret_cast<uintptr_t>(dgamma) | reinterpret_cast<uintptr_t>(dbeta) | reinterpret_cast<uintptr_t>(scratch)) & 15)
+    return DDPX_ERR_ALIGN;
+  // every warp carries register accumulators across its rows; one or two blocks per SM
+  const int grid = ln_bwd_grid(rows, nv);
+  int rc;
   if (is_bf16)
-    return launch_ln_bwd<bf16>(nv, grid, smem, ST(stream), static_cast<const bf16*>(x), static_cast<const bf16*>(dy),
-                               static_cast<const bf16*>(gamma), mean, rstd, static_cast<bf16*>(dx), dgamma, dbeta, rows, C) ||
-           (cudaGetLastError() != cudaSuccess ? DDPX_ERR_LAUNCH : DDPX_OK);
-  return launch_ln_bwd<float>(nv, grid, smem, ST(stream), static_cast<const float*>(x), static_cast<const float*>(dy),
-                              static_cast<const float*>(gamma), mean, rstd, static_cast<float*>(dx), dgamma, dbeta, rows, C) ||
-         (cudaGetLastError() != cudaSuccess ? DDPX_ERR_LAUNCH : DDPX_OK);
+    rc = launch_ln_bwd<bf16>(nv, grid, smem, ST(stream), static_cast<const bf16*>(x), static_cast<const bf16*>(dy),
+                             static_cast<const bf16*>(gamma), mean, rstd, static_cast<bf16*>(dx), dgamma, dbeta, rows, C, scratch);
+  else
+    rc = launch_ln_bwd<float>(nv, grid, smem, ST(stream), static_cast<const float*>(x), static_cast<const float*>(dy),
+                              static_cast<const float*>(gamma), mean, rstd, static_cast<float*>(dx), dgamma, dbeta, rows, C, scratch);
+  if (rc != DDPX_OK) return rc;
+  if (cudaGetLastError() != cudaSuccess) return DDPX_ERR_LAUNCH;
+  if (scratch != nullptr) {
+    ln_partial_reduce_kernel<<<(2 * C + 31) / 32, 256, 0, ST(stream)>>>(scratch, grid, 2 * C, C, dgamma, dbeta);
+    if (cudaGetLastError() != cudaSuccess) return DDPX_ERR_LAUNCH;
+  }
+  return DDPX_OK;
+}
+
+extern "C" int ddpx_layernorm_bwd(const void* x, const void* dy, const void* gamma, const float* mean, const float* rstd,
+                                  void* dx, float* dgamma, float* dbeta, long long rows, int C, int is_bf16, void* stream) {
+  return ddpx_layernorm_bwd_ws(x, dy, gamma, mean, rstd, dx, dgamma, dbeta, rows, C, is_bf16, nullptr, stream);
 }
 
 template <int OP>

@@ -325,9 +325,21 @@ def layernorm_fwd(x, gamma, beta, y, mean, rstd, rows, C, eps):
           c_float(eps), c_int(_bf(x)), _st())
 
 
-def layernorm_bwd(x, dy, gamma, mean, rstd, dx, dgamma, dbeta, rows, C):
-    _call("ddpx_layernorm_bwd", _P(x), _P(dy), _P(gamma), _P(mean), _P(rstd), _P(dx), _P(dgamma), _P(dbeta),
-          c_longlong(rows), c_int(C), c_int(_bf(x)), _st())
+def layernorm_bwd_scratch_floats(rows, C) -> int:
+    """fp32 elements of per-block partial sums ddpx_layernorm_bwd_ws wants: [min(296, ceil(rows / 8))][2C] (the larger
+    grid of csrc/kernels/transformer.cu, restated so that sizing a buffer needs no library call)."""
+    return min(296, max(1, (rows + 7) // 8)) * 2 * C
+
+
+def layernorm_bwd(x, dy, gamma, mean, rstd, dx, dgamma, dbeta, rows, C, scratch=None):
+    """Without scratch dgamma / dbeta are zeroed accumulators; with it they are overwritten."""
+    if scratch is None:
+        _call("ddpx_layernorm_bwd", _P(x), _P(dy), _P(gamma), _P(mean), _P(rstd), _P(dx), _P(dgamma), _P(dbeta),
+              c_longlong(rows), c_int(C), c_int(_bf(x)), _st())
+    else:
+        assert scratch.numel() >= layernorm_bwd_scratch_floats(rows, C) and scratch.dtype == torch.float32
+        _call("ddpx_layernorm_bwd_ws", _P(x), _P(dy), _P(gamma), _P(mean), _P(rstd), _P(dx), _P(dgamma), _P(dbeta),
+              c_longlong(rows), c_int(C), c_int(_bf(x)), _P(scratch), _st())
 
 
 def gelu_fwd(x, y):

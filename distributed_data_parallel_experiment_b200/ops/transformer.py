@@ -47,8 +47,9 @@ class LayerNormFn(Function):
         if not d.is_contiguous():
             d = d.contiguous()
         dx = torch.empty_like(x2)
-        dgb = _zeros((2, C), x2.device)
-        native.layernorm_bwd(x2, d, weight.detach(), stats[0], stats[1], dx, dgb[0], dgb[1], rows, C)
+        dgb = torch.empty((2, C), device=x2.device, dtype=torch.float32)
+        scratch = torch.empty(native.layernorm_bwd_scratch_floats(rows, C), device=x2.device, dtype=torch.float32)
+        native.layernorm_bwd(x2, d, weight.detach(), stats[0], stats[1], dx, dgb[0], dgb[1], rows, C, scratch)
         return dx.view(ctx.shape), _to_dtype(dgb[0], weight.dtype), _to_dtype(dgb[1], weight.dtype), None
 
 
@@ -202,7 +203,8 @@ def _block_workspace(dev, M, C, lse_elems):
         # the fp32 scratch starts with the split-K accumulation area and comes with arrival counters: both must be zero
         # before the first use and are left zero by the kernels that use them
         ws = (torch.empty(M * 9 * C, device=dev, dtype=torch.bfloat16),
-              native.zero_(torch.empty(4 * C * C + 13 * C + lse_elems, device=dev, dtype=torch.float32)),
+              native.zero_(torch.empty(4 * C * C + 13 * C + lse_elems + native.layernorm_bwd_scratch_floats(M, C),
+                                       device=dev, dtype=torch.float32)),
               native.zero_(torch.empty(16 * (4 * C * C // 8192 + 64), device=dev, dtype=torch.int32)))
         _BLOCK_WS[key] = ws
     return ws

@@ -207,6 +207,11 @@ int ddpx_layernorm_fwd(const void* x, const void* gamma, const void* beta, void*
                        long long rows, int C, float eps, int is_bf16, void* stream);
 int ddpx_layernorm_bwd(const void* x, const void* dy, const void* gamma, const float* mean, const float* rstd, void* dx,
                        float* dgamma, float* dbeta, long long rows, int C, int is_bf16, void* stream);
+/* the same with caller-provided scratch (fp32, ddpx_layernorm_bwd_scratch_floats(rows, C) elements): blocks store partial sums
+ * there and a second small kernel adds them up and overwrites dgamma / dbeta (which then need not be zeroed) */
+int ddpx_layernorm_bwd_ws(const void* x, const void* dy, const void* gamma, const float* mean, const float* rstd, void* dx,
+                          float* dgamma, float* dbeta, long long rows, int C, int is_bf16, float* scratch, void* stream);
+long long ddpx_layernorm_bwd_scratch_floats(long long rows, int C);
 int ddpx_gelu_fwd(const void* x, void* y, long long n, int is_bf16, void* stream);
 int ddpx_gelu_bwd(const void* x, const void* dy, void* dx, long long n, int is_bf16, void* stream);
 int ddpx_relu_bwd_bf16(const void* y, const void* dy, void* dx, long long n, void* stream);
