@@ -9,6 +9,7 @@
 #include <cuda_runtime.h>
 #include <cuda_bf16.h>
 #include <stdint.h>
+#include <stdlib.h>
 #include "../../include/ddpx_kernels.h"
 
 #define CHECK(call) do { int rc_ = (call); if (rc_ != DDPX_OK) return rc_; } while (0)
@@ -31,6 +32,15 @@ __global__ void cast_multi_kernel(const CastTable t) {
     t.dst[seg][i] = __float2bfloat16(t.src[seg][i]);
 }
 
+// DDPX_BLOCK_FUSE: bit mask of the elementwise passes folded into GEMM epilogues / LayerNorm backward (for A/B timing):
+// 1 residual adds in the projections, 2 GELU with two outputs in the fc GEMM, 4 gelu' in the fc-activation data gradient,
+// 8 residual-gradient add in LayerNorm backward.  Default: all.
+int fuse_mask() {
+  static int m = -1;
+  if (m < 0) { const char* e = getenv("DDPX_BLOCK_FUSE"); m = e ? atoi(e) : 15; }
+  return m;
+}
+
 // y[M,N] = act(x[M,K] W[N,K]^T + b)
 int linear_fwd(const void* x, const void* W, const void* b, void* y, int M, int N, int K, int act, void* stream) {
   return ddpx_gemm_bias(x, W, y, M, N, K, K, K, N, 0, 0, 1, 1, b, 1, act, 1, 0, stream);
@@ -41,9 +51,12 @@ int linear_fwd(const void* x, const void* W, const void* b, void* y, int M, int 
 // in-kernel fix-up converts the finished sums to bf16 and leaves it zero again - no memset, no cast launch); db32: N floats
 // for the bias sums, OUTSIDE that zero-invariant area (layers of different sizes share ws32 from offset 0);
 // cnt: the fix-up's arrival counters (all zero on entry and on exit).
+// gelu_pre (optional, [M,K]): x was gelu(gelu_pre), and dx comes out multiplied by gelu'(gelu_pre) - the gradient of the
+// pre-activation - in the data-gradient GEMM's epilogue.
 int linear_bwd(const void* d, const void* x, const void* W, void* dx, void* dW, float* ws32, float* db32,
-               unsigned int* cnt, int M, int N, int K, void* stream) {
-  if (dx != nullptr) CHECK(ddpx_gemm(d, W, dx, M, K, N, N, K, K, 0, 1, 1, 1, nullptr, 0, 1, 0, stream));     // d[M,N] @ W[N,K]
+               unsigned int* cnt, int M, int N, int K, void* stream, const void* gelu_pre = nullptr) {
+  if (dx != nullptr)                                                                            // d[M,N] @ W[N,K]
+    CHECK(ddpx_gemm_fused(d, W, dx, M, K, N, N, K, K, 0, 1, nullptr, 0, 0, gelu_pre, gelu_pre != nullptr ? 2 : 0, nullptr, stream));
   // A weight gradient has few output tiles and a long reduction (the tokens): when 256x256 tiles cannot fill the 74 CTA
   // pairs, split the reduction and accumulate in fp32 (then cast) instead of shrinking the tiles.
   const int tiles = ((N + 255) / 256) * ((K + 255) / 256);
@@ -66,7 +79,7 @@ int linear_bwd(const void* d, const void* x, const void* W, void* dx, void* dW, 
 //   x1 = x + proj(attention(qkv(LN1(x)))),   out = x1 + proj2(gelu(fc(LN2(x1))))
 // params[12]: see the enum above.  acts[7]: LN1 out [M,C], qkv [M,3C], attention out [M,C], x1 [M,C], LN2 out [M,C],
 // fc pre-activation [M,4C], fc activation [M,4C] - all kept for the backward.  stats: fp32 [4*M + B*H*Tp] = LN1 mean /
-// rstd, LN2 mean / rstd, attention log-sum-exp (Tp = T rounded up to 128).  tmp: bf16 [M,C] scratch.
+// rstd, LN2 mean / rstd, attention log-sum-exp (Tp = T rounded up to 128).  tmp: bf16 [M,C] scratch (used only when the residual adds run as separate passes).
 extern "C" int ddpx_gpt2_block_fwd(const void* x, void* const* params, void* const* acts, float* stats, void* tmp, void* out,
                                    int B, int T, int C, int H, float eps, void* stream) {
   if (C != H * 64 || C % 8) return DDPX_ERR_SHAPE;
@@ -78,11 +91,27 @@ extern "C" int ddpx_gpt2_block_fwd(const void* x, void* const* params, void* con
   CHECK(ddpx_layernorm_fwd(x, params[LN1_W], params[LN1_B], acts[A_LN1], ln1_mean, ln1_rstd, M, C, eps, 1, stream));
   CHECK(linear_fwd(acts[A_LN1], params[ATTN_W], params[ATTN_B], acts[A_QKV], M, 3 * C, C, 0, stream));
   CHECK(ddpx_attn_fwd(acts[A_QKV], acts[A_ATT], lse2, B, T, H, 0.125f, stream));
-  CHECK(linear_fwd(acts[A_ATT], params[PROJ_W], params[PROJ_B], tmp, M, C, C, 0, stream));
-  CHECK(ddpx_add(x, tmp, acts[A_X1], MC, 1, stream));
+  // the residual connections ride in the projections' epilogues
+  const int fm = fuse_mask();
+  if (fm & 1) {
+    CHECK(ddpx_gemm_fused(acts[A_ATT], params[PROJ_W], acts[A_X1], M, C, C, C, C, C, 0, 0, params[PROJ_B], 1, 0, x, 1, nullptr,
+                          stream));
+  } else {
+    CHECK(linear_fwd(acts[A_ATT], params[PROJ_W], params[PROJ_B], tmp, M, C, C, 0, stream));
+    CHECK(ddpx_add(x, tmp, acts[A_X1], MC, 1, stream));
+  }
   CHECK(ddpx_layernorm_fwd(acts[A_X1], params[LN2_W], params[LN2_B], acts[A_LN2], ln2_mean, ln2_rstd, M, C, eps, 1, stream));
-  CHECK(linear_fwd(acts[A_LN2], params[FC_W], params[FC_B], acts[A_FCPRE], M, 4 * C, C, 0, stream));
-  CHECK(ddpx_gelu_fwd(acts[A_FCPRE], acts[A_FCACT], 4 * MC, 1, stream));
+  // GELU in the epilogue; the pre-activation (needed by the backward) is the kernel's second output
+  if (fm & 2) {
+    CHECK(ddpx_gemm_fused(acts[A_LN2], params[FC_W], acts[A_FCACT], M, 4 * C, C, C, C, 4 * C, 0, 0, params[FC_B], 1, 2, nullptr, 0,
+                          acts[A_FCPRE], stream));
+  } else {
+    CHECK(linear_fwd(acts[A_LN2], params[FC_W], params[FC_B], acts[A_FCPRE], M, 4 * C, C, 0, stream));
+    CHECK(ddpx_gelu_fwd(acts[A_FCPRE], acts[A_FCACT], 4 * MC, 1, stream));
+  }
+  if (fm & 1)
+    return ddpx_gemm_fused(acts[A_FCACT], params[PROJ2_W], out, M, C, 4 * C, 4 * C, 4 * C, C, 0, 0, params[PROJ2_B], 1, 0,
+                           acts[A_X1], 1, nullptr, stream);
   CHECK(linear_fwd(acts[A_FCACT], params[PROJ2_W], params[PROJ2_B], tmp, M, C, 4 * C, 0, stream));
   return ddpx_add(acts[A_X1], tmp, out, MC, 1, stream);
 }
@@ -116,17 +145,21 @@ extern "C" int ddpx_gpt2_block_bwd(const void* x, const void* dout, void* const*
   float* ln_scratch = delta + static_cast<size_t>(B) * H * Tp;
 
   // ---- MLP: out = x1 + proj2(gelu(fc(LN2(x1))))
-  CHECK(linear_bwd(dout, acts[A_FCACT], params[PROJ2_W], d_fc, grads[PROJ2_W], ws32, b_proj2, cnt, M, C, 4 * C, stream));
-  CHECK(ddpx_gelu_bwd(acts[A_FCPRE], d_fc, d_fc, 4 * MC, 1, stream));
+  const int fm = fuse_mask();
+  CHECK(linear_bwd(dout, acts[A_FCACT], params[PROJ2_W], d_fc, grads[PROJ2_W], ws32, b_proj2, cnt, M, C, 4 * C, stream,
+                   (fm & 4) ? acts[A_FCPRE] : nullptr));
+  if (!(fm & 4)) CHECK(ddpx_gelu_bwd(acts[A_FCPRE], d_fc, d_fc, 4 * MC, 1, stream));
   CHECK(linear_bwd(d_fc, acts[A_LN2], params[FC_W], d_a, grads[FC_W], ws32, b_fc, cnt, M, 4 * C, C, stream));
-  CHECK(ddpx_layernorm_bwd_ws(acts[A_X1], d_a, params[LN2_W], ln2_mean, ln2_rstd, d_b, ln2acc, ln2acc + C, M, C, 1, ln_scratch,
-                              stream));
-  CHECK(ddpx_add(d_b, dout, d_b, MC, 1, stream));                       // d_x1 = through LN2 + the residual branch
+  // d_x1 = through LN2 + the residual branch (added inside the LayerNorm kernel)
+  CHECK(ddpx_layernorm_bwd_res(acts[A_X1], d_a, params[LN2_W], ln2_mean, ln2_rstd, d_b, ln2acc, ln2acc + C, M, C, 1, ln_scratch,
+                               (fm & 8) ? dout : nullptr, stream));
+  if (!(fm & 8)) CHECK(ddpx_add(d_b, dout, d_b, MC, 1, stream));
   // ---- attention: x1 = x + proj(attention(qkv(LN1(x))))
   CHECK(linear_bwd(d_b, acts[A_ATT], params[PROJ_W], d_a, grads[PROJ_W], ws32, b_proj, cnt, M, C, C, stream));
   CHECK(ddpx_attn_bwd(acts[A_QKV], acts[A_ATT], d_a, lse2, delta, dqkv, B, T, H, 0.125f, stream));
   CHECK(linear_bwd(dqkv, acts[A_LN1], params[ATTN_W], d_a, grads[ATTN_W], ws32, b_attn, cnt, M, 3 * C, C, stream));
-  CHECK(ddpx_layernorm_bwd_ws(x, d_a, params[LN1_W], ln1_mean, ln1_rstd, dx, ln1acc, ln1acc + C, M, C, 1, ln_scratch, stream));
+  CHECK(ddpx_layernorm_bwd_res(x, d_a, params[LN1_W], ln1_mean, ln1_rstd, dx, ln1acc, ln1acc + C, M, C, 1, ln_scratch,
+                               (fm & 8) ? d_b : nullptr, stream));
   // ---- every small gradient fp32 -> bf16 in one launch
   CastTable t;
   const float* srcs[8] = {b_proj2, b_fc, b_proj, b_attn, ln2acc, ln2acc + C, ln1acc, ln1acc + C};
@@ -136,5 +169,5 @@ extern "C" int ddpx_gpt2_block_bwd(const void* x, const void* dout, void* const*
   t.count = 8;
   cast_multi_kernel<<<dim3((4 * C + 255) / 256, 8), 256, 0, s>>>(t);
   if (cudaGetLastError() != cudaSuccess) return DDPX_ERR_LAUNCH;
-  return ddpx_add(dx, d_b, dx, MC, 1, stream);
+  return (fm & 8) ? DDPX_OK : ddpx_add(dx, d_b, dx, MC, 1, stream);
 }

@@ -74,14 +74,59 @@ struct TcParams {
   // converts the finished sub-block to bf16 into `out` and leaves workspace and counter at zero for the next call
   float* fix_ws;
   unsigned int* fix_cnt;
+  // GEMM, bf16 output: an elementwise pass folded into the store.  `aux` is a bf16 tensor [M][ldo]:
+  //   aux_op 1  D = bf16(bf16(act(...)) + aux)              (residual connection)
+  //   aux_op 2  D = bf16(bf16(...) * gelu'(aux))            (aux = the pre-activation: backward through GELU)
+  // - the numerics of the separate pass without the pass.  out2 (with act = gelu): the pre-activation is stored there as
+  // well, so the forward keeps both tensors the backward needs from one kernel.
+  const __nv_bfloat16* aux;
+  int aux_op;
+  __nv_bfloat16* out2;
   float* stat_sum;          // FPROP: per-channel sum / sum-of-squares of the raw conv output
   float* stat_sq;
 };
 
+// eight bf16 values + eight bf16 values, each sum rounded once
+__device__ __forceinline__ uint4 add_bf16x8(uint4 a, uint4 b) {
+  uint4 r;
+  const __nv_bfloat162* pa = reinterpret_cast<const __nv_bfloat162*>(&a);
+  const __nv_bfloat162* pb = reinterpret_cast<const __nv_bfloat162*>(&b);
+  __nv_bfloat162* pr = reinterpret_cast<__nv_bfloat162*>(&r);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const float2 x = __bfloat1622float2(pa[i]), y = __bfloat1622float2(pb[i]);
+    pr[i] = __floats2bfloat162_rn(x.x + y.x, x.y + y.y);
+  }
+  return r;
+}
+
+__device__ __forceinline__ float tanh_fast(float x) {
+  float y;
+  asm("tanh.approx.f32 %0, %1;" : "=f"(y) : "f"(x));     // one MUFU op; error below bf16 resolution
+  return y;
+}
 __device__ __forceinline__ float gelu_tanh(float x) {
   const float k0 = 0.7978845608028654f, k1 = 0.044715f;
   float u = k0 * (x + k1 * x * x * x);
-  return 0.5f * x * (1.f + tanhf(u));
+  return 0.5f * x * (1.f + tanh_fast(u));
+}
+__device__ __forceinline__ float gelu_tanh_grad(float x) {
+  const float k0 = 0.7978845608028654f, k1 = 0.044715f;
+  const float t = tanh_fast(k0 * (x + k1 * x * x * x));
+  return 0.5f * (1.f + t) + 0.5f * x * (1.f - t * t) * k0 * (1.f + 3.f * k1 * x * x);
+}
+// eight bf16 values times gelu'(eight bf16 pre-activations)
+__device__ __forceinline__ uint4 mul_gelu_grad_bf16x8(uint4 a, uint4 pre) {
+  uint4 r;
+  const __nv_bfloat162* pa = reinterpret_cast<const __nv_bfloat162*>(&a);
+  const __nv_bfloat162* pb = reinterpret_cast<const __nv_bfloat162*>(&pre);
+  __nv_bfloat162* pr = reinterpret_cast<__nv_bfloat162*>(&r);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const float2 x = __bfloat1622float2(pa[i]), y = __bfloat1622float2(pb[i]);
+    pr[i] = __floats2bfloat162_rn(x.x * gelu_tanh_grad(y.x), x.y * gelu_tanh_grad(y.y));
+  }
+  return r;
 }
 
 // kCG = 1: one CTA per tile (128 rows).  kCG = 2: a CTA pair (cluster of 2 on one TPC) per 256-row tile with
@@ -395,6 +440,51 @@ tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
             float f[32];
 #pragma unroll
             for (int j = 0; j < 32; ++j) f[j] = fmaf(__uint_as_float(v[j]), p.alpha, __shfl_sync(0xffffffffu, bl, j));
+            const bool full = (n0 + c0 + 32 <= p.N);
+            uint8_t* stg = epi_stage + (warp - 4) * 4096;
+            const int row0 = m_blk * kTileM + static_cast<int>(cta_rank) * kBlockM + ew * 32;
+            // warp-uniform store of the warp's 32x32 chunk as bf16: transpose through shared memory (XOR-swizzled 16-byte
+            // pieces, conflict-free both ways) so that every global store instruction writes whole row segments; the
+            // elementwise pass folded into the store (aux_op) works on those 16-byte pieces
+            auto store_bf16 = [&](__nv_bfloat16* base, int aux_op) {
+#pragma unroll
+              for (int j = 0; j < 4; ++j) {
+                __nv_bfloat162 h0 = __floats2bfloat162_rn(f[8 * j], f[8 * j + 1]);
+                __nv_bfloat162 h1 = __floats2bfloat162_rn(f[8 * j + 2], f[8 * j + 3]);
+                __nv_bfloat162 h2 = __floats2bfloat162_rn(f[8 * j + 4], f[8 * j + 5]);
+                __nv_bfloat162 h3 = __floats2bfloat162_rn(f[8 * j + 6], f[8 * j + 7]);
+                uint4 u;
+                u.x = *reinterpret_cast<uint32_t*>(&h0); u.y = *reinterpret_cast<uint32_t*>(&h1);
+                u.z = *reinterpret_cast<uint32_t*>(&h2); u.w = *reinterpret_cast<uint32_t*>(&h3);
+                *reinterpret_cast<uint4*>(stg + lane * 64 + ((j ^ ((lane >> 1) & 3)) << 4)) = u;
+              }
+              __syncwarp();
+              __nv_bfloat16* ob = base + boff + n0 + c0;
+#pragma unroll
+              for (int it = 0; it < 4; ++it) {
+                const int r = it * 8 + (lane >> 2), q = lane & 3;
+                uint4 u = *reinterpret_cast<const uint4*>(stg + r * 64 + ((q ^ ((r >> 1) & 3)) << 4));
+                if (row0 + r < p.M) {
+                  const long long off = static_cast<long long>(row0 + r) * p.ldo + q * 8;
+                  if (aux_op == 1) u = add_bf16x8(u, __ldg(reinterpret_cast<const uint4*>(p.aux + n0 + c0 + off)));
+                  else if (aux_op == 2) u = mul_gelu_grad_bf16x8(u, __ldg(reinterpret_cast<const uint4*>(p.aux + n0 + c0 + off)));
+                  *reinterpret_cast<uint4*>(ob + off) = u;
+                }
+              }
+              __syncwarp();
+            };
+            const bool staged = p.st_vec && full;
+            if (p.out2 != nullptr) {
+              // the pre-activation goes out as well (bf16; the host accepts out2 only with whole, 16-byte-aligned rows)
+              if (staged) {
+                store_bf16(p.out2, 0);
+              } else if (row < p.M) {
+                __nv_bfloat16* o2 = p.out2 + static_cast<long long>(row) * p.ldo + n0 + c0;
+#pragma unroll
+                for (int j = 0; j < 32; ++j)
+                  if (n0 + c0 + j < p.N) o2[j] = __float2bfloat16(f[j]);
+              }
+            }
             if (p.act == 1) {
 #pragma unroll
               for (int j = 0; j < 32; ++j) f[j] = fmaxf(f[j], 0.f);
@@ -402,33 +492,9 @@ tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
 #pragma unroll
               for (int j = 0; j < 32; ++j) f[j] = gelu_tanh(f[j]);
             }
-            const bool full = (n0 + c0 + 32 <= p.N);
-            if (p.st_vec && full) {
-              // warp-uniform path: transpose the warp's 32x32 chunk through shared memory (XOR-swizzled 16-byte pieces,
-              // conflict-free both ways) so that every global store instruction writes whole row segments
-              uint8_t* stg = epi_stage + (warp - 4) * 4096;
-              const int row0 = m_blk * kTileM + static_cast<int>(cta_rank) * kBlockM + ew * 32;
+            if (staged) {
               if (p.out_bf16) {
-#pragma unroll
-                for (int j = 0; j < 4; ++j) {
-                  __nv_bfloat162 h0 = __floats2bfloat162_rn(f[8 * j], f[8 * j + 1]);
-                  __nv_bfloat162 h1 = __floats2bfloat162_rn(f[8 * j + 2], f[8 * j + 3]);
-                  __nv_bfloat162 h2 = __floats2bfloat162_rn(f[8 * j + 4], f[8 * j + 5]);
-                  __nv_bfloat162 h3 = __floats2bfloat162_rn(f[8 * j + 6], f[8 * j + 7]);
-                  uint4 u;
-                  u.x = *reinterpret_cast<uint32_t*>(&h0); u.y = *reinterpret_cast<uint32_t*>(&h1);
-                  u.z = *reinterpret_cast<uint32_t*>(&h2); u.w = *reinterpret_cast<uint32_t*>(&h3);
-                  *reinterpret_cast<uint4*>(stg + lane * 64 + ((j ^ ((lane >> 1) & 3)) << 4)) = u;
-                }
-                __syncwarp();
-                __nv_bfloat16* ob = reinterpret_cast<__nv_bfloat16*>(p.out) + boff + n0 + c0;
-#pragma unroll
-                for (int it = 0; it < 4; ++it) {
-                  const int r = it * 8 + (lane >> 2), q = lane & 3;
-                  const uint4 u = *reinterpret_cast<const uint4*>(stg + r * 64 + ((q ^ ((r >> 1) & 3)) << 4));
-                  if (row0 + r < p.M) *reinterpret_cast<uint4*>(ob + static_cast<long long>(row0 + r) * p.ldo + q * 8) = u;
-                }
-                __syncwarp();
+                store_bf16(reinterpret_cast<__nv_bfloat16*>(p.out), p.aux_op);
               } else {
 #pragma unroll
                 for (int j = 0; j < 8; ++j)
@@ -449,7 +515,14 @@ tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
                 __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(p.out) + boff + static_cast<long long>(row) * p.ldo + n0 + c0;
 #pragma unroll
                 for (int j = 0; j < 32; ++j)
-                  if (n0 + c0 + j < p.N) o[j] = __float2bfloat16(f[j]);
+                  if (n0 + c0 + j < p.N) {
+                    __nv_bfloat16 hv = __float2bfloat16(f[j]);
+                    if (p.aux_op != 0) {
+                      const float a = __bfloat162float(p.aux[static_cast<long long>(row) * p.ldo + n0 + c0 + j]);
+                      hv = __float2bfloat16(p.aux_op == 1 ? __bfloat162float(hv) + a : __bfloat162float(hv) * gelu_tanh_grad(a));
+                    }
+                    o[j] = hv;
+                  }
               } else {
                 float* o = reinterpret_cast<float*>(p.out) + boff + static_cast<long long>(row) * p.ldo + n0 + c0;
 #pragma unroll
@@ -718,7 +791,8 @@ static int gemm_impl(const void* A, const void* B, void* D, int M, int N, int K,
                      long long ldd, int a_mn, int b_mn, int bf16, int out_bf16, const void* bias_, int bias_bf16, int act,
                      float alpha, int split_k, int accumulate, int batch1, int batch2, long long a_bs1,
                      long long a_bs2, long long b_bs1, long long b_bs2, long long d_bs1, long long d_bs2,
-                     int causal, void* stream_, float* fix_ws = nullptr, unsigned int* fix_cnt = nullptr) {
+                     int causal, void* stream_, float* fix_ws = nullptr, unsigned int* fix_cnt = nullptr,
+                     const void* aux = nullptr, int aux_op = 0, void* out2 = nullptr) {
   const float* bias = static_cast<const float*>(bias_);
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
   const int elt = bf16 ? 2 : 4;
@@ -782,6 +856,13 @@ static int gemm_impl(const void* A, const void* B, void* D, int M, int N, int K,
     return DDPX_ERR_ARG;
   }
   p.act = act; p.bias = bias; p.bias_bf16 = bias_bf16;
+  if (aux_op != 0 || out2 != nullptr) {
+    if (!out_bf16 || p.atomic || batch1 * batch2 != 1 || aux_op < 0 || aux_op > 2 || (aux_op != 0 && aux == nullptr) ||
+        (reinterpret_cast<uintptr_t>(aux) & 15) || (reinterpret_cast<uintptr_t>(out2) & 15) ||
+        (out2 != nullptr && (act != 2 || (ldd % 8))))
+      return DDPX_ERR_ARG;
+    p.aux = static_cast<const __nv_bfloat16*>(aux); p.aux_op = aux_op; p.out2 = static_cast<__nv_bfloat16*>(out2);
+  }
   {
     const int oe = out_bf16 ? 2 : 4;
     p.st_vec = ((ldd * oe) % 16 == 0 && (d_bs1 * oe) % 16 == 0 && (d_bs2 * oe) % 16 == 0 &&
@@ -850,6 +931,16 @@ extern "C" int ddpx_gemm_bias(const void* A, const void* B, void* D, int M, int 
                               int act, int split_k, int accumulate, void* stream_) {
   return gemm_impl(A, B, D, M, N, K, lda, ldb, ldd, a_mn, b_mn, bf16, out_bf16, bias, bias_bf16, act, 1.0f, split_k,
                    accumulate, 1, 1, 0, 0, 0, 0, 0, 0, 0, stream_);
+}
+
+// bf16 GEMM with an elementwise pass folded into the epilogue's store (see TcParams::aux):
+//   aux_op 1: D = act(A B + bias) + aux (residual);  aux_op 2: D = (A B) * gelu'(aux);  out2 (act = 2 only): also store the
+//   pre-activation A B + bias there.  aux / out2 are bf16 [M][ldd].
+extern "C" int ddpx_gemm_fused(const void* A, const void* B, void* D, int M, int N, int K, long long lda, long long ldb,
+                               long long ldd, int a_mn, int b_mn, const void* bias, int bias_bf16, int act, const void* aux,
+                               int aux_op, void* out2, void* stream_) {
+  return gemm_impl(A, B, D, M, N, K, lda, ldb, ldd, a_mn, b_mn, 1, 1, bias, bias_bf16, act, 1.0f, 1, 0, 1, 1, 0, 0, 0, 0, 0, 0,
+                   0, stream_, nullptr, nullptr, aux, aux_op, out2);
 }
 
 extern "C" int ddpx_gemm(const void* A, const void* B, void* D, int M, int N, int K, long long lda, long long ldb,

@@ -64,7 +64,7 @@ __global__ void __launch_bounds__(256, (NV <= 4 ? 2 : 1))
 layernorm_bwd_kernel(const T* __restrict__ x, const T* __restrict__ dy, const T* __restrict__ gamma,
                      const float* __restrict__ mean, const float* __restrict__ rstd, T* __restrict__ dx,
                      float* __restrict__ dgamma, float* __restrict__ dbeta, long long rows, int C,
-                     float* __restrict__ partial) {
+                     float* __restrict__ partial, const T* __restrict__ dres) {
   constexpr int V = VecOf<T>::N;
   // rows up to 2 vectors per lane (C <= 512 in bf16) stay in registers between the two passes over a row; wider rows
   // are read again (from L1) for the second pass - registers go to the column sums instead, so that two blocks fit on
@@ -122,6 +122,12 @@ layernorm_bwd_kernel(const T* __restrict__ x, const T* __restrict__ dy, const T*
             const float xh = (f[k] - m) * rs;
             f[k] = rs * (d[k] * g[k] - a - xh * b);
           }
+        }
+        if (dres != nullptr) {          // the gradient arriving over the residual connection around this LayerNorm
+          float e[V];
+          vload(dres + r * C + i * V, e);
+#pragma unroll
+          for (int k = 0; k < V; ++k) f[k] += e[k];
         }
         vstore(dxr + i * V, f);
       }
@@ -305,8 +311,8 @@ __global__ void dropout_kernel(const T* __restrict__ x, T* __restrict__ y, long 
 
 template <typename T>
 int launch_ln_bwd(int nv, int grid, size_t smem, cudaStream_t s, const T* x, const T* dy, const T* g, const float* mean,
-                  const float* rstd, T* dx, float* dgamma, float* dbeta, long long rows, int C, float* partial) {
-#define LN_CASE(NVV) case NVV: layernorm_bwd_kernel<T, NVV><<<grid, 256, smem, s>>>(x, dy, g, mean, rstd, dx, dgamma, dbeta, rows, C, partial); break;
+                  const float* rstd, T* dx, float* dgamma, float* dbeta, long long rows, int C, float* partial, const T* dres) {
+#define LN_CASE(NVV) case NVV: layernorm_bwd_kernel<T, NVV><<<grid, 256, smem, s>>>(x, dy, g, mean, rstd, dx, dgamma, dbeta, rows, C, partial, dres); break;
   switch (nv) {
     LN_CASE(1) LN_CASE(2) LN_CASE(3) LN_CASE(4) LN_CASE(5) LN_CASE(6) LN_CASE(7) LN_CASE(8)
     LN_CASE(9) LN_CASE(10) LN_CASE(11) LN_CASE(12) LN_CASE(13) LN_CASE(14) LN_CASE(15) LN_CASE(16)
@@ -347,9 +353,11 @@ extern "C" long long ddpx_layernorm_bwd_scratch_floats(long long rows, int C) {
   return static_cast<long long>(ln_bwd_grid(rows, 1)) * 2 * C;          // the larger of the two grids
 }
 
-extern "C" int ddpx_layernorm_bwd_ws(const void* x, const void* dy, const void* gamma, const float* mean, const float* rstd,
-                                     void* dx, float* dgamma, float* dbeta, long long rows, int C, int is_bf16, float* scratch,
-                                     void* stream) {
+// `dres` (optional, same shape and dtype as dx, not aliasing it) is added to dx: the gradient of the residual branch around
+// the LayerNorm, so that no separate add pass runs.
+extern "C" int ddpx_layernorm_bwd_res(const void* x, const void* dy, const void* gamma, const float* mean, const float* rstd,
+                                      void* dx, float* dgamma, float* dbeta, long long rows, int C, int is_bf16, float* scratch,
+                                      const void* dres, void* stream) {
   const int V = is_bf16 ? 8 : 4;
   if (C % V) return DDPX_ERR_SHAPE;
   const int nv = (C / V + 31) / 32;
@@ -362,10 +370,12 @@ extern "C" int ddpx_layernorm_bwd_ws(const void* x, const void* dy, const void* 
   int rc;
   if (is_bf16)
     rc = launch_ln_bwd<bf16>(nv, grid, smem, ST(stream), static_cast<const bf16*>(x), static_cast<const bf16*>(dy),
-                             static_cast<const bf16*>(gamma), mean, rstd, static_cast<bf16*>(dx), dgamma, dbeta, rows, C, scratch);
+                             static_cast<const bf16*>(gamma), mean, rstd, static_cast<bf16*>(dx), dgamma, dbeta, rows, C, scratch,
+                             static_cast<const bf16*>(dres));
   else
     rc = launch_ln_bwd<float>(nv, grid, smem, ST(stream), static_cast<const float*>(x), static_cast<const float*>(dy),
-                              static_cast<const float*>(gamma), mean, rstd, static_cast<float*>(dx), dgamma, dbeta, rows, C, scratch);
+                              static_cast<const float*>(gamma), mean, rstd, static_cast<float*>(dx), dgamma, dbeta, rows, C, scratch,
+                              static_cast<const float*>(dres));
   if (rc != DDPX_OK) return rc;
   if (cudaGetLastError() != cudaSuccess) return DDPX_ERR_LAUNCH;
   if (scratch != nullptr) {
@@ -373,6 +383,12 @@ extern "C" int ddpx_layernorm_bwd_ws(const void* x, const void* dy, const void* 
     if (cudaGetLastError() != cudaSuccess) return DDPX_ERR_LAUNCH;
   }
   return DDPX_OK;
+}
+
+extern "C" int ddpx_layernorm_bwd_ws(const void* x, const void* dy, const void* gamma, const float* mean, const float* rstd,
+                                     void* dx, float* dgamma, float* dbeta, long long rows, int C, int is_bf16, float* scratch,
+                                     void* stream) {
+  return ddpx_layernorm_bwd_res(x, dy, gamma, mean, rstd, dx, dgamma, dbeta, rows, C, is_bf16, scratch, nullptr, stream);
 }
 
 extern "C" int ddpx_layernorm_bwd(const void* x, const void* dy, const void* gamma, const float* mean, const float* rstd,

@@ -438,6 +438,14 @@ def gpt2_block_bwd(x, dout, params, acts, stats, grads, dx, wsb, ws32, cnt, B, T
           launches=24)
 
 
+def gemm_fused(A, B, D, M, N, K, lda, ldb, ldd, a_mn=0, b_mn=0, bias=None, act=0, aux=None, aux_op=0, out2=None):
+    """bf16 GEMM with an elementwise pass folded into the store: aux_op 1 adds `aux` (residual), aux_op 2 multiplies by
+    gelu'(aux); out2 (act = 2) also receives the pre-activation.  aux / out2: bf16 [M, ldd]."""
+    _call("ddpx_gemm_fused", _P(A), _P(B), _P(D), c_int(M), c_int(N), c_int(K), c_longlong(lda), c_longlong(ldb),
+          c_longlong(ldd), c_int(a_mn), c_int(b_mn), _P(bias), c_int(1 if bias is not None and bias.dtype == torch.bfloat16 else 0),
+          c_int(act), _P(aux), c_int(aux_op), _P(out2), _st())
+
+
 def gemm_splitk_bf16(A, B, D, M, N, K, lda, ldb, ldd, a_mn, b_mn, split_k, ws, cnt):
     """bf16 split-K GEMM with the fix-up inside the kernel; ws (fp32 [M*N]) and cnt (int32) all zero before and after."""
     _call("ddpx_gemm_splitk_bf16", _P(A), _P(B), _P(D), c_int(M), c_int(N), c_int(K), c_longlong(lda), c_longlong(ldb),

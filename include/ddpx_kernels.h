@@ -40,6 +40,11 @@ int ddpx_gemm(const void* A, const void* B, void* D, int M, int N, int K, long l
 int ddpx_gemm_bias(const void* A, const void* B, void* D, int M, int N, int K, long long lda, long long ldb, long long ldd,
                    int a_mn, int b_mn, int bf16, int out_bf16, const void* bias, int bias_bf16, int act, int split_k,
                    int accumulate, void* stream);
+/* bf16 GEMM with an elementwise pass folded into the store: aux_op 1: D = act(A B + bias) + aux (residual); aux_op 2:
+ * D = (A B) * gelu'(aux); out2 (act = 2 only): the pre-activation is stored there as well.  aux / out2: bf16 [M][ldd]. */
+int ddpx_gemm_fused(const void* A, const void* B, void* D, int M, int N, int K, long long lda, long long ldb, long long ldd,
+                    int a_mn, int b_mn, const void* bias, int bias_bf16, int act, const void* aux, int aux_op, void* out2,
+                    void* stream);
 
 /* Split-K GEMM, bf16 in and out, with the fix-up inside the kernel (no memset / cast launches): partial tiles are reduced into
  * ws (fp32 [M*N]); the epilogue warp that delivers the last partial sum of a sub-block converts it into D and clears ws.
@@ -212,6 +217,10 @@ int ddpx_layernorm_bwd(const void* x, const void* dy, const void* gamma, const f
 int ddpx_layernorm_bwd_ws(const void* x, const void* dy, const void* gamma, const float* mean, const float* rstd, void* dx,
                           float* dgamma, float* dbeta, long long rows, int C, int is_bf16, float* scratch, void* stream);
 long long ddpx_layernorm_bwd_scratch_floats(long long rows, int C);
+/* ... and with `dres` (optional; shape and dtype of dx, no aliasing) added to dx: the residual branch's gradient */
+int ddpx_layernorm_bwd_res(const void* x, const void* dy, const void* gamma, const float* mean, const float* rstd, void* dx,
+                           float* dgamma, float* dbeta, long long rows, int C, int is_bf16, float* scratch, const void* dres,
+                           void* stream);
 int ddpx_gelu_fwd(const void* x, void* y, long long n, int is_bf16, void* stream);
 int ddpx_gelu_bwd(const void* x, const void* dy, void* dx, long long n, int is_bf16, void* stream);
 int ddpx_relu_bwd_bf16(const void* y, const void* dy, void* dx, long long n, void* stream);

@@ -155,6 +155,31 @@ def test_splitk_gemm_with_in_kernel_fixup(Mo, No, Kr, split):
         assert float(ws.abs().max()) == 0.0 and int(cnt.abs().max()) == 0
 
 
+@pytest.mark.parametrize("M,N,K", [(2048, 1600, 1600), (300, 200, 136), (1024, 3072, 768)])
+def test_gemm_with_fused_epilogue_passes(M, N, K):
+    """Residual add, multiplication by gelu'(pre-activation) and the GELU with two outputs, all inside the GEMM's store
+    (whole tiles take the staged vector path, the odd shape the per-element one)."""
+    torch.manual_seed(11)
+    x = (torch.randn(M, K, device="cuda") * 0.5).bfloat16()
+    w = (torch.randn(N, K, device="cuda") * 0.05).bfloat16()
+    b = (torch.randn(N, device="cuda") * 0.1).bfloat16()
+    aux = torch.randn(M, N, device="cuda").bfloat16()
+    lin = x.double() @ w.double().t() + b.double()
+    out = torch.empty(M, N, device="cuda", dtype=torch.bfloat16)
+    native.gemm_fused(x, w, out, M, N, K, K, K, N, bias=b, aux=aux, aux_op=1)
+    assert rel_l2(out, lin + aux.double()) < 6e-3
+    native.gemm_fused(x, w, out, M, N, K, K, K, N, aux=aux, aux_op=2)
+    a = aux.double().requires_grad_()
+    F.gelu(a, approximate="tanh").sum().backward()
+    assert rel_l2(out, (lin - b.double()) * a.grad) < 8e-3
+    pre = torch.empty_like(out)
+    native.gemm_fused(x, w, out, M, N, K, K, K, N, bias=b, act=2, out2=pre)
+    torch.cuda.synchronize()
+    assert rel_l2(pre, lin) < 6e-3
+    assert rel_l2(out, F.gelu(lin, approximate="tanh")) < 8e-3
+    assert native.read_error_word() == 0
+
+
 def test_embedding_sum_and_padded_ce():
     torch.manual_seed(3)
     V, Vp, C, B, T = 1000, 1024, 128, 4, 64
