@@ -41,14 +41,6 @@ __device__ __forceinline__ void bulk_load(void* dst, const void* src, uint32_t b
                : "memory");
 }
 
-// Work item of round k for this CTA: items are sorted heaviest first; even rounds deal them left to right, odd rounds right
-// to left, so that every CTA's share has nearly the same weight.  Returns -1 when the CTA has no item in that round.
-__device__ __forceinline__ int snake_item(int k, int nitems) {
-  const int G = static_cast<int>(gridDim.x), c = static_cast<int>(blockIdx.x);
-  const long long idx = static_cast<long long>(k) * G + ((k & 1) ? (G - 1 - c) : c);
-  return idx < nitems ? static_cast<int>(idx) : -1;
-}
-
 // =====================================================================================================================
 // dQ
 // =====================================================================================================================

@@ -44,6 +44,14 @@ __device__ __forceinline__ uint64_t desc_mnmajor(uint32_t saddr, int kk) {
   return make_smem_desc_sw128(saddr + kk * 2048, 8192, 1024, 2);
 }
 
+// Work item of round k for this CTA: items are sorted heaviest first; even rounds deal them left to right, odd rounds right
+// to left, so that every CTA's share has nearly the same weight.  Returns -1 when the CTA has no item in that round.
+__device__ __forceinline__ int snake_item(int k, int nitems) {
+  const int G = static_cast<int>(gridDim.x), c = static_cast<int>(blockIdx.x);
+  const long long idx = static_cast<long long>(k) * G + ((k & 1) ? (G - 1 - c) : c);
+  return idx < nitems ? static_cast<int>(idx) : -1;
+}
+
 // [B][T][row_elems] bf16 viewed as (row_elems, T, B); a box is 128 rows x 64 columns (one head's slice of 128 tokens).
 // Rows past T are out of bounds in dimension 1 and arrive as zeros.
 inline int attn_map(CUtensorMap* tm, const void* base, int B, int T, int row_elems) {
