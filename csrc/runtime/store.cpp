@@ -12,6 +12,7 @@
 #include <netinet/tcp.h>
 #include <poll.h>
 #include <sys/socket.h>
+#include <sys/time.h>
 #include <unistd.h>
 
 #include <atomic>
@@ -127,6 +128,10 @@ struct Server {
         if (c >= 0) {
           int one = 1;
           setsockopt(c, IPPROTO_TCP, TCP_NODELAY, &one, sizeof(one));
+          // a client that stalls in the middle of a request must not freeze the server (one thread serves every rank):
+          // its blocking reads give up after two seconds and the connection is dropped
+          timeval tv{2, 0};
+          setsockopt(c, SOL_SOCKET, SO_RCVTIMEO, &tv, sizeof(tv));
           fds.push_back({c, POLLIN, 0});
         }
       }

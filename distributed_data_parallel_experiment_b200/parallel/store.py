@@ -103,17 +103,28 @@ class NativeStore:
         self._gen[name] = g + 1
         return f"{name}/{g}"
 
+    def _retire(self, name: str, keys) -> None:
+        """Rank 0 deletes the keys of the generation before the one that just completed: every rank has entered the current
+        generation, so nobody reads the previous one any more (a long job must not grow the server's map without bound)."""
+        g = self._gen[name] - 2
+        if self.rank == 0 and g >= 0:
+            for k in keys(f"{name}/{g}"):
+                self.delete(k)
+
     def barrier(self, name: str = "barrier") -> None:
         tag = self._next(name)
         n = self.add(tag + "/arrived", 1)
         if n == self.world_size:
             self.set(tag + "/go", b"1")
         self.get(tag + "/go")
+        self._retire(name, lambda t: (t + "/arrived", t + "/go"))
 
     def all_gather(self, payload: bytes, name: str = "gather") -> List[bytes]:
         tag = self._next(name)
         self.set(f"{tag}/{self.rank}", payload)
-        return [self.get(f"{tag}/{r}") for r in range(self.world_size)]
+        out = [self.get(f"{tag}/{r}") for r in range(self.world_size)]
+        self._retire(name, lambda t: [f"{t}/{r}" for r in range(self.world_size)])
+        return out
 
     def all_gather_object(self, obj: Any, name: str = "gather_obj") -> List[Any]:
         return [pickle.loads(b) for b in self.all_gather(pickle.dumps(obj), name)]

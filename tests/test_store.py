@@ -34,6 +34,30 @@ def test_primitives_single_process():
     second.close(); s.close()
 
 
+def test_consumed_generations_are_retired():
+    """Barrier / gather keys of finished generations are deleted: a long job must not grow the server's map."""
+    s = NativeStore("127.0.0.1", 0, rank=0, world_size=1)
+    for _ in range(20):
+        s.barrier("b")
+        s.all_gather(b"x", "g")
+    assert s.num_keys() <= 6          # the last two generations of each (2 barrier keys, 1 gather key per generation)
+    s.close()
+
+
+def test_stalled_client_does_not_freeze_the_server():
+    """A peer that sends half a request and goes silent is dropped after the receive timeout; the others keep being served."""
+    import socket
+    import time
+    s = NativeStore("127.0.0.1", 0, rank=0, world_size=1)
+    bad = socket.create_connection(("127.0.0.1", s.port))
+    bad.sendall(b"\x01")               # an opcode and nothing else
+    t0 = time.time()
+    s.set("k", b"v")                   # may wait for the stalled read to time out, but must come back
+    assert s.get("k") == b"v"
+    assert time.time() - t0 < 10.0
+    bad.close(); s.close()
+
+
 def _worker(rank, world, port_file, outdir):
     if rank == 0:
         s = NativeStore("127.0.0.1", 0, rank, world)
