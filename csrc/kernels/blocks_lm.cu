@@ -71,7 +71,9 @@ int linear_bwd(const void* d, const void* x, const void* W, void* dx, void* dW, 
   } else {
     CHECK(ddpx_gemm(d, x, dW, N, K, M, N, K, K, 1, 1, 1, 1, nullptr, 0, 1, 0, stream));
   }
-  return ddpx_colsum_bf16(d, db32, M, N, stream);       // fp32 sums; the block casts all its small gradients at the end
+  // bias gradient: fp32 column sums; the block casts all its small gradients at the end.  A null db32 leaves them to the
+  // caller (the GPT-2 block sums the four of them in one launch)
+  return db32 != nullptr ? ddpx_colsum_bf16(d, db32, M, N, stream) : DDPX_OK;
 }
 }  // namespace
 
@@ -146,20 +148,29 @@ extern "C" int ddpx_gpt2_block_bwd(const void* x, const void* dout, void* const*
 
   // ---- MLP: out = x1 + proj2(gelu(fc(LN2(x1))))
   const int fm = fuse_mask();
-  CHECK(linear_bwd(dout, acts[A_FCACT], params[PROJ2_W], d_fc, grads[PROJ2_W], ws32, b_proj2, cnt, M, C, 4 * C, stream,
+  CHECK(linear_bwd(dout, acts[A_FCACT], params[PROJ2_W], d_fc, grads[PROJ2_W], ws32, nullptr, cnt, M, C, 4 * C, stream,
                    (fm & 4) ? acts[A_FCPRE] : nullptr));
   if (!(fm & 4)) CHECK(ddpx_gelu_bwd(acts[A_FCPRE], d_fc, d_fc, 4 * MC, 1, stream));
-  CHECK(linear_bwd(d_fc, acts[A_LN2], params[FC_W], d_a, grads[FC_W], ws32, b_fc, cnt, M, 4 * C, C, stream));
+  CHECK(linear_bwd(d_fc, acts[A_LN2], params[FC_W], d_a, grads[FC_W], ws32, nullptr, cnt, M, 4 * C, C, stream));
   // d_x1 = through LN2 + the residual branch (added inside the LayerNorm kernel)
   CHECK(ddpx_layernorm_bwd_res(acts[A_X1], d_a, params[LN2_W], ln2_mean, ln2_rstd, d_b, ln2acc, ln2acc + C, M, C, 1, ln_scratch,
                                (fm & 8) ? dout : nullptr, stream));
   if (!(fm & 8)) CHECK(ddpx_add(d_b, dout, d_b, MC, 1, stream));
   // ---- attention: x1 = x + proj(attention(qkv(LN1(x))))
-  CHECK(linear_bwd(d_b, acts[A_ATT], params[PROJ_W], d_a, grads[PROJ_W], ws32, b_proj, cnt, M, C, C, stream));
+  CHECK(linear_bwd(d_b, acts[A_ATT], params[PROJ_W], d_a, grads[PROJ_W], ws32, nullptr, cnt, M, C, C, stream));
   CHECK(ddpx_attn_bwd(acts[A_QKV], acts[A_ATT], d_a, lse2, delta, dqkv, B, T, H, 0.125f, stream));
-  CHECK(linear_bwd(dqkv, acts[A_LN1], params[ATTN_W], d_a, grads[ATTN_W], ws32, b_attn, cnt, M, 3 * C, C, stream));
+  CHECK(linear_bwd(dqkv, acts[A_LN1], params[ATTN_W], d_a, grads[ATTN_W], ws32, nullptr, cnt, M, 3 * C, C, stream));
   CHECK(ddpx_layernorm_bwd_res(x, d_a, params[LN1_W], ln1_mean, ln1_rstd, dx, ln1acc, ln1acc + C, M, C, 1, ln_scratch,
                                (fm & 8) ? d_b : nullptr, stream));
+  // ---- the four bias gradients: column sums of dout, d_fc, d_x1, dqkv (all still intact) in one launch over one
+  // cleared stretch of the scratch (the first 9C floats of small32), instead of a memset + kernel pair per linear layer
+  {
+    if (cudaMemsetAsync(small32, 0, sizeof(float) * 9 * C, s) != cudaSuccess) return DDPX_ERR_LAUNCH;
+    const void* xs[4] = {dout, d_fc, d_b, dqkv};
+    float* outs[4] = {b_proj2, b_fc, b_proj, b_attn};
+    const int cs[4] = {C, 4 * C, C, 3 * C};
+    CHECK(ddpx_colsum_bf16_multi(4, xs, outs, M, cs, stream));
+  }
   // ---- every small gradient fp32 -> bf16 in one launch
   CastTable t;
   const float* srcs[8] = {b_proj2, b_fc, b_proj, b_attn, ln2acc, ln2acc + C, ln1acc, ln1acc + C};

@@ -297,6 +297,40 @@ __global__ void colsum_bf16_vec_kernel(const bf16* __restrict__ x, float* __rest
     atomicAdd(out + c, a);
   }
 }
+// the same for up to four matrices with the same number of rows in one launch (the four bias gradients of a transformer
+// block): blockIdx.x walks the concatenated column groups, the table says which matrix a block belongs to
+struct ColsumTable { const bf16* x[4]; float* out[4]; int cols[4]; int first_block[5]; int count; };
+__global__ void colsum_bf16_multi_kernel(const ColsumTable t, long long rows) {
+  __shared__ float sh[8][32][9];
+  int m = 0;
+  while (m + 1 < t.count && static_cast<int>(blockIdx.x) >= t.first_block[m + 1]) ++m;
+  const bf16* __restrict__ x = t.x[m];
+  const int cols = t.cols[m];
+  const int bx = static_cast<int>(blockIdx.x) - t.first_block[m];
+  const int cg = bx * 32 + threadIdx.x;              // column group (8 columns)
+  float s[8];
+#pragma unroll
+  for (int k = 0; k < 8; ++k) s[k] = 0.f;
+  if (cg * 8 < cols)
+    for (long long r = static_cast<long long>(blockIdx.y) * 8 + threadIdx.y; r < rows; r += static_cast<long long>(gridDim.y) * 8) {
+      float f[8];
+      vload(x + r * cols + cg * 8, f);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) s[k] += f[k];
+    }
+#pragma unroll
+  for (int k = 0; k < 8; ++k) sh[threadIdx.y][threadIdx.x][k] = s[k];
+  __syncthreads();
+  const int tt = threadIdx.y * 32 + threadIdx.x;
+  const int g = tt >> 3, k = tt & 7;
+  const int c = (bx * 32 + g) * 8 + k;
+  if (c < cols) {
+    float a = 0.f;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) a += sh[j][g][k];
+    atomicAdd(t.out[m] + c, a);
+  }
+}
 // inverted dropout with a counter-based hash RNG: keep iff hash(seed, i) >= p * 2^32
 __device__ __forceinline__ uint32_t hash32(uint64_t x) {
   x ^= x >> 33; x *= 0xff51afd7ed558ccdULL; x ^= x >> 33; x *= 0xc4ceb9fe1a85ec53ULL; x ^= x >> 33;
@@ -449,6 +483,27 @@ extern "C" int ddpx_colsum_bf16(const void* x, float* out, long long rows, int c
   }
   dim3 grid((cols + 31) / 32, gy);
   colsum_bf16_kernel<<<grid, block, 0, ST(stream)>>>(static_cast<const bf16*>(x), out, rows, cols);
+  return LAUNCH_OK();
+}
+// out[i][c] += sum_r x[i][r][c] for n <= 4 bf16 matrices [rows][cols[i]] (cols[i] % 8 == 0, 16-byte aligned) in ONE launch;
+// the outputs are fp32 accumulators the caller has zeroed (they may be slices of one buffer cleared with one memset)
+extern "C" int ddpx_colsum_bf16_multi(int n, const void* const* x, float* const* out, long long rows, const int* cols,
+                                      void* stream) {
+  if (n < 1 || n > 4) return DDPX_ERR_ARG;
+  ColsumTable t{};
+  t.count = n;
+  int blocks = 0;
+  for (int i = 0; i < n; ++i) {
+    if (cols[i] % 8 || (reinterpret_cast<uintptr_t>(x[i]) & 15)) return DDPX_ERR_ALIGN;
+    t.x[i] = static_cast<const bf16*>(x[i]); t.out[i] = out[i]; t.cols[i] = cols[i];
+    t.first_block[i] = blocks;
+    blocks += (cols[i] / 8 + 31) / 32;
+  }
+  t.first_block[n] = blocks;
+  int gy = static_cast<int>(rows / 128);
+  if (gy < 1) gy = 1;
+  if (gy > 64) gy = 64;
+  colsum_bf16_multi_kernel<<<dim3(blocks, gy), dim3(32, 8), 0, ST(stream)>>>(t, rows);
   return LAUNCH_OK();
 }
 extern "C" int ddpx_dropout(const void* x, void* y, long long n, float p, unsigned long long seed, int is_bf16, void* stream) {

@@ -227,6 +227,8 @@ int ddpx_relu_bwd_bf16(const void* y, const void* dy, void* dx, long long n, voi
 int ddpx_add(const void* a, const void* b, void* out, long long n, int is_bf16, void* stream);
 int ddpx_cast_scale(const void* src, void* dst, long long n, float scale, int kind, void* stream);
 int ddpx_colsum_bf16(const void* x, float* out, long long rows, int cols, void* stream);
+/* out[i][c] += column sums of n <= 4 bf16 matrices [rows][cols[i]] in one launch; the fp32 outputs are NOT zeroed here */
+int ddpx_colsum_bf16_multi(int n, const void* const* x, float* const* out, long long rows, const int* cols, void* stream);
 int ddpx_dropout(const void* x, void* y, long long n, float p, unsigned long long seed, int is_bf16, void* stream);
 int ddpx_embedding_fwd(const long long* idx, const void* wte, const void* wpe, void* out, long long BT, int T, int C,
                        int is_bf16, void* stream);
