@@ -4,6 +4,7 @@
 #include <cuda_runtime.h>
 #include <cuda_bf16.h>
 #include <stdint.h>
+#include <stdlib.h>
 #include "vec.cuh"
 #include "../../include/ddpx_kernels.h"
 
@@ -60,16 +61,18 @@ layernorm_fwd_kernel(const T* __restrict__ x, const T* __restrict__ gamma, const
 // the rows its warp visits (NV vectors per lane), then the block folds them through shared memory and issues one
 // atomic per column into the fp32 accumulators (pre-zeroed).
 template <typename T, int NV>
-__global__ void __launch_bounds__(256, (NV <= 4 ? 2 : 1))
+__global__ void __launch_bounds__(256, (NV <= 2 ? 2 : 1))
 layernorm_bwd_kernel(const T* __restrict__ x, const T* __restrict__ dy, const T* __restrict__ gamma,
                      const float* __restrict__ mean, const float* __restrict__ rstd, T* __restrict__ dx,
                      float* __restrict__ dgamma, float* __restrict__ dbeta, long long rows, int C,
                      float* __restrict__ partial, const T* __restrict__ dres) {
   constexpr int V = VecOf<T>::N;
-  // rows up to 2 vectors per lane (C <= 512 in bf16) stay in registers between the two passes over a row; wider rows
-  // are read again (from L1) for the second pass - registers go to the column sums instead, so that two blocks fit on
-  // an SM up to NV = 4 (the kernel is latency-bound: ncu showed 12 % occupancy and 24 us for 38 MB with one block)
-  constexpr bool kKeep = NV <= 2;
+  // A row is loaded ONCE, as raw 16-byte vectors issued back to back (predicated, no branches in between), and kept packed
+  // in registers for the second pass; the residual gradient's vectors are in flight during the first pass.  With a
+  // branch and a load-use pair per vector the NV loads of a pass were serialised - NV full memory round trips per pass,
+  // 27 us for a 2048 x 1600 call whose traffic is worth 4 us.  Rows wider than 8 vectors per lane (C > 2048 in bf16) would
+  // not fit the register file this way and take the vector-at-a-time path.
+  constexpr bool kBatch = NV <= 8;
   extern __shared__ float acc[];   // [2][C]
   const int lane = threadIdx.x & 31;
   const long long warp0 = (static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
@@ -80,56 +83,105 @@ layernorm_bwd_kernel(const T* __restrict__ x, const T* __restrict__ dy, const T*
   for (int j = 0; j < NV; ++j)
 #pragma unroll
     for (int k = 0; k < V; ++k) { ag[j][k] = 0.f; ab[j][k] = 0.f; }
+  const uint4 zero4 = make_uint4(0u, 0u, 0u, 0u);
   for (long long r = warp0; r < rows; r += nwarps) {
     const T* xr = x + r * C;
     const T* dr = dy + r * C;
     const float m = mean[r], rs = rstd[r];
     float s1 = 0.f, s2 = 0.f;
-    float kf[kKeep ? NV : 1][V], kd[kKeep ? NV : 1][V];      // x-hat and dy * gamma of this lane's columns
+    T* dxr = dx + r * C;
+    if constexpr (kBatch) {
+      uint4 rx[NV], rd[NV], rr[NV];
 #pragma unroll
-    for (int j = 0; j < NV; ++j) {
-      const int i = lane + j * 32;
-      if (i < nvec) {
+      for (int j = 0; j < NV; ++j) {
+        const int i = lane + j * 32;
+        const bool in = i < nvec;
+        rx[j] = in ? __ldg(reinterpret_cast<const uint4*>(xr + i * V)) : zero4;
+        rd[j] = in ? __ldg(reinterpret_cast<const uint4*>(dr + i * V)) : zero4;
+      }
+      if (dres != nullptr) {
+#pragma unroll
+        for (int j = 0; j < NV; ++j) {
+          const int i = lane + j * 32;
+          rr[j] = (i < nvec) ? __ldg(reinterpret_cast<const uint4*>(dres + r * C + i * V)) : zero4;
+        }
+      }
+#pragma unroll
+      for (int j = 0; j < NV; ++j) {
+        const int i = lane + j * 32;
         float f[V], d[V], g[V];
-        vload(xr + i * V, f); vload(dr + i * V, d); vload(gamma + i * V, g);
+        vunpack<T>(rx[j], f); vunpack<T>(rd[j], d);
+        vunpack<T>(i < nvec ? __ldg(reinterpret_cast<const uint4*>(gamma + i * V)) : zero4, g);
 #pragma unroll
-        for (int k = 0; k < V; ++k) {
+        for (int k = 0; k < V; ++k) {            // lanes past the row hold zeros: d = 0 keeps every sum unchanged
           const float xh = (f[k] - m) * rs;
           const float gd = d[k] * g[k];
           s1 += gd; s2 += gd * xh;
           ag[j][k] += d[k] * xh;
           ab[j][k] += d[k];
-          if constexpr (kKeep) { kf[j][k] = xh; kd[j][k] = gd; }
         }
       }
-    }
-    s1 = warp_sum_f(s1); s2 = warp_sum_f(s2);
-    const float a = s1 / C, b = s2 / C;
-    T* dxr = dx + r * C;
+      s1 = warp_sum_f(s1); s2 = warp_sum_f(s2);
+      const float a = s1 / C, b = s2 / C;
 #pragma unroll
-    for (int j = 0; j < NV; ++j) {
-      const int i = lane + j * 32;
-      if (i < nvec) {
-        float f[V];
-        if constexpr (kKeep) {
+      for (int j = 0; j < NV; ++j) {
+        const int i = lane + j * 32;
+        if (i < nvec) {
+          float f[V], d[V], g[V];
+          vunpack<T>(rx[j], f); vunpack<T>(rd[j], d);
+          vload(gamma + i * V, g);               // L1 hit
 #pragma unroll
-          for (int k = 0; k < V; ++k) f[k] = rs * (kd[j][k] - a - kf[j][k] * b);
-        } else {
-          float d[V], g[V];
+          for (int k = 0; k < V; ++k) {
+            const float xh = (f[k] - m) * rs;
+            f[k] = rs * (d[k] * g[k] - a - xh * b);
+          }
+          if (dres != nullptr) {                  // the gradient arriving over the residual connection around this LayerNorm
+            float e[V];
+            vunpack<T>(rr[j], e);
+#pragma unroll
+            for (int k = 0; k < V; ++k) f[k] += e[k];
+          }
+          vstore(dxr + i * V, f);
+        }
+      }
+    } else {
+#pragma unroll
+      for (int j = 0; j < NV; ++j) {
+        const int i = lane + j * 32;
+        if (i < nvec) {
+          float f[V], d[V], g[V];
+          vload(xr + i * V, f); vload(dr + i * V, d); vload(gamma + i * V, g);
+#pragma unroll
+          for (int k = 0; k < V; ++k) {
+            const float xh = (f[k] - m) * rs;
+            const float gd = d[k] * g[k];
+            s1 += gd; s2 += gd * xh;
+            ag[j][k] += d[k] * xh;
+            ab[j][k] += d[k];
+          }
+        }
+      }
+      s1 = warp_sum_f(s1); s2 = warp_sum_f(s2);
+      const float a = s1 / C, b = s2 / C;
+#pragma unroll
+      for (int j = 0; j < NV; ++j) {
+        const int i = lane + j * 32;
+        if (i < nvec) {
+          float f[V], d[V], g[V];
           vload(xr + i * V, f); vload(dr + i * V, d); vload(gamma + i * V, g);
 #pragma unroll
           for (int k = 0; k < V; ++k) {
             const float xh = (f[k] - m) * rs;
             f[k] = rs * (d[k] * g[k] - a - xh * b);
           }
-        }
-        if (dres != nullptr) {          // the gradient arriving over the residual connection around this LayerNorm
-          float e[V];
-          vload(dres + r * C + i * V, e);
+          if (dres != nullptr) {
+            float e[V];
+            vload(dres + r * C + i * V, e);
 #pragma unroll
-          for (int k = 0; k < V; ++k) f[k] += e[k];
+            for (int k = 0; k < V; ++k) f[k] += e[k];
+          }
+          vstore(dxr + i * V, f);
         }
-        vstore(dxr + i * V, f);
       }
     }
   }
@@ -175,6 +227,101 @@ layernorm_bwd_kernel(const T* __restrict__ x, const T* __restrict__ dy, const T*
                  "f"(acc[c + 3]) : "memory");
     asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(dbeta + c), "f"(acc[C + c]), "f"(acc[C + c + 1]),
                  "f"(acc[C + c + 2]), "f"(acc[C + c + 3]) : "memory");
+  }
+}
+
+// ---- the same backward as two kernels with more parallelism (rows up to 8 vectors per lane): the column sums are what
+// force the fused kernel to keep 2 * NV * V accumulators per lane alive across rows and to run at eight warps per SM.
+// (1) dx alone: one row per warp at a time, nothing carried between rows, 16+ warps per SM.
+template <typename T, int NV>
+__global__ void __launch_bounds__(256, 2)
+layernorm_bwd_dx_kernel(const T* __restrict__ x, const T* __restrict__ dy, const T* __restrict__ gamma,
+                        const float* __restrict__ mean, const float* __restrict__ rstd, T* __restrict__ dx,
+                        long long rows, int C, const T* __restrict__ dres) {
+  constexpr int V = VecOf<T>::N;
+  const int lane = threadIdx.x & 31;
+  const long long warp0 = (static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
+  const long long nwarps = (static_cast<long long>(gridDim.x) * blockDim.x) >> 5;
+  const int nvec = C / V;
+  const uint4 zero4 = make_uint4(0u, 0u, 0u, 0u);
+  for (long long r = warp0; r < rows; r += nwarps) {
+    const T* xr = x + r * C;
+    const T* dr = dy + r * C;
+    const float m = mean[r], rs = rstd[r];
+    uint4 rx[NV], rd[NV], rg[NV], rr[NV];
+#pragma unroll
+    for (int j = 0; j < NV; ++j) {
+      const int i = lane + j * 32;
+      const bool in = i < nvec;
+      rx[j] = in ? __ldg(reinterpret_cast<const uint4*>(xr + i * V)) : zero4;
+      rd[j] = in ? __ldg(reinterpret_cast<const uint4*>(dr + i * V)) : zero4;
+      rg[j] = in ? __ldg(reinterpret_cast<const uint4*>(gamma + i * V)) : zero4;
+      rr[j] = (in && dres != nullptr) ? __ldg(reinterpret_cast<const uint4*>(dres + r * C + i * V)) : zero4;
+    }
+    float s1 = 0.f, s2 = 0.f;
+#pragma unroll
+    for (int j = 0; j < NV; ++j) {
+      float f[V], d[V], g[V];
+      vunpack<T>(rx[j], f); vunpack<T>(rd[j], d); vunpack<T>(rg[j], g);
+#pragma unroll
+      for (int k = 0; k < V; ++k) {
+        const float gd = d[k] * g[k];
+        s1 += gd; s2 += gd * ((f[k] - m) * rs);
+      }
+    }
+    s1 = warp_sum_f(s1); s2 = warp_sum_f(s2);
+    const float a = s1 / C, b = s2 / C;
+    T* dxr = dx + r * C;
+#pragma unroll
+    for (int j = 0; j < NV; ++j) {
+      const int i = lane + j * 32;
+      if (i < nvec) {
+        float f[V], d[V], g[V], e[V];
+        vunpack<T>(rx[j], f); vunpack<T>(rd[j], d); vunpack<T>(rg[j], g); vunpack<T>(rr[j], e);
+#pragma unroll
+        for (int k = 0; k < V; ++k) f[k] = rs * (d[k] * g[k] - a - ((f[k] - m) * rs) * b) + e[k];
+        vstore(dxr + i * V, f);
+      }
+    }
+  }
+}
+// (2) partial[by][c] = sum over the block's rows of dy * x-hat, partial[by][C + c] = sum of dy: block = 32 column vectors x
+// 8 row lanes, rows split over gridDim.y; ln_partial_reduce_kernel adds the gridDim.y rows up
+template <typename T>
+__global__ void __launch_bounds__(256)
+layernorm_bwd_colsum_kernel(const T* __restrict__ x, const T* __restrict__ dy, const float* __restrict__ mean,
+                            const float* __restrict__ rstd, float* __restrict__ partial, long long rows, int C) {
+  constexpr int V = VecOf<T>::N;
+  __shared__ float shg[8][32][V + 1], shb[8][32][V + 1];
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  const int cv = blockIdx.x * 32 + tx;               // column vector
+  float sg[V], sb[V];
+#pragma unroll
+  for (int k = 0; k < V; ++k) { sg[k] = 0.f; sb[k] = 0.f; }
+  if (cv * V < C) {
+#pragma unroll 4
+    for (long long r = static_cast<long long>(blockIdx.y) * 8 + ty; r < rows; r += static_cast<long long>(gridDim.y) * 8) {
+      float f[V], d[V];
+      vload(x + r * C + cv * V, f); vload(dy + r * C + cv * V, d);
+      const float m = mean[r], rs = rstd[r];
+#pragma unroll
+      for (int k = 0; k < V; ++k) { sg[k] += d[k] * ((f[k] - m) * rs); sb[k] += d[k]; }
+    }
+  }
+#pragma unroll
+  for (int k = 0; k < V; ++k) { shg[ty][tx][k] = sg[k]; shb[ty][tx][k] = sb[k]; }
+  __syncthreads();
+  // 256 threads fold the 8 row lanes of the block's 32 * V columns
+  for (int t = threadIdx.x; t < 32 * V; t += 256) {
+    const int g = t / V, k = t - g * V;
+    const int c = (blockIdx.x * 32 + g) * V + k;
+    if (c < C) {
+      float a = 0.f, b = 0.f;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) { a += shg[j][g][k]; b += shb[j][g][k]; }
+      float* row = partial + static_cast<size_t>(blockIdx.y) * 2 * C;
+      row[c] = a; row[C + c] = b;
+    }
   }
 }
 
@@ -311,13 +458,15 @@ __global__ void colsum_bf16_multi_kernel(const ColsumTable t, long long rows) {
   float s[8];
 #pragma unroll
   for (int k = 0; k < 8; ++k) s[k] = 0.f;
-  if (cg * 8 < cols)
+  if (cg * 8 < cols) {
+#pragma unroll 8
     for (long long r = static_cast<long long>(blockIdx.y) * 8 + threadIdx.y; r < rows; r += static_cast<long long>(gridDim.y) * 8) {
       float f[8];
       vload(x + r * cols + cg * 8, f);
 #pragma unroll
       for (int k = 0; k < 8; ++k) s[k] += f[k];
     }
+  }
 #pragma unroll
   for (int k = 0; k < 8; ++k) sh[threadIdx.y][threadIdx.x][k] = s[k];
   __syncthreads();
@@ -328,7 +477,8 @@ __global__ void colsum_bf16_multi_kernel(const ColsumTable t, long long rows) {
     float a = 0.f;
 #pragma unroll
     for (int j = 0; j < 8; ++j) a += sh[j][g][k];
-    atomicAdd(t.out[m] + c, a);
+    // explicit global reduction: through the table's runtime-indexed pointer a plain atomicAdd compiles to the generic form
+    asm volatile("red.global.add.f32 [%0], %1;" ::"l"(t.out[m] + c), "f"(a) : "memory");
   }
 }
 // inverted dropout with a counter-based hash RNG: keep iff hash(seed, i) >= p * 2^32
@@ -341,6 +491,18 @@ __global__ void dropout_kernel(const T* __restrict__ x, T* __restrict__ y, long 
   const uint32_t thr = static_cast<uint32_t>(fminf(p, 0.999999f) * 4294967296.0f);
   for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < n; i += static_cast<long long>(gridDim.x) * blockDim.x)
     stf(y + i, hash32(seed * 0x9E3779B97F4A7C15ULL + static_cast<uint64_t>(i)) >= thr ? ldf(x + i) * scale : 0.f);
+}
+
+template <typename T>
+int launch_ln_bwd_dx(int nv, int grid, cudaStream_t s, const T* x, const T* dy, const T* g, const float* mean, const float* rstd,
+                     T* dx, long long rows, int C, const T* dres) {
+#define LN_CASE(NVV) case NVV: layernorm_bwd_dx_kernel<T, NVV><<<grid, 256, 0, s>>>(x, dy, g, mean, rstd, dx, rows, C, dres); break;
+  switch (nv) {
+    LN_CASE(1) LN_CASE(2) LN_CASE(3) LN_CASE(4) LN_CASE(5) LN_CASE(6) LN_CASE(7) LN_CASE(8)
+    default: return DDPX_ERR_SHAPE;
+  }
+#undef LN_CASE
+  return DDPX_OK;
 }
 
 template <typename T>
@@ -381,7 +543,7 @@ extern "C" int ddpx_layernorm_fwd(const void* x, const void* gamma, const void* 
 // dgamma / dbeta: fp32 [C].  Without scratch they are accumulators that must be zero on entry (every block reduces into
 // them); with `scratch` (fp32, at least ddpx_layernorm_bwd_scratch_floats(rows, C) elements) the blocks store partial sums
 // there, a second small kernel adds them up and OVERWRITES dgamma / dbeta - no zeroing needed and ~25 us less per call.
-static int ln_bwd_grid(long long rows, int nv) { return cap_blocks((rows + 7) / 8, nv <= 4 ? 296 : 148); }
+static int ln_bwd_grid(long long rows, int nv) { return cap_blocks((rows + 7) / 8, nv <= 2 ? 296 : 148); }
 
 extern "C" long long ddpx_layernorm_bwd_scratch_floats(long long rows, int C) {
   return static_cast<long long>(ln_bwd_grid(rows, 1)) * 2 * C;          // the larger of the two grids
@@ -399,6 +561,41 @@ extern "C" int ddpx_layernorm_bwd_res(const void* x, const void* dy, const void*
   if (nv > 16 || smem > 48 * 1024) return DDPX_ERR_SHAPE;
   if ((reinterpret_cast<uintptr_t>(dgamma) | reinterpret_cast<uintptr_t>(dbeta) | reinterpret_cast<uintptr_t>(scratch)) & 15)
     return DDPX_ERR_ALIGN;
+  static int split = -1;            // DDPX_LN_SPLIT=0: the single fused kernel also when scratch is given (A/B timing)
+  if (split < 0) { const char* e = getenv("DDPX_LN_SPLIT"); split = (e && e[0] == '0') ? 0 : 1; }
+  // worth it when the fused kernel's warps would see only a few rows each (their 2 * NV * V accumulators are set up and
+  // folded per warp whatever the row count): GPT-2 XL's 2048-row calls 18.9 -> ~12 us, 144.4 instead of 146.6 ms per step;
+  // at 8192 rows (seven rows per warp) the fused kernel is as fast
+  if (scratch != nullptr && nv <= 8 && split && rows < 148 * 8 * 4) {
+    // two kernels: dx with one row per warp and nothing carried between rows (high occupancy), then the column sums as a
+    // tiled reduction over rows; the scratch rows are those of the second kernel's gridDim.y (<= 64 <= the documented size)
+    const int grid_dx = cap_blocks((rows + 7) / 8, 148 * 8);
+    int rc2;
+    if (is_bf16)
+      rc2 = launch_ln_bwd_dx<bf16>(nv, grid_dx, ST(stream), static_cast<const bf16*>(x), static_cast<const bf16*>(dy),
+                                   static_cast<const bf16*>(gamma), mean, rstd, static_cast<bf16*>(dx), rows, C,
+                                   static_cast<const bf16*>(dres));
+    else
+      rc2 = launch_ln_bwd_dx<float>(nv, grid_dx, ST(stream), static_cast<const float*>(x), static_cast<const float*>(dy),
+                                    static_cast<const float*>(gamma), mean, rstd, static_cast<float*>(dx), rows, C,
+                                    static_cast<const float*>(dres));
+    if (rc2 != DDPX_OK) return rc2;
+    if (cudaGetLastError() != cudaSuccess) return DDPX_ERR_LAUNCH;
+    int gy = static_cast<int>((rows + 63) / 64);       // >= 8 rows per thread
+    if (gy > 64) gy = 64;
+    if (gy > ln_bwd_grid(rows, 1)) gy = ln_bwd_grid(rows, 1);      // never more rows than the scratch is sized for
+    if (gy < 1) gy = 1;
+    const dim3 grid_cs((C / V + 31) / 32, gy);
+    if (is_bf16)
+      layernorm_bwd_colsum_kernel<bf16><<<grid_cs, 256, 0, ST(stream)>>>(static_cast<const bf16*>(x), static_cast<const bf16*>(dy),
+                                                                         mean, rstd, scratch, rows, C);
+    else
+      layernorm_bwd_colsum_kernel<float><<<grid_cs, 256, 0, ST(stream)>>>(static_cast<const float*>(x), static_cast<const float*>(dy),
+                                                                          mean, rstd, scratch, rows, C);
+    if (cudaGetLastError() != cudaSuccess) return DDPX_ERR_LAUNCH;
+    ln_partial_reduce_kernel<<<(2 * C + 31) / 32, 256, 0, ST(stream)>>>(scratch, gy, 2 * C, C, dgamma, dbeta);
+    return cudaGetLastError() == cudaSuccess ? DDPX_OK : DDPX_ERR_LAUNCH;
+  }
   // every warp carries register accumulators across its rows; one or two blocks per SM
   const int grid = ln_bwd_grid(rows, nv);
   int rc;
