@@ -112,7 +112,7 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
 
   if (warp == 0) {
     // ================================================ TMA producer ================================================
-    if (lane == 0) {
+    if (elect_one()) {
       // the rows of the n-th item of this CTA (one buffer: refilled as soon as the compute warps have read it)
       auto load_rows = [&](int idx, int n) {
         int qt, b, h;
@@ -147,7 +147,7 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
     }
   } else if (warp == 1) {
     // ================================================ MMA issuer ==================================================
-    if (lane == 0) {
+    if (elect_one()) {
       const uint32_t idesc_s = make_idesc(true, false, false, kTile, kSub);     // [128 q][64 kv]
       const uint32_t idesc_dq = make_idesc(true, false, true, kTile, kHD);      // [128 q][64], K tile read MN-major
       int g = 0;                 // key tiles consumed before this item
@@ -360,7 +360,7 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_cons
 
   if (warp == 0) {
     // ================================================ TMA producer ================================================
-    if (lane == 0) {
+    if (elect_one()) {
       auto load_rows = [&](int idx, int n) {
         int kt, b, h;
         decode(idx, kt, b, h);
@@ -393,7 +393,7 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_cons
     }
   } else if (warp == 1) {
     // ================================================ MMA issuer ==================================================
-    if (lane == 0) {
+    if (elect_one()) {
       const uint32_t idesc_s = make_idesc(true, false, false, kTile, kSub);     // [128 kv][64 q]
       const uint32_t idesc_acc = make_idesc(true, false, true, kTile, kHD);     // [128 kv][64], Q / dO tiles read MN-major
       int g = 0;

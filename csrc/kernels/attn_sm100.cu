@@ -83,7 +83,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const AttnParams p) {
 
   if (warp == 0) {
     // ================================================ TMA producer ================================================
-    if (lane == 0) {
+    if (elect_one()) {
       auto load_q = [&](int idx, int n) {
         int qt, b, h;
         decode(idx, qt, b, h);
@@ -116,7 +116,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const AttnParams p) {
     }
   } else if (warp == 1) {
     // ================================================ MMA issuer ==================================================
-    if (lane == 0) {
+    if (elect_one()) {
       const uint32_t idesc_qk = make_idesc(true, false, false, kTile, kTile);   // S[128 q][128 kv]
       const uint32_t idesc_pv = make_idesc(true, false, true, kTile, kHD);      // O[128 q][64], V is MN-major
       int g = 0;                 // key blocks before this item

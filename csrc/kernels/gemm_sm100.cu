@@ -219,7 +219,8 @@ tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
   };
   if (warp == 0) {
     // ======================================= TMA producer =======================================
-    if (lane == 0) {
+    // (entered through elect.sync, not `lane == 0`: see elect_one() in sm100_ptx.cuh)
+    if (elect_one()) {
       int stage = 0;
       uint32_t phase = 0;
       for (int item = first_item; item < num_items; item += item_stride) {
@@ -325,7 +326,7 @@ tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
     }
   } else if (warp == 1) {
     // ======================================= MMA issuer =========================================
-    if (lane == 0 && leader) {
+    if (leader && elect_one()) {
       const bool a_mn = (kMode == MODE_WGRAD) ? true : (kMode == MODE_FPROP ? false : (p.a_mn != 0));
       const bool b_mn = (kMode == MODE_WGRAD) ? true : (kMode == MODE_FPROP ? false : (p.b_mn != 0));
       const uint32_t idesc = make_idesc(kBF16, a_mn, b_mn, kTileM, static_cast<uint32_t>(p.block_n));

@@ -331,9 +331,14 @@ def layernorm_bwd_scratch_floats(rows, C) -> int:
     return min(296, max(1, (rows + 7) // 8)) * 2 * C
 
 
-def layernorm_bwd(x, dy, gamma, mean, rstd, dx, dgamma, dbeta, rows, C, scratch=None):
-    """Without scratch dgamma / dbeta are zeroed accumulators; with it they are overwritten."""
-    if scratch is None:
+def layernorm_bwd(x, dy, gamma, mean, rstd, dx, dgamma, dbeta, rows, C, scratch=None, dres=None):
+    """Without scratch dgamma / dbeta are zeroed accumulators; with it they are overwritten.  dres (needs scratch): the
+    gradient of the residual branch around the LayerNorm, added to dx."""
+    if dres is not None:
+        assert scratch is not None and scratch.numel() >= layernorm_bwd_scratch_floats(rows, C)
+        _call("ddpx_layernorm_bwd_res", _P(x), _P(dy), _P(gamma), _P(mean), _P(rstd), _P(dx), _P(dgamma), _P(dbeta),
+              c_longlong(rows), c_int(C), c_int(_bf(x)), _P(scratch), _P(dres), _st())
+    elif scratch is None:
         _call("ddpx_layernorm_bwd", _P(x), _P(dy), _P(gamma), _P(mean), _P(rstd), _P(dx), _P(dgamma), _P(dbeta),
               c_longlong(rows), c_int(C), c_int(_bf(x)), _st())
     else:

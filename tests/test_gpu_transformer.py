@@ -42,6 +42,26 @@ def test_layernorm(dtype, tol, rows, C):
     assert rel_l2(w.grad, wr.grad) < tol and rel_l2(b.grad, br.grad) < tol
 
 
+@pytest.mark.parametrize("rows,C", [(2048, 1600), (8192, 768), (300, 512)])
+def test_layernorm_backward_with_residual_gradient(rows, C):
+    """ddpx_layernorm_bwd_res at the shapes that take the two-kernel form (few rows per warp) and the fused form: dx with
+    the residual branch's gradient added, dgamma / dbeta overwritten (no zeroing), against float64 torch."""
+    torch.manual_seed(5)
+    x = torch.randn(rows, C, device="cuda").bfloat16()
+    w = (torch.rand(C, device="cuda") + 0.5).bfloat16(); b = torch.randn(C, device="cuda").bfloat16()
+    dy = torch.randn(rows, C, device="cuda").bfloat16(); dres = torch.randn(rows, C, device="cuda").bfloat16()
+    y = torch.empty_like(x); stats = torch.empty(2, rows, device="cuda")
+    native.layernorm_fwd(x, w, b, y, stats[0], stats[1], rows, C, 1e-5)
+    dx = torch.empty_like(x)
+    dgb = torch.full((2, C), 7.0, device="cuda")                     # garbage: must be overwritten
+    scratch = torch.empty(native.layernorm_bwd_scratch_floats(rows, C), device="cuda")
+    native.layernorm_bwd(x, dy, w, stats[0], stats[1], dx, dgb[0], dgb[1], rows, C, scratch, dres)
+    xr, wr, br = (t.double().requires_grad_() for t in (x, w, b))
+    F.layer_norm(xr, (C,), wr, br, 1e-5).backward(dy.double())
+    assert rel_l2(dx, xr.grad + dres.double()) < 1e-2
+    assert rel_l2(dgb[0], wr.grad) < 5e-3 and rel_l2(dgb[1], br.grad) < 5e-3
+
+
 @pytest.mark.parametrize("dtype,tol", [(torch.float32, 5e-3), (torch.bfloat16, 2e-2)])
 def test_linear_gelu(dtype, tol):
     torch.manual_seed(1)
