@@ -232,7 +232,8 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
         lse2 = valid ? sLse[r] : 0.f;
         __syncwarp();
         if (lane == 0) mbar_arrive(rows_empty);
-        if (half == 1) p.delta[(static_cast<long long>(b) * p.H + h) * p.Tp + q] = delta;      // q < Tp always
+        // (published pre-multiplied by the softmax scale: the dkv kernel only ever uses delta * scale)
+        if (half == 1) p.delta[(static_cast<long long>(b) * p.H + h) * p.Tp + q] = delta * p.scale;      // q < Tp always
         tmem_st_32x32(tmem + lane_base + (half == 0 ? kColQ : kColDO), rowv);
         tmem_st_wait();
         tc_fence_before();
@@ -250,18 +251,28 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
         tmem_ld_32x32(tS + buf, sv);
         tmem_ld_32x32(tDP + buf, dv);
         tmem_ld_wait();
+        // dS = P * (dP - delta) * scale = P * fma(dP, scale, -delta * scale).  The diagonal tile's masking is its own code
+        // path (warp-uniform branch): folded into one loop it cost a compare and a select per element on every tile.
         uint32_t pk[16];
+        const float nds = -delta * p.scale;
+        if (!diag) {
 #pragma unroll
-        for (int i = 0; i < 32; i += 2) {
-          float p0 = ex2(fmaf(__uint_as_float(sv[i]), sl2, -lse2));
-          float p1 = ex2(fmaf(__uint_as_float(sv[i + 1]), sl2, -lse2));
-          float d0 = p0 * (__uint_as_float(dv[i]) - delta) * p.scale;
-          float d1 = p1 * (__uint_as_float(dv[i + 1]) - delta) * p.scale;
-          if (diag) {
+          for (int i = 0; i < 32; i += 2) {
+            const float p0 = ex2(fmaf(__uint_as_float(sv[i]), sl2, -lse2));
+            const float p1 = ex2(fmaf(__uint_as_float(sv[i + 1]), sl2, -lse2));
+            pk[i >> 1] = pack_bf16(p0 * fmaf(__uint_as_float(dv[i]), p.scale, nds), p1 * fmaf(__uint_as_float(dv[i + 1]), p.scale, nds));
+          }
+        } else {
+#pragma unroll
+          for (int i = 0; i < 32; i += 2) {
+            const float p0 = ex2(fmaf(__uint_as_float(sv[i]), sl2, -lse2));
+            const float p1 = ex2(fmaf(__uint_as_float(sv[i + 1]), sl2, -lse2));
+            float d0 = p0 * fmaf(__uint_as_float(dv[i]), p.scale, nds);
+            float d1 = p1 * fmaf(__uint_as_float(dv[i + 1]), p.scale, nds);
             if (col0 + i > r) d0 = 0.f;
             if (col0 + i + 1 > r) d1 = 0.f;
+            pk[i >> 1] = pack_bf16(d0, d1);
           }
-          pk[i >> 1] = pack_bf16(d0, d1);
         }
         tmem_st_32x16(tDP + buf, pk);           // overlays dP columns this warp has already consumed
         tmem_st_wait();
@@ -495,24 +506,41 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_cons
         tmem_ld_32x32(tS + buf, sv);
         tmem_ld_32x32(tDP + buf, dv);
         tmem_ld_wait();
+        // sDelta holds delta * scale (the dq kernel publishes it that way): dS^T = P^T * fma(dP^T, scale, -delta * scale).
+        // Masked tiles (the diagonal one, and the last one of a sequence that is not a multiple of 128) take their own path.
         uint32_t pk[16], dk[16];
+        if (!masked) {
 #pragma unroll
-        for (int gq = 0; gq < 8; ++gq) {
-          const float4 L = lse4[gq], D = del4[gq];
-          const float ls[4] = {L.x, L.y, L.z, L.w}, ds[4] = {D.x, D.y, D.z, D.w};
-          float pv[4], dsv[4];
+          for (int gq = 0; gq < 8; ++gq) {
+            const float4 L = lse4[gq], D = del4[gq];
+            const float ls[4] = {L.x, L.y, L.z, L.w}, ds[4] = {D.x, D.y, D.z, D.w};
+            float pv[4], dsv[4];
 #pragma unroll
-          for (int e = 0; e < 4; ++e) {
-            const int x = gq * 4 + e;
-            pv[e] = ex2(fmaf(__uint_as_float(sv[x]), sl2, -ls[e]));
-            dsv[e] = pv[e] * (__uint_as_float(dv[x]) - ds[e]) * p.scale;
-            if (masked) {
+            for (int e = 0; e < 4; ++e) {
+              const int x = gq * 4 + e;
+              pv[e] = ex2(fmaf(__uint_as_float(sv[x]), sl2, -ls[e]));
+              dsv[e] = pv[e] * fmaf(__uint_as_float(dv[x]), p.scale, -ds[e]);
+            }
+            pk[gq * 2] = pack_bf16(pv[0], pv[1]); pk[gq * 2 + 1] = pack_bf16(pv[2], pv[3]);
+            dk[gq * 2] = pack_bf16(dsv[0], dsv[1]); dk[gq * 2 + 1] = pack_bf16(dsv[2], dsv[3]);
+          }
+        } else {
+#pragma unroll
+          for (int gq = 0; gq < 8; ++gq) {
+            const float4 L = lse4[gq], D = del4[gq];
+            const float ls[4] = {L.x, L.y, L.z, L.w}, ds[4] = {D.x, D.y, D.z, D.w};
+            float pv[4], dsv[4];
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+              const int x = gq * 4 + e;
+              pv[e] = ex2(fmaf(__uint_as_float(sv[x]), sl2, -ls[e]));
+              dsv[e] = pv[e] * fmaf(__uint_as_float(dv[x]), p.scale, -ds[e]);
               const int col = col0 + x;                               // query row inside the tile
               if ((it == 0 && col < r) || i * kTile + col >= p.T) { pv[e] = 0.f; dsv[e] = 0.f; }
             }
+            pk[gq * 2] = pack_bf16(pv[0], pv[1]); pk[gq * 2 + 1] = pack_bf16(pv[2], pv[3]);
+            dk[gq * 2] = pack_bf16(dsv[0], dsv[1]); dk[gq * 2 + 1] = pack_bf16(dsv[2], dsv[3]);
           }
-          pk[gq * 2] = pack_bf16(pv[0], pv[1]); pk[gq * 2 + 1] = pack_bf16(pv[2], pv[3]);
-          dk[gq * 2] = pack_bf16(dsv[0], dsv[1]); dk[gq * 2 + 1] = pack_bf16(dsv[2], dsv[3]);
         }
         tmem_st_32x16(tS + buf, pk);        // P^T over the S^T columns this warp has consumed
         tmem_st_32x16(tDP + buf, dk);       // dS^T over the dP^T columns

@@ -20,7 +20,7 @@ struct AttnParams {
   float* lse2;                     // [B, H, Tp] row log-sum-exp in base 2 (of the scaled scores)
   const __nv_bfloat16* qkv;
   const __nv_bfloat16* dout;       // backward
-  float* delta;                    // [B, H, Tp] rowsum(dO * O): written by the dq kernel, read by the dkv kernel
+  float* delta;                    // [B, H, Tp] rowsum(dO * O) * scale: written by the dq kernel, read by the dkv kernel
   const __nv_bfloat16* o;          // backward: the forward output
   __nv_bfloat16* dqkv;             // [B, T, 3C]
 };

@@ -237,16 +237,24 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const AttnParams p) {
           tmem_ld_wait();
           if (c < 3) tmem_ld_32x32(tS + (c + 1) * 32, (c & 1) ? va : vb);
           uint32_t pk[16];
+          if (!diag) {          // the diagonal block's masking is its own code path: no compare / select on the other blocks
 #pragma unroll
-          for (int i = 0; i < 32; i += 2) {
-            float p0 = ex2(fmaf(__uint_as_float(v[i]), sl2, -moff));
-            float p1 = ex2(fmaf(__uint_as_float(v[i + 1]), sl2, -moff));
-            if (diag) {
+            for (int i = 0; i < 32; i += 2) {
+              const float p0 = ex2(fmaf(__uint_as_float(v[i]), sl2, -moff));
+              const float p1 = ex2(fmaf(__uint_as_float(v[i + 1]), sl2, -moff));
+              l0 += p0; l1 += p1;
+              pk[i >> 1] = pack_bf16(p0, p1);
+            }
+          } else {
+#pragma unroll
+            for (int i = 0; i < 32; i += 2) {
+              float p0 = ex2(fmaf(__uint_as_float(v[i]), sl2, -moff));
+              float p1 = ex2(fmaf(__uint_as_float(v[i + 1]), sl2, -moff));
               if (c * 32 + i > r) p0 = 0.f;
               if (c * 32 + i + 1 > r) p1 = 0.f;
+              l0 += p0; l1 += p1;
+              pk[i >> 1] = pack_bf16(p0, p1);
             }
-            l0 += p0; l1 += p1;
-            pk[i >> 1] = pack_bf16(p0, p1);
           }
           tmem_st_32x16(tP + c * 16, pk);
         }
