@@ -28,8 +28,14 @@ struct CastTable { const float* src[8]; bf16* dst[8]; int n[8]; int count; };
 __global__ void cast_multi_kernel(const CastTable t) {
   const int seg = blockIdx.y;
   if (seg >= t.count) return;
-  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < t.n[seg]; i += gridDim.x * blockDim.x)
-    t.dst[seg][i] = __float2bfloat16(t.src[seg][i]);
+  // compile-time indices only: a runtime index into the by-value table would make the compiler copy it to local memory
+  const float* src = t.src[0];
+  bf16* dst = t.dst[0];
+  int n = t.n[0];
+#pragma unroll
+  for (int i = 1; i < 8; ++i)
+    if (seg == i) { src = t.src[i]; dst = t.dst[i]; n = t.n[i]; }
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) dst[i] = __float2bfloat16(src[i]);
 }
 
 // DDPX_BLOCK_FUSE: bit mask of the elementwise passes folded into GEMM epilogues / LayerNorm backward (for A/B timing):

@@ -449,11 +449,14 @@ __global__ void colsum_bf16_vec_kernel(const bf16* __restrict__ x, float* __rest
 struct ColsumTable { const bf16* x[4]; float* out[4]; int cols[4]; int first_block[5]; int count; };
 __global__ void colsum_bf16_multi_kernel(const ColsumTable t, long long rows) {
   __shared__ float sh[8][32][9];
-  int m = 0;
-  while (m + 1 < t.count && static_cast<int>(blockIdx.x) >= t.first_block[m + 1]) ++m;
-  const bf16* __restrict__ x = t.x[m];
-  const int cols = t.cols[m];
-  const int bx = static_cast<int>(blockIdx.x) - t.first_block[m];
+  // (compile-time indices only: a runtime index into the by-value table would make the compiler copy it to local memory)
+  const bf16* __restrict__ x = t.x[0];
+  float* out = t.out[0];
+  int cols = t.cols[0], first = 0;
+#pragma unroll
+  for (int i = 1; i < 4; ++i)
+    if (i < t.count && static_cast<int>(blockIdx.x) >= t.first_block[i]) { x = t.x[i]; out = t.out[i]; cols = t.cols[i]; first = t.first_block[i]; }
+  const int bx = static_cast<int>(blockIdx.x) - first;
   const int cg = bx * 32 + threadIdx.x;              // column group (8 columns)
   float s[8];
 #pragma unroll
@@ -478,7 +481,7 @@ __global__ void colsum_bf16_multi_kernel(const ColsumTable t, long long rows) {
 #pragma unroll
     for (int j = 0; j < 8; ++j) a += sh[j][g][k];
     // explicit global reduction: through the table's runtime-indexed pointer a plain atomicAdd compiles to the generic form
-    asm volatile("red.global.add.f32 [%0], %1;" ::"l"(t.out[m] + c), "f"(a) : "memory");
+    asm volatile("red.global.add.f32 [%0], %1;" ::"l"(out + c), "f"(a) : "memory");
   }
 }
 // inverted dropout with a counter-based hash RNG: keep iff hash(seed, i) >= p * 2^32
