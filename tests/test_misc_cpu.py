@@ -134,3 +134,31 @@ def test_datautils_toy_dataset():
     ds = MyTrainDataset(2048)
     x, y = ds[5]
     assert len(ds) == 2048 and x.shape == (20,) and y.shape == (1,)
+
+
+def test_algorithm_table_is_generated_from_sweep_rows(tmp_path):
+    """bench/allreduce_sweep.emit_table: one-shot up to the largest size where it is not slower than two-shot (all smaller
+    sizes agreeing), NVLS from the smallest size above which it beats two-shot by 3 % everywhere; other world sizes' entries
+    are kept; and parallel/p2p.py reads the thresholds it wrote."""
+    import importlib.util
+    import json
+    spec = importlib.util.spec_from_file_location("allreduce_sweep", REPO / "bench" / "allreduce_sweep.py")
+    sweep = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(sweep)
+    rows = []
+    for size, one, two, nv in [(1024, 10.0, 11.0, 11.5), (4096, 11.0, 11.1, 11.0), (16384, 14.0, 12.0, 11.9),
+                               (1 << 20, 40.0, 30.0, 29.5), (1 << 24, 200.0, 100.0, 90.0), (1 << 26, None, 400.0, 350.0)]:
+        if one is not None:
+            rows.append({"impl": "p2p_oneshot+sgd", "bytes": size, "us": one})
+        rows.append({"impl": "p2p_twoshot+sgd", "bytes": size, "us": two})
+        rows.append({"impl": "p2p_nvls+sgd", "bytes": size, "us": nv})
+    path = tmp_path / "table.json"
+    path.write_text(json.dumps({"2": {"oneshot_max_bytes": 1 << 20, "nvls_min_bytes": None}}))
+    entry = sweep.emit_table(rows, 8, str(path))
+    assert entry == {"oneshot_max_bytes": 4096, "nvls_min_bytes": 1 << 24}      # 1 MB: NVLS only 1.7 % ahead -> not taken
+    table = json.loads(path.read_text())
+    assert table["2"]["oneshot_max_bytes"] == 1 << 20 and table["8"] == entry
+    from distributed_data_parallel_experiment_b200.parallel import p2p
+    shipped = json.loads((REPO / "distributed_data_parallel_experiment_b200" / "parallel" / "algo_table.json").read_text())
+    assert p2p.oneshot_max_bytes(8) == shipped["8"]["oneshot_max_bytes"]
+    assert p2p.nvls_min_bytes(8) == shipped["8"]["nvls_min_bytes"]
