@@ -432,15 +432,19 @@ def attn_error_word() -> int:
 
 # ------------------------------------------------------------------------------------------------ transformer block
 def gpt2_block_fwd(x, params, acts, stats, tmp, out, B, T, C, H, eps):
-    """One GPT-2 block forward in one call (10 launches).  params / acts: lists of device pointers (ints)."""
+    """One GPT-2 block forward in one call: 7 kernels with the default DDPX_BLOCK_FUSE (two LayerNorms, four GEMMs with the
+    residual adds / GELU in their epilogues, fused attention).  params / acts: lists of device pointers (ints)."""
     _call("ddpx_gpt2_block_fwd", _P(x), (c_void_p * 12)(*params), (c_void_p * 7)(*acts), _P(stats), _P(tmp), _P(out),
-          c_int(B), c_int(T), c_int(C), c_int(H), c_float(eps), _st(), launches=10)
+          c_int(B), c_int(T), c_int(C), c_int(H), c_float(eps), _st(), launches=7)
 
 
 def gpt2_block_bwd(x, dout, params, acts, stats, grads, dx, wsb, ws32, cnt, B, T, C, H):
+    """Backward of the block in one call: eight GEMMs, two attention kernels, two LayerNorm backwards (two kernels each, three
+    in the few-rows form), one column-sum and one cast launch."""
+    ln = 3 if B * T < 148 * 8 * 4 else 2
     _call("ddpx_gpt2_block_bwd", _P(x), _P(dout), (c_void_p * 12)(*params), (c_void_p * 7)(*acts), _P(stats),
           (c_void_p * 12)(*grads), _P(dx), _P(wsb), _P(ws32), _P(cnt), c_int(B), c_int(T), c_int(C), c_int(H), _st(),
-          launches=24)
+          launches=12 + 2 * ln)
 
 
 def gemm_fused(A, B, D, M, N, K, lda, ldb, ldd, a_mn=0, b_mn=0, bias=None, act=0, aux=None, aux_op=0, out2=None):
