@@ -337,14 +337,14 @@ def layernorm_bwd(x, dy, gamma, mean, rstd, dx, dgamma, dbeta, rows, C, scratch=
     if dres is not None:
         assert scratch is not None and scratch.numel() >= layernorm_bwd_scratch_floats(rows, C)
         _call("ddpx_layernorm_bwd_res", _P(x), _P(dy), _P(gamma), _P(mean), _P(rstd), _P(dx), _P(dgamma), _P(dbeta),
-              c_longlong(rows), c_int(C), c_int(_bf(x)), _P(scratch), _P(dres), _st())
+              c_longlong(rows), c_int(C), c_int(_bf(x)), _P(scratch), _P(dres), _st(), launches=3 if rows < 148 * 8 * 4 else 2)
     elif scratch is None:
         _call("ddpx_layernorm_bwd", _P(x), _P(dy), _P(gamma), _P(mean), _P(rstd), _P(dx), _P(dgamma), _P(dbeta),
               c_longlong(rows), c_int(C), c_int(_bf(x)), _st())
     else:
         assert scratch.numel() >= layernorm_bwd_scratch_floats(rows, C) and scratch.dtype == torch.float32
         _call("ddpx_layernorm_bwd_ws", _P(x), _P(dy), _P(gamma), _P(mean), _P(rstd), _P(dx), _P(dgamma), _P(dbeta),
-              c_longlong(rows), c_int(C), c_int(_bf(x)), _P(scratch), _st())
+              c_longlong(rows), c_int(C), c_int(_bf(x)), _P(scratch), _st(), launches=3 if rows < 148 * 8 * 4 else 2)
 
 
 def gelu_fwd(x, y):
