@@ -693,10 +693,23 @@ int make_tmap(CUtensorMap* out, const void* base, bool bf16, int rank, const uin
   cuuint32_t bx[5], es[5];
   for (int i = 0; i < rank; ++i) { gdim[i] = dims[i]; bx[i] = box[i]; es[i] = 1; }
   for (int i = 0; i < rank - 1; ++i) gstr[i] = strides_bytes[i];
-  CUresult r = fn(out, bf16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32, rank,
-                  const_cast<void*>(base), gdim, gstr, bx, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
-                  atom32 ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B : CU_TENSOR_MAP_SWIZZLE_128B,
-                  CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  // cuTensorMapEncodeTiled is a driver-API call: it needs a context current on THIS thread.  A thread that has not yet made
+  // a runtime call of its own - autograd's backward thread whose first native operation builds a tensor map - has none
+  // (CUDA_ERROR_INVALID_CONTEXT), so bind the runtime's primary context once per thread, and once more if the driver
+  // still says so.
+  static thread_local bool ctx_bound = false;
+  if (!ctx_bound) { cudaFree(nullptr); ctx_bound = true; }
+  auto encode = [&]() {
+    return fn(out, bf16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32, rank,
+              const_cast<void*>(base), gdim, gstr, bx, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
+              atom32 ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B : CU_TENSOR_MAP_SWIZZLE_128B,
+              CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  };
+  CUresult r = encode();
+  if (r == CUDA_ERROR_INVALID_CONTEXT || r == CUDA_ERROR_NOT_INITIALIZED) {
+    cudaFree(nullptr);
+    r = encode();
+  }
   if (r != CUDA_SUCCESS) {
     fprintf(stderr, "[ddpx] cuTensorMapEncodeTiled failed: %d (rank %d)\n", static_cast<int>(r), rank);
     return DDPX_ERR_TMAP;

@@ -77,7 +77,10 @@ def test_linear_gelu(dtype, tol):
 
 
 @pytest.mark.parametrize("dtype,tol", [(torch.float32, 5e-3), (torch.bfloat16, 3e-2)])
-@pytest.mark.parametrize("B,T,H,hd", [(2, 128, 2, 64), (2, 256, 4, 64), (1, 1024, 2, 64), (2, 200, 3, 64), (1, 128, 2, 32)])
+# the last case has 600 work items (more than the persistent kernels' 148 / 296 CTAs: several rounds of the snake schedule,
+# the last one partial) and a ragged sequence length
+@pytest.mark.parametrize("B,T,H,hd", [(2, 128, 2, 64), (2, 256, 4, 64), (1, 1024, 2, 64), (2, 200, 3, 64), (1, 128, 2, 32),
+                                      (3, 1000, 25, 64)])
 def test_causal_attention(dtype, tol, B, T, H, hd):
     torch.manual_seed(2)
     C = H * hd
