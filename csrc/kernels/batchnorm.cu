@@ -5,6 +5,7 @@
 // convolution epilogue already accumulated (ddpx_conv3x3_fprop), so the forward is ONE pass (normalise + affine +
 // ReLU + optional pool) and the backward is two passes that recompute the ReLU mask and the pool arg-max from the
 // saved pre-BN tensor instead of storing them.
+#include <atomic>
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stdio.h>
@@ -519,14 +520,14 @@ static __device__ __align__(256) float g_bn_static_scratch[2 * DDPX_BN_STATIC_MA
 
 namespace {
 constexpr int kMaxDevices = 64;
-float* g_bn_static_ptr[kMaxDevices] = {nullptr};
+std::atomic<float*> g_bn_static_ptr[kMaxDevices];        // zero-initialised; every thread would store the same value
 
 // `g_bn_static_scratch` in host code is only a handle for the runtime, not a device address: ask the runtime for the
 // address on the current device, once.
 int bn_static_scratch_ptr(float** out) {
   int dev = -1;
   if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= kMaxDevices) return DDPX_ERR_DRIVER;
-  if (g_bn_static_ptr[dev] == nullptr) {
+  if (g_bn_static_ptr[dev].load(std::memory_order_acquire) == nullptr) {
     void* p = nullptr;
     const cudaError_t e = cudaGetSymbolAddress(&p, g_bn_static_scratch);
     if (e != cudaSuccess || p == nullptr) {
@@ -534,9 +535,9 @@ int bn_static_scratch_ptr(float** out) {
               cudaGetErrorString(e));
       return DDPX_ERR_DRIVER;
     }
-    g_bn_static_ptr[dev] = static_cast<float*>(p);
+    g_bn_static_ptr[dev].store(static_cast<float*>(p), std::memory_order_release);
   }
-  *out = g_bn_static_ptr[dev];
+  *out = g_bn_static_ptr[dev].load(std::memory_order_acquire);
   return DDPX_OK;
 }
 }  // namespace

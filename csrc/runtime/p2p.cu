@@ -702,7 +702,7 @@ static int allreduce_impl(int rank, int world, void* const* bufs, void* const* p
   if (mode == 2 && mc == nullptr) return DDPX_ERR_ARG;
   const int vec = is_bf16 ? 8 : 4;
   if (n % vec) return DDPX_ERR_ALIGN;
-  static SlotTable tab;   // filled per call; passed by value
+  SlotTable tab;          // filled per call; passed by value (a local: the launcher is reentrant)
   memset(&tab, 0, sizeof(tab));
   tab.n = nslots;
   for (int i = 0; i < nslots; ++i) {
@@ -766,7 +766,7 @@ extern "C" int ddpx_p2p_broadcast(int rank, int world, void* const* pads, int sr
   int rc = fill_peers(P, rank, world, nullptr, pads);
   if (rc != DDPX_OK) return rc;
   if (n > kMaxSlots) return DDPX_ERR_LIMIT;
-  static CopyTable tab;
+  CopyTable tab;
   memset(&tab, 0, sizeof(tab));
   tab.n = n;
   for (int i = 0; i < n; ++i) { tab.e[i].ptr = ptrs[i]; tab.e[i].offset = offs[i]; tab.e[i].bytes = bytes[i]; }
