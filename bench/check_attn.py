@@ -1,5 +1,5 @@
 """Micro-timings of the attention building blocks at GPT-2-small shape (B=8, H=12, T=1024, hd=64, bf16)."""
-import math, sys
+import sys
 from pathlib import Path
 sys.path.insert(0, str(Path(__file__).resolve().parent.parent))
 import torch

@@ -2,7 +2,6 @@
 (cuobjdump -sass on the object files), written as a markdown table.   python bench/sass_summary.py > profiles/sass_summary.md"""
 import re
 import subprocess
-import sys
 from pathlib import Path
 
 REPO = Path(__file__).resolve().parent.parent

@@ -12,7 +12,6 @@
 from __future__ import annotations
 
 import math
-import os
 from typing import Iterator, Optional
 
 import torch

@@ -7,7 +7,6 @@ implicit-GEMM convolution and the fused BatchNorm kernels read.
 """
 from __future__ import annotations
 
-from typing import Optional
 
 import torch
 import torch.nn.functional as F

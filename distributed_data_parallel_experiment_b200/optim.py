@@ -9,7 +9,6 @@ State lives where ``optimizer.state_dict()`` expects it (``momentum_buffer`` / `
 from __future__ import annotations
 
 import types
-from typing import Optional
 
 import torch
 

@@ -14,7 +14,7 @@ from __future__ import annotations
 
 import ctypes
 import os
-from typing import List, Optional
+from typing import List
 
 import torch
 

@@ -17,7 +17,6 @@ import math
 from typing import List, Optional, Sequence
 
 import torch
-import torch.distributed as dist
 
 from .. import _lib, config
 from .comm import CommBase

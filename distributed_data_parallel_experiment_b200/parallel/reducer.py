@@ -15,7 +15,7 @@ csrc/runtime/reducer_core.cpp; this file owns the tensors:
 from __future__ import annotations
 
 import ctypes
-from typing import List, Optional, Sequence
+from typing import List, Sequence
 
 import torch
 
