@@ -162,3 +162,46 @@ def test_algorithm_table_is_generated_from_sweep_rows(tmp_path):
     shipped = json.loads((REPO / "distributed_data_parallel_experiment_b200" / "parallel" / "algo_table.json").read_text())
     assert p2p.oneshot_max_bytes(8) == shipped["8"]["oneshot_max_bytes"]
     assert p2p.nvls_min_bytes(8) == shipped["8"]["nvls_min_bytes"]
+
+
+def test_select_mode_follows_the_table():
+    """one-shot up to the table's threshold, the in-switch reduction only for multicast-bound buckets, two-shot otherwise;
+    forced algorithms override the table."""
+    from distributed_data_parallel_experiment_b200.parallel import p2p
+    one = p2p.oneshot_max_bytes(8)
+    assert p2p.select_mode("auto", one, 8) == 1 and p2p.select_mode("auto", one + 4, 8) == 0
+    assert p2p.select_mode("auto", 1 << 27, 8, nvls=True) == 2 and p2p.select_mode("auto", 1 << 27, 8, nvls=False) == 0
+    assert p2p.select_mode("twoshot", 64, 8) == 0 and p2p.select_mode("oneshot", 1 << 20, 8) == 1
+
+
+def test_shards_partition_a_bucket():
+    """FusedUpdate.shard_range restates the kernel's shard arithmetic: the ranks' ranges are disjoint, ordered, whole
+    16-byte vectors, and cover the bucket (the last shards may be short or empty)."""
+    from types import SimpleNamespace
+    from distributed_data_parallel_experiment_b200.parallel.p2p import FusedUpdate
+    for world in (2, 3, 8):
+        fake = SimpleNamespace(comm=SimpleNamespace(world_size=world))
+        for dtype, V in ((torch.float32, 4), (torch.bfloat16, 8)):
+            for n in (V, 7 * V, 1856, 6787072, 8 * 1000 + V):
+                got = [FusedUpdate.shard_range(fake, n, dtype, r) for r in range(world)]
+                assert got[0][0] == 0 and got[-1][1] == n
+                for (a0, a1), (b0, b1) in zip(got, got[1:]):
+                    assert a1 == b0 and a0 <= a1 and a0 % V == 0
+                assert all(b >= a for a, b in got)
+
+
+def test_tail_bucket_split():
+    """The reducer gives the last-ready parameters (at most DDPX_SPLIT_TAIL_BYTES) their own bucket on the fused backend
+    and leaves torch's layout alone everywhere else."""
+    from types import SimpleNamespace
+    from distributed_data_parallel_experiment_b200.parallel.reducer import Reducer
+    sizes = [64, 128 * 64 * 9, 128, 128, 64 * 27, 64, 64]          # elements, fp32: ... bn1, conv0 (1728), bn0 x2
+    params = [torch.empty(s) for s in sizes]
+    fused = SimpleNamespace(params=params, comm=SimpleNamespace(supports_fused_update=True))
+    idx = [[0], [1, 2, 3, 4, 5, 6]]
+    out = Reducer._split_tail(fused, idx)
+    assert out[0] == [0] and out[1] + out[2] == idx[1] and len(out) == 3
+    tail_bytes = sum(sizes[i] * 4 for i in out[2])
+    assert 0 < tail_bytes <= 65536 and (sizes[out[1][-1]] * 4 + tail_bytes) > 65536        # as much as fits, no more
+    plain = SimpleNamespace(params=params, comm=SimpleNamespace(supports_fused_update=False))
+    assert Reducer._split_tail(plain, idx) == idx
