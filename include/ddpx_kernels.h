@@ -164,7 +164,8 @@ int ddpx_conv_bn_bwd(const float* y, const float* dout, const float* xin, const 
  * ln_1.{weight,bias}, attn.c_attn.{weight,bias}, attn.c_proj.{weight,bias}, ln_2.{weight,bias}, mlp.c_fc.{weight,bias},
  * mlp.c_proj.{weight,bias}; acts[7] = LN1 out, qkv, attention out, x1, LN2 out, fc pre-activation, fc activation (kept
  * for the backward); stats = fp32 [4*B*T + B*H*Tp]; tmp = bf16 [B*T, C]; backward scratch: wsb = bf16 [B*T, 9C],
- * ws32 = fp32 [4C*C + 13C + B*H*Tp] (first 4C*C all zero on entry, left all zero), cnt = uint32 [16*(4C*C/8192 + 64)] all
+ * ws32 = fp32 [4C*C + 13C + B*H*Tp + ddpx_layernorm_bwd_scratch_floats(B*T, C)] (first 4C*C all zero on entry, left all
+ * zero), cnt = uint32 [16*(4C*C/8192 + 64)] all
  * zero on entry and exit.  Nothing is allocated.  No counterpart in the reference (a CNN). */
 int ddpx_gpt2_block_fwd(const void* x, void* const* params, void* const* acts, float* stats, void* tmp, void* out, int B,
                         int T, int C, int H, float eps, void* stream);
@@ -175,6 +176,7 @@ int ddpx_gpt2_block_bwd(const void* x, const void* dout, void* const* params, vo
 /* ---- fused causal attention, bf16, head dimension 64 (csrc/kernels/attn_sm100.cu, attn_bwd_sm100.cu) ---------------
  * qkv [B][T][3*H*64] (q | k | v, heads contiguous inside each), out / dout [B][T][H*64], lse2 / delta [B][H][Tp] fp32 with
  * Tp = T rounded up to 128 (lse2 = base-2 log-sum-exp of the scaled scores; delta is scratch of the backward).
+ * All three kernels are persistent: one launch of at most 148 (forward: 296) CTAs walks every (batch, head, tile) item.
  * No counterpart in the reference (a CNN); serves the GPT-2 configurations of BASELINE.json. */
 int ddpx_attn_fwd(const void* qkv, void* out, float* lse2, int B, int T, int H, float scale, void* stream);
 int ddpx_attn_bwd(const void* qkv, const void* out, const void* dout, const float* lse2, float* delta, void* dqkv, int B,
