@@ -1,13 +1,15 @@
 // Fused causal attention (flash style) on tcgen05 / TMEM / TMA for sm_100a, bf16, head dimension 64.
 //
 // No [B,H,T,T] tensor exists in either direction:
-//   forward   one CTA per (batch, head, 128-query tile):  S = Q K^T lands in tensor memory, 128 threads (one per query
+//   forward   work item = (batch, head, 128-query tile):  S = Q K^T lands in tensor memory, 128 threads (one per query
 //             row = TMEM lane) run the online softmax, P goes back into tensor memory as bf16 and is the A operand of
 //             O += P V (TS-mode tcgen05.mma: no shared-memory round trip for P); output + per-row log-sum-exp.
-//   backward  probabilities are recomputed from the saved log-sum-exp.  Kernel "dkv" (one CTA per 128-key tile, K and V
-//             resident in tensor memory) walks the query tiles and accumulates dK, dV; kernel "dq" (one CTA per
+//   backward  probabilities are recomputed from the saved log-sum-exp.  Kernel "dkv" (work item = 128-key tile, K and V
+//             resident in tensor memory) walks the query tiles and accumulates dK, dV; kernel "dq" (work item =
 //             128-query tile, Q and dO resident in tensor memory) walks the key tiles and accumulates dQ.  Every
 //             contraction whose left operand lives in tensor memory is a TS-mode MMA.
+// All three kernels are persistent: a fixed number of CTAs (two per SM forward, one per SM backward) walk the items,
+// heaviest first, and the TMA producer runs ahead into the next item.
 //
 // The reference is a CNN (/root/reference/multigpu.py:36-71) and has no attention; this serves the GPT-2 configurations
 // of BASELINE.json, where torch's SDPA/flash kernels are the bar.
